@@ -1,0 +1,79 @@
+"""Generate golden vectors from the LIVE reference module.
+
+Run in the build container only (``/root/reference`` does not exist on the GPU box):
+
+    python tests/golden/make_golden.py
+
+The reference is path-loaded (``model/__init__.py`` imports matplotlib, absent here)
+and built with ``CANNet(load_weights=True)`` (the default constructor downloads
+VGG-16).  Weights come from ``oracle.harness.make_state_dict``
+so fixtures stay small: only outputs, checksums and gradient summaries are stored.
+"""
+import importlib.util
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import harness  # noqa: E402
+
+CASES = [
+    # name, regime, N, H, W
+    ("he_1x64x96", "he", 1, 64, 96),
+    ("he_2x48x80", "he", 2, 48, 80),
+    ("he_1x104x136", "he", 1, 104, 136),
+    ("default_1x64x64", "default", 1, 64, 64),
+    ("ref_1x64x64", "ref", 1, 64, 64),
+    ("he_1x128x192", "he", 1, 128, 192),
+]
+
+
+def load_reference():
+    spec = importlib.util.spec_from_file_location("ref_cannet", "/root/reference/model/CANNet.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def summarize(t):
+    t = t.detach().double().flatten()
+    return np.array([t.sum().item(), t.norm().item(), t.abs().max().item()] + t[:5].tolist())
+
+
+def main():
+    torch.set_num_threads(os.cpu_count())
+    ref = load_reference()
+    out = {}
+    for name, regime, n, h, w in CASES:
+        sd = harness.make_state_dict(regime, seed=0)
+        x = harness.make_input(n, h, w)
+        gt = harness.make_gt(n, h, w)
+        for dt, tag in ((torch.float64, "f64"), (torch.float32, "f32")):
+            m = ref.CANNet(load_weights=True).to(dt)
+            m.load_state_dict({k: v.to(dt) for k, v in sd.items()}, strict=True)
+            feats = {}
+            m.frontend.register_forward_hook(lambda mod, i, o: feats.__setitem__("fv", o.detach().clone()))
+            m.backend.register_forward_hook(lambda mod, i, o: feats.__setitem__("cat", i[0].detach().clone()))
+            et = m(x.to(dt))
+            loss = torch.nn.MSELoss(reduction="sum")(et, gt.to(dt))  # train_eval_utils.py:20,37
+            loss.backward()
+            out[f"{name}/{tag}/out"] = et.detach().numpy()
+            out[f"{name}/{tag}/loss"] = np.array(loss.item())
+            if tag == "f64":
+                out[f"{name}/fv_sum"] = summarize(feats["fv"])
+                out[f"{name}/fi_sum"] = summarize(feats["cat"][:, 512:])
+                # full fv / fi only for the smallest cases (kept < 1 MB each)
+                if h * w <= 64 * 96:
+                    out[f"{name}/fv"] = feats["fv"].float().numpy()
+                    out[f"{name}/fi"] = feats["cat"][:, 512:].float().numpy()
+                for k, p in m.state_dict(keep_vars=True).items():
+                    out[f"{name}/grad/{k}"] = summarize(p.grad)
+        print(name, "ok", out[f"{name}/f64/out"].shape, float(out[f"{name}/f64/loss"]))
+    np.savez_compressed(os.path.join(os.path.dirname(__file__), "cannet_golden.npz"), **out)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,113 @@
+"""CPU: the oracle (numpy restatement + torch-CPU port) against the golden vectors
+generated from the live reference module (tests/golden/make_golden.py)."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import cannet_oracle as O
+from oracle import cannet_torch_cpu as T
+from oracle import harness
+
+CASES = {
+    "he_1x64x96": ("he", 1, 64, 96),
+    "he_2x48x80": ("he", 2, 48, 80),
+    "he_1x104x136": ("he", 1, 104, 136),
+    "default_1x64x64": ("default", 1, 64, 64),
+    "ref_1x64x64": ("ref", 1, 64, 64),
+}
+
+
+def test_state_dict_layout():
+    keys = O.state_dict_keys()
+    assert len(keys) == 42
+    shapes = O.state_dict_shapes()
+    assert sum(int(np.prod(shapes[k])) for k in keys) == 20_719_937
+    assert keys[0] == "frontend.0.weight" and keys[-1] == "conv6_2.weight"
+    assert shapes["backend.0.weight"] == (512, 1024, 3, 3)
+
+
+@pytest.mark.parametrize("in_size", [1, 5, 6, 7, 13, 17, 48, 64, 96, 128, 256])
+@pytest.mark.parametrize("s", [1, 2, 3, 6])
+def test_adaptive_windows_match_aten(in_size, s):
+    # a ramp distinguishes every window: mean of [a,b) of arange is (a+b-1)/2
+    x = torch.arange(in_size, dtype=torch.float64).view(1, 1, 1, in_size)
+    got = F.adaptive_avg_pool2d(x, (1, s)).flatten().numpy()
+    ones = F.adaptive_avg_pool2d(x * x, (1, s)).flatten().numpy()
+    for i, (a, b) in enumerate(O.adaptive_windows(in_size, s)):
+        assert got[i] == pytest.approx((a + b - 1) / 2.0, abs=1e-12)
+        assert ones[i] == pytest.approx(sum(v * v for v in range(a, b)) / (b - a), rel=1e-12)
+
+
+def test_known_overlapping_windows():
+    # SURVEY.md section 8a row C1
+    assert O.adaptive_windows(64, 3) == [(0, 22), (21, 43), (42, 64)]
+    assert O.adaptive_windows(128, 6) == [(0, 22), (21, 43), (42, 64), (64, 86), (85, 107), (106, 128)]
+    assert O.adaptive_windows(96, 6) == [(16 * i, 16 * i + 16) for i in range(6)]
+
+
+@pytest.mark.parametrize("in_size", [1, 2, 3, 6])
+@pytest.mark.parametrize("out_size", [1, 6, 8, 13, 17, 48, 64, 96, 128, 256])
+def test_bilinear_taps_match_aten(in_size, out_size):
+    i0, i1, l0, l1 = O.bilinear_taps(in_size, out_size)
+    # one-hot probes recover the exact fp32 weights ATen applies
+    for k in range(in_size):
+        src = torch.zeros(1, 1, 1, in_size)
+        src[..., k] = 1.0
+        up = F.interpolate(src, size=(1, out_size), mode="bilinear", align_corners=True).flatten().numpy()
+        mine = np.where(i0 == k, l0, 0).astype(np.float32) + np.where(i1 == k, l1, 0).astype(np.float32)
+        assert np.array_equal(up, mine), (in_size, out_size, k)
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_numpy_oracle_matches_reference(golden, name):
+    regime, n, h, w = CASES[name]
+    if h * w > 64 * 96:
+        pytest.skip("numpy oracle kept to the small cases")
+    sd = {k: v.numpy() for k, v in harness.make_state_dict(regime).items()}
+    x = harness.make_input(n, h, w).numpy()
+    out, inter = O.forward(x, sd, dtype=np.float64, return_intermediates=True)
+    ref = golden[f"{name}/f64/out"]
+    assert np.linalg.norm(out - ref) / np.linalg.norm(ref) < 1e-10
+    if f"{name}/fv" in golden.files:
+        assert np.linalg.norm(inter["fv"] - golden[f"{name}/fv"]) / np.linalg.norm(golden[f"{name}/fv"]) < 1e-6
+        assert np.linalg.norm(inter["fi"] - golden[f"{name}/fi"]) / np.linalg.norm(golden[f"{name}/fi"]) < 1e-6
+    gt = harness.make_gt(n, h, w).numpy()
+    assert O.mse_sum(out, gt) == pytest.approx(float(golden[f"{name}/f64/loss"]), rel=1e-10)
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_torch_port_matches_reference(golden, name):
+    regime, n, h, w = CASES[name]
+    sd = harness.make_state_dict(regime)
+    x = harness.make_input(n, h, w)
+    gt = harness.make_gt(n, h, w)
+    loss, out, grads = T.loss_and_grads(x, gt, sd, dtype=torch.float64)
+    ref = torch.from_numpy(golden[f"{name}/f64/out"])
+    assert harness.rel_l2(out, ref) < 1e-10
+    assert float(loss) == pytest.approx(float(golden[f"{name}/f64/loss"]), rel=1e-10)
+    for k, g in grads.items():
+        s = golden[f"{name}/grad/{k}"]
+        assert float(g.norm()) == pytest.approx(s[1], rel=1e-8, abs=1e-300), k
+        assert np.allclose(g.flatten()[:5].numpy(), s[3:], rtol=1e-7, atol=1e-12 * max(1.0, s[2])), k
+
+
+def test_fp32_reference_self_noise(golden):
+    # the tolerance budget: reference fp32 vs fp64
+    for name in CASES:
+        a = torch.from_numpy(golden[f"{name}/f32/out"])
+        b = torch.from_numpy(golden[f"{name}/f64/out"])
+        assert harness.rel_l2(a, b) < 2e-5
+
+
+def test_sgd_oracle_matches_torch():
+    p = torch.randn(50, dtype=torch.float64)
+    g1, g2 = torch.randn(50, dtype=torch.float64), torch.randn(50, dtype=torch.float64)
+    q = p.clone().requires_grad_(True)
+    opt = torch.optim.SGD([q], lr=1e-3, momentum=0.95)
+    pn, buf = p.numpy().copy(), None
+    for g in (g1, g2):
+        q.grad = g.clone()
+        opt.step()
+        pn, buf = O.sgd_momentum_step(pn, g.numpy(), buf, 1e-3, 0.95)
+    assert np.allclose(q.detach().numpy(), pn, rtol=1e-14)
