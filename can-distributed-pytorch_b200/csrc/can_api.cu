@@ -1,0 +1,476 @@
+// extern "C" surface of libcan_b200.so (declared in include/can_b200.h).
+// Host side: argument validation, TMA tensor-map encoding, launch configuration.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cudaTypedefs.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../../include/can_b200.h"
+#include "can_conv_tc.cuh"
+#include "can_simple.cuh"
+#include "can_wgrad_tc.cuh"
+
+using namespace canb;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+int cuda_fail(cudaError_t e, const char* what) {
+  snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+  return static_cast<int>(e);
+}
+#define CAN_CHECK_LAUNCH(what)                                   \
+  do {                                                           \
+    cudaError_t e__ = cudaGetLastError();                        \
+    if (e__ != cudaSuccess) return cuda_fail(e__, what);         \
+  } while (0)
+
+PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  }
+  return fn;
+}
+
+// bf16 tensor map with a 128-byte swizzled box whose innermost extent is 64 elements.
+int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+              const uint32_t* box) {
+  auto enc = get_encode();
+  if (!enc) return fail(-100, "cuTensorMapEncodeTiled entry point not available");
+  uint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(-101, "cuTensorMapEncodeTiled failed (CUresult %d)", static_cast<int>(r));
+  return 0;
+}
+
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+
+constexpr int kMaxSmem = 232448;  // 227 KB opt-in limit per CTA on sm_100
+
+template <int BN, int NSPLIT, int MODE>
+int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p, dim3 grid, int stages_override,
+                cudaStream_t st) {
+  using L = ConvTcSmem<BN, NSPLIT>;
+  const bool ctx = (MODE == MODE_CTX);
+  int stages = (kMaxSmem - L::bytes(0, ctx)) / L::kStageBytes;
+  if (stages > 8) stages = 8;
+  if (stages_override > 0 && stages_override < stages) stages = stages_override;
+  if (stages < 2) return fail(-20, "conv_tc: tile BN=%d nsplit=%d does not fit shared memory", BN, NSPLIT);
+  p.stages = stages;
+  const int smem = L::bytes(stages, ctx);
+  auto kern = conv_tc_kernel<BN, NSPLIT, MODE>;
+  static bool attr_done = false;  // per template instantiation
+  static int attr_smem = 0;
+  if (!attr_done || smem > attr_smem) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tc)");
+    attr_done = true;
+    attr_smem = kMaxSmem;
+  }
+  kern<<<grid, 192, smem, st>>>(tmA, tmB, p);
+  CAN_CHECK_LAUNCH("conv_tc launch");
+  return 0;
+}
+
+template <int BN, int NSPLIT>
+int dispatch_mode(int mode, const CUtensorMap& a, const CUtensorMap& b, ConvTcParams& p, dim3 grid, int so,
+                  cudaStream_t st) {
+  switch (mode) {
+    case MODE_STORE: return launch_conv<BN, NSPLIT, MODE_STORE>(a, b, p, grid, so, st);
+    case MODE_POOL: return launch_conv<BN, NSPLIT, MODE_POOL>(a, b, p, grid, so, st);
+    case MODE_UNPOOL: return launch_conv<BN, NSPLIT, MODE_UNPOOL>(a, b, p, grid, so, st);
+    default: return fail(-21, "conv_tc: mode %d not available for BN=%d", mode, BN);
+  }
+}
+
+
+struct WgradPlan {
+  int TW, TH, tiles_x, tiles_y, total_patches, m_tiles, n_tiles, bn, ksplit, per;
+};
+WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nsplit) {
+  WgradPlan pl;
+  pl.TW = (W >= 16) ? 16 : 8;
+  pl.TH = 64 / pl.TW;
+  pl.tiles_x = (W + pl.TW - 1) / pl.TW;
+  pl.tiles_y = (H + pl.TH - 1) / pl.TH;
+  pl.total_patches = pl.tiles_x * pl.tiles_y * N;
+  pl.m_tiles = (Cout + 127) / 128;
+  pl.bn = Cin < 256 ? Cin : (nsplit > 1 ? 128 : 256);
+  pl.n_tiles = Cin / pl.bn;
+  const int tiles = pl.m_tiles * pl.n_tiles * taps;
+  int ks = (2 * 148 + tiles - 1) / tiles;  // about two CTAs per SM in flight
+  if (ks > pl.total_patches) ks = pl.total_patches;
+  if (ks < 1) ks = 1;
+  pl.per = (pl.total_patches + ks - 1) / ks;
+  pl.ksplit = (pl.total_patches + pl.per - 1) / pl.per;  // every split non-empty
+  return pl;
+}
+
+template <int BN, int NSPLIT>
+int launch_wgrad(const CUtensorMap& tmDZ, const CUtensorMap& tmX, WgradTcParams& p, dim3 grid, cudaStream_t st) {
+  using L = WgradTcSmem<BN, NSPLIT>;
+  int stages = (kMaxSmem - L::bytes(0)) / L::kStageBytes;
+  if (stages > 8) stages = 8;
+  if (stages < 2) return fail(-20, "wgrad_tc: tile BN=%d nsplit=%d does not fit shared memory", BN, NSPLIT);
+  p.stages = stages;
+  auto kern = wgrad_tc_kernel<BN, NSPLIT>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(wgrad_tc)");
+    attr_done = true;
+  }
+  kern<<<grid, 192, L::bytes(stages), st>>>(tmDZ, tmX, p);
+  CAN_CHECK_LAUNCH("wgrad_tc launch");
+  return 0;
+}
+
+int make_act_tmap(CUtensorMap* m, const void* base, int coff, int C, int cs, int64_t plane, int nsplit, int N, int H,
+                  int W, int TW, int TH) {
+  const uint64_t dims[5] = {static_cast<uint64_t>(C), static_cast<uint64_t>(W), static_cast<uint64_t>(H),
+                            static_cast<uint64_t>(N), static_cast<uint64_t>(nsplit)};
+  const uint64_t csb = static_cast<uint64_t>(cs) * 2;
+  const uint64_t pb = nsplit > 1 ? static_cast<uint64_t>(plane) * 2 : csb * W * H * N;
+  const uint64_t str[4] = {csb, csb * W, csb * W * H, pb};
+  const uint32_t box[5] = {64, static_cast<uint32_t>(TW), static_cast<uint32_t>(TH), 1, 1};
+  return make_tmap(m, static_cast<const __nv_bfloat16*>(base) + coff, 5, dims, str, box);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* can_last_error_string(void) { return g_err; }
+int can_version(void) { return 100; }
+
+int can_conv_tc(const can_conv_args* a, void* stream) {
+  if (!a) return fail(-1, "conv_tc: null args");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool ctx = a->mode == CAN_MODE_CTX;
+  if (a->N <= 0 || a->H <= 0 || a->W <= 0) return fail(-2, "conv_tc: bad shape N=%d H=%d W=%d", a->N, a->H, a->W);
+  if (a->Cin <= 0 || a->Cin % 64) return fail(-3, "conv_tc: Cin=%d must be a positive multiple of 64", a->Cin);
+  if (a->taps != 1 && a->taps != 9) return fail(-4, "conv_tc: taps=%d (want 1 or 9)", a->taps);
+  if (a->dil < 1 || a->dil > 4) return fail(-5, "conv_tc: dil=%d", a->dil);
+  if (a->nsplit < 1 || a->nsplit > 2) return fail(-6, "conv_tc: nsplit=%d (want 1 or 2)", a->nsplit);
+  if (!a->x || !a->w) return fail(-7, "conv_tc: null x/w");
+  if (a->x_cs % 8 || a->x_coff % 8 || a->out_cs % 8 || a->out_coff % 8)
+    return fail(-8, "conv_tc: channel strides/offsets must be multiples of 8 (16-byte alignment)");
+  if ((reinterpret_cast<uintptr_t>(a->x) & 15) || (reinterpret_cast<uintptr_t>(a->w) & 15) ||
+      (reinterpret_cast<uintptr_t>(a->out) & 15))
+    return fail(-9, "conv_tc: pointers must be 16-byte aligned");
+  int bn = a->bn;
+  if (ctx) {
+    if (a->Cout != 2048 || a->Cin != 512 || a->taps != 1) return fail(-10, "conv_tc: CTX wants Cin=512 Cout=2048 taps=1");
+    if (!a->tabA || !a->tabB || !a->out) return fail(-10, "conv_tc: CTX needs tabA/tabB/out");
+    bn = 256;
+  } else if (a->mode == CAN_MODE_HEAD) {
+    if (a->Cout != 64 || !a->head_w || !a->head_b || !a->head_out) return fail(-11, "conv_tc: HEAD wants Cout=64, head_w, head_out");
+    bn = 64;
+  } else {
+    if (a->Cout != 64 && a->Cout != 128 && a->Cout != 256 && a->Cout != 512)
+      return fail(-12, "conv_tc: Cout=%d unsupported", a->Cout);
+    if (!a->out) return fail(-12, "conv_tc: null out");
+    if (bn == 0) bn = env_int("CAN_B200_BN", 0);
+    if (bn == 0) bn = a->Cout < 256 ? a->Cout : (a->nsplit > 1 ? 128 : 256);
+    if (bn > a->Cout) bn = a->Cout;
+    if (bn != 64 && bn != 128 && bn != 256) return fail(-13, "conv_tc: bn=%d", bn);
+  }
+  if (a->mode == CAN_MODE_UNPOOL && (!a->mask || !a->arg || a->OH < 2 * a->H || a->OW < 2 * a->W))
+    return fail(-14, "conv_tc: UNPOOL needs mask, arg and OH>=2H, OW>=2W");
+  if (a->mode < 0 || a->mode > CAN_MODE_CTX) return fail(-15, "conv_tc: mode=%d", a->mode);
+
+  ConvTcParams p;
+  memset(&p, 0, sizeof(p));
+  p.N = a->N; p.H = a->H; p.W = a->W;
+  p.kchunks = a->Cin / 64;
+  p.taps = a->taps;
+  p.dil = a->dil;
+  p.TW = (a->W >= 16) ? 16 : 8;
+  p.TH = 128 / p.TW;
+  p.tiles_x = (a->W + p.TW - 1) / p.TW;
+  p.tiles_y = (a->H + p.TH - 1) / p.TH;
+  p.relu = a->relu;
+  p.bias = a->bias;
+  p.out = static_cast<__nv_bfloat16*>(a->out);
+  p.out_plane = a->out_plane;
+  p.out_cs = a->out_cs; p.out_coff = a->out_coff;
+  p.out_f32 = a->out_f32;
+  p.mask = static_cast<const __nv_bfloat16*>(a->mask);
+  p.mask_cs = a->mask_cs; p.mask_coff = a->mask_coff;
+  p.arg = a->arg; p.arg_cs = a->arg_cs;
+  p.OH = a->OH; p.OW = a->OW;
+  p.head_w = a->head_w; p.head_b = a->head_b; p.head_out = a->head_out;
+  p.tabA = a->tabA; p.tabB = a->tabB;
+
+  // activation map: (C, W, H, N, plane), box (64, TW, TH, 1, 1)
+  CUtensorMap tmA, tmB;
+  {
+    const uint64_t dims[5] = {static_cast<uint64_t>(a->Cin), static_cast<uint64_t>(a->W), static_cast<uint64_t>(a->H),
+                              static_cast<uint64_t>(a->N), static_cast<uint64_t>(a->nsplit)};
+    const uint64_t cs = static_cast<uint64_t>(a->x_cs) * 2;
+    const uint64_t plane = a->nsplit > 1 ? static_cast<uint64_t>(a->x_plane) * 2 : cs * a->W * a->H * a->N;
+    const uint64_t str[4] = {cs, cs * a->W, cs * a->W * a->H, plane};
+    const uint32_t box[5] = {64, static_cast<uint32_t>(p.TW), static_cast<uint32_t>(p.TH), 1, 1};
+    const __nv_bfloat16* base = static_cast<const __nv_bfloat16*>(a->x) + a->x_coff;
+    int rc = make_tmap(&tmA, base, 5, dims, str, box);
+    if (rc) return rc;
+  }
+  {
+    const uint64_t K = static_cast<uint64_t>(a->taps) * a->Cin;
+    const uint64_t dims[3] = {K, static_cast<uint64_t>(a->Cout), static_cast<uint64_t>(a->nsplit)};
+    const uint64_t str[2] = {K * 2, K * 2 * a->Cout};
+    const uint32_t box[3] = {64, static_cast<uint32_t>(bn), 1};
+    int rc = make_tmap(&tmB, a->w, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  dim3 grid(p.tiles_x * p.tiles_y * a->N, a->Cout / bn);
+  const int so = a->stages > 0 ? a->stages : env_int("CAN_B200_STAGES", 0);
+  const int ns = a->nsplit;
+  if (ctx) {
+    return ns == 1 ? launch_conv<256, 1, MODE_CTX>(tmA, tmB, p, grid, so, st)
+                   : launch_conv<256, 2, MODE_CTX>(tmA, tmB, p, grid, so, st);
+  }
+  if (a->mode == CAN_MODE_HEAD) {
+    return ns == 1 ? launch_conv<64, 1, MODE_HEAD>(tmA, tmB, p, grid, so, st)
+                   : launch_conv<64, 2, MODE_HEAD>(tmA, tmB, p, grid, so, st);
+  }
+  if (bn == 64) return ns == 1 ? dispatch_mode<64, 1>(a->mode, tmA, tmB, p, grid, so, st)
+                               : dispatch_mode<64, 2>(a->mode, tmA, tmB, p, grid, so, st);
+  if (bn == 128) return ns == 1 ? dispatch_mode<128, 1>(a->mode, tmA, tmB, p, grid, so, st)
+                                : dispatch_mode<128, 2>(a->mode, tmA, tmB, p, grid, so, st);
+  return ns == 1 ? dispatch_mode<256, 1>(a->mode, tmA, tmB, p, grid, so, st)
+                 : dispatch_mode<256, 2>(a->mode, tmA, tmB, p, grid, so, st);
+}
+
+int can_pack_conv_weight(const float* w, void* dst, int cout, int cin, int taps, int nsplit, int dgrad,
+                         void* stream) {
+  if (!w || !dst || cout <= 0 || cin <= 0 || taps <= 0 || nsplit < 1 || nsplit > 3)
+    return fail(-1, "pack_conv_weight: bad arguments");
+  const long long total = static_cast<long long>(cout) * cin * taps;
+  const int blocks = static_cast<int>((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256);
+  pack_conv_weight_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      w, static_cast<__nv_bfloat16*>(dst), cout, cin, taps, nsplit, dgrad);
+  CAN_CHECK_LAUNCH("pack_conv_weight");
+  return 0;
+}
+
+int can_pack_ctx_w2(const float* w0, const float* w1, const float* w2, const float* w3, void* dst, int nsplit,
+                    void* stream) {
+  if (!w0 || !w1 || !w2 || !w3 || !dst || nsplit < 1 || nsplit > 3) return fail(-1, "pack_ctx_w2: bad arguments");
+  pack_ctx_w2_kernel<<<2048, 256, 0, static_cast<cudaStream_t>(stream)>>>(w0, w1, w2, w3,
+                                                                         static_cast<__nv_bfloat16*>(dst), nsplit);
+  CAN_CHECK_LAUNCH("pack_ctx_w2");
+  return 0;
+}
+
+int can_transpose_f32(const float* src, float* dst, int rows, int cols, void* stream) {
+  if (!src || !dst || rows <= 0 || cols <= 0) return fail(-1, "transpose_f32: bad arguments");
+  dim3 grid((cols + 31) / 32, (rows + 31) / 32), block(32, 8);
+  transpose_f32_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(src, dst, rows, cols);
+  CAN_CHECK_LAUNCH("transpose_f32");
+  return 0;
+}
+
+int can_conv_first_fwd(const float* x, const float* w, const float* b, void* out, int64_t out_plane, int nsplit,
+                       int N, int H, int W, void* stream) {
+  if (!x || !w || !b || !out || N <= 0 || H <= 0 || W <= 0 || nsplit < 1 || nsplit > 3)
+    return fail(-1, "conv_first_fwd: bad arguments");
+  if (H > 65535 || N > 65535) return fail(-2, "conv_first_fwd: H or N exceeds grid limits");
+  dim3 grid((W + 127) / 128, H, N);
+  conv_first_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(x, w, b, static_cast<__nv_bfloat16*>(out),
+                                                                        out_plane, nsplit, N, H, W);
+  CAN_CHECK_LAUNCH("conv_first_fwd");
+  return 0;
+}
+
+int64_t can_ctx_pool_workspace_bytes(int N, int H) {
+  return static_cast<int64_t>(N) * H * 12 * 512 * sizeof(float);
+}
+
+int can_ctx_pool_fwd(const void* fv, int64_t fv_plane, int nsplit, int cs, int coff, int N, int H, int W,
+                     const float* w1t, const float* w2t, float* pooled, float* tabA, float* tabB, void* ws,
+                     void* stream) {
+  if (!fv || !w1t || !w2t || !pooled || !tabA || !tabB || !ws) return fail(-1, "ctx_pool_fwd: null pointer");
+  if (N <= 0 || H <= 0 || W <= 0 || N > 65535) return fail(-2, "ctx_pool_fwd: bad shape");
+  if (cs % 2 || coff % 2) return fail(-3, "ctx_pool_fwd: cs/coff must be even");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* R = static_cast<float*>(ws);
+  ctx_pool_rows_kernel<<<dim3(H, N), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(fv), fv_plane, nsplit, cs, coff,
+                                                   R, H, W);
+  CAN_CHECK_LAUNCH("ctx_pool_rows");
+  ctx_pool_finalize_kernel<<<dim3(50, N), 512, 0, st>>>(R, pooled, H, W);
+  CAN_CHECK_LAUNCH("ctx_pool_finalize");
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(ctx_pos_gemv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 36 * 512 * 4);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(ctx_pos_gemv)");
+    attr = true;
+  }
+  ctx_pos_gemv_kernel<<<dim3(8, 4, N), 256, 36 * 512 * 4, st>>>(w1t, pooled, tabA);
+  CAN_CHECK_LAUNCH("ctx_pos_gemv(A)");
+  ctx_pos_gemv_kernel<<<dim3(8, 4, N), 256, 36 * 512 * 4, st>>>(w2t, tabA, tabB);
+  CAN_CHECK_LAUNCH("ctx_pos_gemv(B)");
+  return 0;
+}
+
+int64_t can_mse_count_workspace_bytes(int N) { return static_cast<int64_t>(N) * 4 + 16; }
+
+int can_mse_count_fwd_bwd(const float* et, const float* gt, int N, int HW, float* loss, float* cnt_et, float* cnt_gt,
+                          float* grad, float grad_scale, void* ws, void* stream) {
+  if (!et || !gt || !loss || !cnt_et || !cnt_gt || !ws) return fail(-1, "mse_count: null pointer");
+  if (N <= 0 || HW <= 0) return fail(-2, "mse_count: bad shape N=%d HW=%d", N, HW);
+  float* part = static_cast<float*>(ws);
+  unsigned int* counter = reinterpret_cast<unsigned int*>(part + N);
+  mse_count_kernel<<<N, 1024, 0, static_cast<cudaStream_t>(stream)>>>(et, gt, N, HW, loss, cnt_et, cnt_gt, grad,
+                                                                     grad_scale, part, counter);
+  CAN_CHECK_LAUNCH("mse_count");
+  return 0;
+}
+
+int can_sgd_momentum_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float grad_scale,
+                          int first_step, void* stream) {
+  if (!p || !g || !buf || n <= 0) return fail(-1, "sgd_momentum_step: bad arguments");
+  if ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(buf)) & 15)
+    return fail(-2, "sgd_momentum_step: arenas must be 16-byte aligned");
+  long long blocks = (n / 4 + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  sgd_momentum_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      p, g, buf, n, lr, momentum, grad_scale, first_step);
+  CAN_CHECK_LAUNCH("sgd_momentum_step");
+  return 0;
+}
+
+int can_bilinear_taps(int in_size, int out_size, int32_t* i0, int32_t* i1, float* l0, float* l1, void* stream) {
+  if (in_size <= 0 || out_size <= 0 || !i0 || !i1 || !l0 || !l1) return fail(-1, "bilinear_taps: bad arguments");
+  bilinear_taps_kernel<<<(out_size + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(in_size, out_size, i0,
+                                                                                            i1, l0, l1);
+  CAN_CHECK_LAUNCH("bilinear_taps");
+  return 0;
+}
+
+int can_adaptive_windows(int in_size, int out_size, int32_t* start, int32_t* end, void* stream) {
+  if (in_size <= 0 || out_size <= 0 || out_size > 1024 || !start || !end)
+    return fail(-1, "adaptive_windows: bad arguments");
+  adaptive_windows_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(in_size, out_size, start, end);
+  CAN_CHECK_LAUNCH("adaptive_windows");
+  return 0;
+}
+
+int can_nhwc_to_nchw_f32(const void* src, int64_t plane, int nsplit, int cs, int coff, float* dst, int N, int C, int H,
+                         int W, void* stream) {
+  if (!src || !dst || N <= 0 || C <= 0 || H <= 0 || W <= 0) return fail(-1, "nhwc_to_nchw_f32: bad arguments");
+  nhwc_planes_to_nchw_f32_kernel<<<1184, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(src), plane, nsplit, cs, coff, dst, N, C, H, W);
+  CAN_CHECK_LAUNCH("nhwc_to_nchw_f32");
+  return 0;
+}
+
+int can_nchw_f32_to_nhwc(const float* src, void* dst, int64_t plane, int nsplit, int cs, int coff, int N, int C, int H,
+                         int W, void* stream) {
+  if (!src || !dst || N <= 0 || C <= 0 || H <= 0 || W <= 0) return fail(-1, "nchw_f32_to_nhwc: bad arguments");
+  nchw_f32_to_nhwc_planes_kernel<<<1184, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, static_cast<__nv_bfloat16*>(dst), plane, nsplit, cs, coff, N, C, H, W);
+  CAN_CHECK_LAUNCH("nchw_f32_to_nhwc");
+  return 0;
+}
+
+int64_t can_conv_wgrad_workspace_bytes(int N, int H, int W, int Cin, int Cout, int taps, int nsplit) {
+  if (N <= 0 || H <= 0 || W <= 0 || Cin <= 0 || Cin % 64 || Cout <= 0 || Cout % 64) return -1;
+  const WgradPlan pl = wgrad_plan(N, H, W, Cin, Cout, taps, nsplit);
+  return static_cast<int64_t>(pl.ksplit) * taps * Cout * Cin * sizeof(float);
+}
+
+int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, const void* x, int64_t x_plane, int x_cs,
+                   int x_coff, int nsplit, int N, int H, int W, int Cin, int Cout, int taps, int dil, float* grad,
+                   int accumulate, void* ws, int64_t ws_bytes, void* stream) {
+  if (!dz || !x || !grad || !ws) return fail(-1, "conv_wgrad: null pointer");
+  if (N <= 0 || H <= 0 || W <= 0) return fail(-2, "conv_wgrad: bad shape");
+  if (Cin <= 0 || Cin % 64 || Cout <= 0 || Cout % 64) return fail(-3, "conv_wgrad: Cin/Cout must be multiples of 64");
+  if (Cout > 128 && Cout % 128) return fail(-3, "conv_wgrad: Cout must be 64 or a multiple of 128");
+  if (Cin > 256 && Cin % 256) return fail(-3, "conv_wgrad: Cin must be 64, 128 or a multiple of 256");
+  if (taps != 1 && taps != 9) return fail(-4, "conv_wgrad: taps=%d", taps);
+  if (nsplit < 1 || nsplit > 2) return fail(-5, "conv_wgrad: nsplit=%d", nsplit);
+  if (dz_cs % 8 || dz_coff % 8 || x_cs % 8 || x_coff % 8) return fail(-6, "conv_wgrad: strides/offsets must be multiples of 8");
+  const WgradPlan pl = wgrad_plan(N, H, W, Cin, Cout, taps, nsplit);
+  const int64_t need = static_cast<int64_t>(pl.ksplit) * taps * Cout * Cin * sizeof(float);
+  if (ws_bytes < need) return fail(-7, "conv_wgrad: workspace %lld < %lld bytes", (long long)ws_bytes, (long long)need);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CUtensorMap tmDZ, tmX;
+  int rc = make_act_tmap(&tmDZ, dz, dz_coff, Cout, dz_cs, dz_plane, nsplit, N, H, W, pl.TW, pl.TH);
+  if (rc) return rc;
+  rc = make_act_tmap(&tmX, x, x_coff, Cin, x_cs, x_plane, nsplit, N, H, W, pl.TW, pl.TH);
+  if (rc) return rc;
+  WgradTcParams p;
+  memset(&p, 0, sizeof(p));
+  p.N = N; p.H = H; p.W = W; p.Cout = Cout; p.Cin = Cin; p.taps = taps; p.dil = dil;
+  p.TW = pl.TW; p.TH = pl.TH; p.tiles_x = pl.tiles_x; p.tiles_y = pl.tiles_y;
+  p.m_tiles = pl.m_tiles; p.n_tiles = pl.n_tiles;
+  p.patches_per_split = pl.per; p.total_patches = pl.total_patches;
+  p.m_groups = Cout >= 128 ? 2 : 1;
+  p.ws = static_cast<float*>(ws);
+  dim3 grid(pl.m_tiles * pl.n_tiles * taps, pl.ksplit);
+  if (pl.bn == 64) rc = nsplit == 1 ? launch_wgrad<64, 1>(tmDZ, tmX, p, grid, st) : launch_wgrad<64, 2>(tmDZ, tmX, p, grid, st);
+  else if (pl.bn == 128) rc = nsplit == 1 ? launch_wgrad<128, 1>(tmDZ, tmX, p, grid, st) : launch_wgrad<128, 2>(tmDZ, tmX, p, grid, st);
+  else rc = nsplit == 1 ? launch_wgrad<256, 1>(tmDZ, tmX, p, grid, st) : launch_wgrad<256, 2>(tmDZ, tmX, p, grid, st);
+  if (rc) return rc;
+  const long long total = static_cast<long long>(Cout) * Cin * taps;
+  const int blocks = static_cast<int>((total + 255) / 256 > 2368 ? 2368 : (total + 255) / 256);
+  wgrad_reduce_kernel<<<blocks, 256, 0, st>>>(p.ws, grad, pl.ksplit, taps, Cout, Cin, accumulate);
+  CAN_CHECK_LAUNCH("wgrad_reduce");
+  return 0;
+}
+
+int can_im2col_first(const float* x_nchw, void* out, int64_t out_plane, int nsplit, int N, int H, int W, void* stream) {
+  if (!x_nchw || !out || N <= 0 || H <= 0 || W <= 0 || nsplit < 1 || nsplit > 3) return fail(-1, "im2col_first: bad arguments");
+  im2col_first_kernel<<<148 * 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(x_nchw, static_cast<__nv_bfloat16*>(out),
+                                                                             out_plane, nsplit, N, H, W);
+  CAN_CHECK_LAUNCH("im2col_first");
+  return 0;
+}
+
+int can_bias_grad(const void* dz, int64_t plane, int nsplit, int cs, int coff, int C, int64_t npix, float* db,
+                  void* stream) {
+  if (!dz || !db || C <= 0 || C > 1024 || C % 2 || npix <= 0 || cs % 2 || coff % 2) return fail(-1, "bias_grad: bad arguments");
+  long long blocks = (npix + 63) / 64;
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  bias_grad_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dz), plane, nsplit, cs, coff, C, npix, db);
+  CAN_CHECK_LAUNCH("bias_grad");
+  return 0;
+}
+
+int can_head_bwd(const float* dout, const void* y5, int64_t y_plane, int nsplit, const float* head_w, void* dz,
+                 int64_t dz_plane, int64_t npix, float* d_head_w, float* d_head_b, void* stream) {
+  if (!dout || !y5 || !head_w || !dz || !d_head_w || !d_head_b || npix <= 0) return fail(-1, "head_bwd: bad arguments");
+  long long blocks = (npix + 63) / 64;
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  head_bwd_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      dout, static_cast<const __nv_bfloat16*>(y5), y_plane, nsplit, head_w, static_cast<__nv_bfloat16*>(dz), dz_plane,
+      npix, d_head_w, d_head_b);
+  CAN_CHECK_LAUNCH("head_bwd");
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,457 @@
+// Implicit-GEMM convolution on tcgen05/TMEM fed by TMA (sm_100a).
+//
+//   D[pixel][cout] = sum_{tap, cin} X[pixel + off(tap)][cin] * Wp[cout][tap][cin]
+//
+// One CTA computes a 128-pixel (TH x TW spatial patch of one image) x BN-channel tile:
+//   warp 0   TMA producer: per k-block one 5-D box of the NHWC activation shifted by the
+//            tap offset (out-of-image pixels are zero-filled by TMA = conv padding) and
+//            one box of the K-major packed weights, both 128B-swizzled.
+//   warp 1   allocates TMEM and issues tcgen05.mma (M=128, N=BN, K=16) x4 per k-block.
+//   warps2-5 epilogue: tcgen05.ld the fp32 accumulator, fuse bias / ReLU / 2x2 max-pool /
+//            1x1 density head / ReLU-mask / max-unpool scatter / contextual fusion, store.
+// NSPLIT > 1 is the fp32-parity mode: activations and weights are carried as NSPLIT bf16
+// planes (x = hi + lo [+ lo2]) and the products hi*hi, hi*lo, lo*hi (...) are accumulated
+// in the same fp32 TMEM tile.
+#pragma once
+#include "can_ptx.cuh"
+#include "can_simple.cuh"
+
+namespace canb {
+
+enum ConvMode : int {
+  MODE_STORE = 0,   // y = [relu](acc + bias) [* (mask > 0)]  -> NHWC bf16 planes (+ optional fp32 copy)
+  MODE_POOL = 1,    // y = maxpool2x2(relu(acc + bias))        -> pooled NHWC (+ argmax codes)
+  MODE_HEAD = 2,    // y = relu(acc + bias) stored, and density = y . head_w + head_b (BN == Cout == 64)
+  MODE_UNPOOL = 3,  // g = acc * (mask > 0); scatter to the arg-max position of a 2x upsampled map
+  MODE_CTX = 4,     // contextual fusion epilogue (see can_ctx.cuh comments in can_api.cu)
+};
+
+struct ConvTcParams {
+  int N, H, W;         // spatial size of the GEMM's pixel grid (output == input grid, stride 1)
+  int kchunks;         // Cin / 64
+  int taps;            // 9 (3x3) or 1 (1x1)
+  int dil;             // tap spacing (1 | 2); padding == dil
+  int TW, TH;          // spatial tile, TW*TH == 128, TW in {8,16}
+  int tiles_x, tiles_y;
+  int stages;
+  int relu;
+  const float* bias;   // [Cout] or null
+  // primary output, NHWC bf16 planes
+  __nv_bfloat16* out;
+  long long out_plane;  // elements between planes
+  int out_cs, out_coff; // pixel stride (channels) and channel offset
+  float* out_f32;       // optional fp32 NHWC copy (same cs/coff addressing), may be null
+  // mask source (dgrad): activation whose sign gates the gradient, NHWC bf16 (plane 0)
+  const __nv_bfloat16* mask;
+  int mask_cs, mask_coff;
+  // pool / unpool
+  uint8_t* arg;         // [N][H/2][W/2][C] argmax codes (MODE_POOL writes if non-null, MODE_UNPOOL reads)
+  int arg_cs;
+  int OH, OW;           // MODE_UNPOOL: size of the upsampled map
+  // head
+  const float* head_w;  // [64]
+  const float* head_b;  // [1]
+  float* head_out;      // [N][H][W]
+  // ctx
+  const float* tabA;    // [N][50][512] a_j  = W_j1 pool_j
+  const float* tabB;    // [N][50][512] b_j  = W_j2 a_j
+};
+
+template <int BN, int NSPLIT>
+struct ConvTcSmem {
+  static constexpr int kABytes = 128 * 128;       // 128 pixels x 64 ch x bf16
+  static constexpr int kBBytes = BN * 128;        // BN rows x 64 k x bf16
+  static constexpr int kStageBytes = NSPLIT * (kABytes + kBBytes);
+  static constexpr int kCtxTabBytes = 2 * 50 * 64 * 4;
+  static constexpr int kTailBytes = 1024 + BN * 4;  // barriers + tmem ptr, bias
+  static __host__ __device__ constexpr int bytes(int stages, bool ctx) {
+    return 1024 /*align slack*/ + stages * kStageBytes + kTailBytes + (ctx ? kCtxTabBytes : 0);
+  }
+};
+
+template <int NSPLIT, int NV>
+__device__ __forceinline__ void store_bf16_planes(__nv_bfloat16* base, long long plane, const float* v) {
+  // NV (multiple of 8) values; base is 16B aligned.  Plane k holds bf16(v - sum of planes < k).
+#pragma unroll
+  for (int pl = 0; pl < NSPLIT; ++pl) {
+    __nv_bfloat16* dst = base + pl * plane;
+#pragma unroll
+    for (int i = 0; i < NV; i += 8) {
+      {
+        float r[8];
+        uint4 q;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) r[e] = v[i + e];
+        if (pl > 0) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            float acc = r[e];
+#pragma unroll
+            for (int pp = 0; pp < pl; ++pp) {
+              float h = bf16_round(acc);
+              acc = acc - h;
+            }
+            r[e] = acc;
+          }
+        }
+        q.x = pack_bf16x2(r[0], r[1]);
+        q.y = pack_bf16x2(r[2], r[3]);
+        q.z = pack_bf16x2(r[4], r[5]);
+        q.w = pack_bf16x2(r[6], r[7]);
+        *reinterpret_cast<uint4*>(dst + i) = q;
+      }
+    }
+  }
+}
+
+template <int BN, int NSPLIT, int MODE>
+__global__ void __launch_bounds__(192, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const ConvTcParams p) {
+  using L = ConvTcSmem<BN, NSPLIT>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int stages = p.stages;
+  uint8_t* tail = smem + stages * L::kStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
+  uint64_t* empty_bar = full_bar + 8;
+  uint64_t* tmem_full_bar = empty_bar + 8;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  float* s_bias = reinterpret_cast<float*>(tail + 1024);
+  float* s_tab = s_bias + BN;  // MODE_CTX only: [2][50][64]
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // tile coordinates
+  int t = blockIdx.x;
+  const int tx_i = t % p.tiles_x;
+  t /= p.tiles_x;
+  const int ty_i = t % p.tiles_y;
+  const int n_img = t / p.tiles_y;
+  const int x0 = tx_i * p.TW, y0 = ty_i * p.TH;
+  const int n0 = blockIdx.y * BN;
+  const int num_kb = p.taps * p.kchunks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < stages; ++s) {
+        mbar_init(&full_bar[s], 1);
+        mbar_init(&empty_bar[s], 1);
+      }
+      mbar_init(tmem_full_bar, 1);
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_ptr_smem, BN < 32 ? 32 : BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        const int tap = kb / p.kchunks;
+        const int chunk = kb - tap * p.kchunks;
+        int dy = 0, dx = 0;
+        if (p.taps == 9) {
+          dy = (tap / 3 - 1) * p.dil;
+          dx = (tap % 3 - 1) * p.dil;
+        }
+        uint8_t* sa = smem + stage * L::kStageBytes;
+        uint8_t* sb = sa + NSPLIT * L::kABytes;
+        mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+#pragma unroll
+        for (int pl = 0; pl < NSPLIT; ++pl) {
+          tma_load_5d(sa + pl * L::kABytes, &tmA, &full_bar[stage], chunk * 64, x0 + dx, y0 + dy, n_img, pl);
+          tma_load_3d(sb + pl * L::kBBytes, &tmB, &full_bar[stage], kb * 64, n0, pl);
+        }
+        if (++stage == stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t accum = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
+        const uint32_t sb = sa + NSPLIT * L::kABytes;
+#pragma unroll
+        for (int pa = 0; pa < NSPLIT; ++pa) {
+#pragma unroll
+          for (int pb = 0; pb < NSPLIT; ++pb) {
+            if (pa + pb < NSPLIT) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const uint64_t da = umma_smem_desc(sa + pa * L::kABytes + k * 32, 16, 1024);
+                const uint64_t db = umma_smem_desc(sb + pb * L::kBBytes + k * 32, 16, 1024);
+                umma_bf16(tmem_base, da, db, idesc, accum);
+                accum = 1;
+              }
+            }
+          }
+        }
+        umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+        if (++stage == stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit(tmem_full_bar);  // accumulator complete
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    const int etid = threadIdx.x - 64;
+    for (int i = etid; i < BN; i += 128) s_bias[i] = p.bias ? p.bias[n0 + i] : 0.f;
+    if (MODE == MODE_CTX) {
+      // tables of this image for the 64 channels of this n-tile: [2][50][64]
+      const float* ga = p.tabA + (static_cast<long long>(n_img) * 50) * 512 + blockIdx.y * 64;
+      const float* gb = p.tabB + (static_cast<long long>(n_img) * 50) * 512 + blockIdx.y * 64;
+      for (int i = etid; i < 50 * 16; i += 128) {
+        const int pos = i >> 4, c4 = (i & 15) * 4;
+        *reinterpret_cast<float4*>(s_tab + pos * 64 + c4) = *reinterpret_cast<const float4*>(ga + pos * 512 + c4);
+        *reinterpret_cast<float4*>(s_tab + 3200 + pos * 64 + c4) =
+            *reinterpret_cast<const float4*>(gb + pos * 512 + c4);
+      }
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+
+    const int m = q * 32 + lane;
+    const int ty = m / p.TW, tx = m - ty * p.TW;
+    const int y = y0 + ty, x = x0 + tx;
+    const bool valid = (y < p.H) && (x < p.W);
+    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+
+    if (MODE == MODE_STORE) {
+      const long long pix = (static_cast<long long>(n_img) * p.H + y) * p.W + x;
+      __nv_bfloat16* obase = p.out + pix * p.out_cs + p.out_coff + n0;
+      const __nv_bfloat16* mbase = p.mask ? p.mask + pix * p.mask_cs + p.mask_coff + n0 : nullptr;
+      float* fbase = p.out_f32 ? p.out_f32 + pix * p.out_cs + p.out_coff + n0 : nullptr;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c0, r);
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          v[i] = __uint_as_float(r[i]) + s_bias[c0 + i];
+          if (p.relu) v[i] = fmaxf(v[i], 0.f);
+        }
+        if (valid) {
+          if (mbase) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 8) {
+              uint4 mq = *reinterpret_cast<const uint4*>(mbase + c0 + i);
+              const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mq);
+#pragma unroll
+              for (int e = 0; e < 8; ++e)
+                if (!(__bfloat162float(mb[e]) > 0.f)) v[i + e] = 0.f;
+            }
+          }
+          if (p.out) store_bf16_planes<NSPLIT, 32>(obase + c0, p.out_plane, v);
+          if (fbase) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4)
+              *reinterpret_cast<float4*>(fbase + c0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+          }
+        }
+      }
+    } else if (MODE == MODE_POOL) {
+      // 2x2 window = lanes {l, l^1, l^TW, l^TW^1}; the lane at the even/even corner writes.
+      const int PH = p.H >> 1, PW = p.W >> 1;
+      const int py = y >> 1, px = x >> 1;
+      const bool writer = ((tx & 1) == 0) && ((ty & 1) == 0) && (py < PH) && (px < PW);
+      const int pos = ((ty & 1) << 1) | (tx & 1);  // scan order inside the window
+      const long long ppix = (static_cast<long long>(n_img) * PH + py) * PW + px;
+      __nv_bfloat16* obase = p.out + ppix * p.out_cs + p.out_coff + n0;
+      uint8_t* abase = p.arg ? p.arg + ppix * p.arg_cs + n0 : nullptr;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c0, r);
+        tmem_ld_wait();
+        float v[32];
+        uint32_t codes[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) codes[i] = 0;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          // floor-mode pooling only writes windows that lie fully inside the image, so the
+          // garbage computed for out-of-image tile pixels never reaches a written window.
+          float a = fmaxf(__uint_as_float(r[i]) + s_bias[c0 + i], 0.f);
+          if (NSPLIT == 1) a = bf16_round(a);  // ties are decided on the stored precision
+          float mx = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, 1));
+          mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, p.TW));
+          int code = (a == mx) ? pos : 4;
+          code = min(code, __shfl_xor_sync(0xffffffffu, code, 1));
+          code = min(code, __shfl_xor_sync(0xffffffffu, code, p.TW));
+          v[i] = mx;
+          codes[i >> 2] |= static_cast<uint32_t>(code) << ((i & 3) * 8);
+        }
+        if (writer) {
+          store_bf16_planes<NSPLIT, 32>(obase + c0, p.out_plane, v);
+          if (abase) {
+            *reinterpret_cast<uint4*>(abase + c0) = make_uint4(codes[0], codes[1], codes[2], codes[3]);
+            *reinterpret_cast<uint4*>(abase + c0 + 16) = make_uint4(codes[4], codes[5], codes[6], codes[7]);
+          }
+        }
+      }
+    } else if (MODE == MODE_HEAD) {
+      const long long pix = (static_cast<long long>(n_img) * p.H + y) * p.W + x;
+      __nv_bfloat16* obase = p.out ? p.out + pix * p.out_cs + p.out_coff + n0 : nullptr;
+      float dot = 0.f;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c0, r);
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          v[i] = fmaxf(__uint_as_float(r[i]) + s_bias[c0 + i], 0.f);
+          dot = fmaf(v[i], __ldg(p.head_w + c0 + i), dot);
+        }
+        if (valid && obase) store_bf16_planes<NSPLIT, 32>(obase + c0, p.out_plane, v);
+      }
+      if (valid) p.head_out[pix] = dot + __ldg(p.head_b);
+    } else if (MODE == MODE_UNPOOL) {
+      // this GEMM runs on the pooled grid (H x W); gradients land on the OH x OW map
+      const long long pix = (static_cast<long long>(n_img) * p.H + y) * p.W + x;
+      const __nv_bfloat16* mbase = p.mask + pix * p.mask_cs + p.mask_coff + n0;
+      const uint8_t* abase = p.arg + pix * p.arg_cs + n0;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c0, r);
+        tmem_ld_wait();
+        if (valid) {
+          float g[32];
+          uint32_t code[8];
+          {
+            uint4 a0 = *reinterpret_cast<const uint4*>(abase + c0);
+            uint4 a1 = *reinterpret_cast<const uint4*>(abase + c0 + 16);
+            code[0] = a0.x; code[1] = a0.y; code[2] = a0.z; code[3] = a0.w;
+            code[4] = a1.x; code[5] = a1.y; code[6] = a1.z; code[7] = a1.w;
+          }
+#pragma unroll
+          for (int i = 0; i < 32; i += 8) {
+            uint4 mq = *reinterpret_cast<const uint4*>(mbase + c0 + i);
+            const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mq);
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+              g[i + e] = (__bfloat162float(mb[e]) > 0.f) ? __uint_as_float(r[i + e]) : 0.f;
+          }
+#pragma unroll
+          for (int wpos = 0; wpos < 4; ++wpos) {
+            const int oy = 2 * y + (wpos >> 1), ox = 2 * x + (wpos & 1);
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const int cd = (code[i >> 2] >> ((i & 3) * 8)) & 0xff;
+              v[i] = (cd == wpos) ? g[i] : 0.f;
+            }
+            const long long opix = (static_cast<long long>(n_img) * p.OH + oy) * p.OW + ox;
+            store_bf16_planes<NSPLIT, 32>(p.out + opix * p.out_cs + p.out_coff + n0 + c0, p.out_plane, v);
+          }
+        }
+      }
+    } else if (MODE == MODE_CTX) {
+      // BN == 256 columns = 4 scales x 64 channels of n-tile blockIdx.y; column j*64+c holds
+      // (W_j2 fv)[c].  z_j = U(b_j) - W_j2 fv ; w_j = sigmoid(z_j) ; s_j = U(a_j)
+      // fi = sum_j w_j s_j / (sum_j w_j + 1e-12)            (CANNet.py:47-84)
+      const int SS[4] = {1, 2, 3, 6};
+      const int OFF[4] = {0, 1, 5, 14};
+      int pidx[4][4];
+      float ly0[4], ly1[4], lx0[4], lx1[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        int yi0, yi1, xi0, xi1;
+        bilinear_tap(min(y, p.H - 1), SS[j], p.H, yi0, yi1, ly0[j], ly1[j]);
+        bilinear_tap(min(x, p.W - 1), SS[j], p.W, xi0, xi1, lx0[j], lx1[j]);
+        pidx[j][0] = (OFF[j] + yi0 * SS[j] + xi0) * 64;
+        pidx[j][1] = (OFF[j] + yi0 * SS[j] + xi1) * 64;
+        pidx[j][2] = (OFF[j] + yi1 * SS[j] + xi0) * 64;
+        pidx[j][3] = (OFF[j] + yi1 * SS[j] + xi1) * 64;
+      }
+      const long long pix = (static_cast<long long>(n_img) * p.H + y) * p.W + x;
+      __nv_bfloat16* obase = p.out + pix * p.out_cs + p.out_coff + blockIdx.y * 64;
+      const float* sA = s_tab;
+      const float* sB = s_tab + 3200;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 64; c0 += 16) {
+        uint32_t r[4][16];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) tmem_ld_32x16(taddr + j * 64 + c0, r[j]);
+        tmem_ld_wait();
+        float fi[16];
+#pragma unroll
+        for (int c = 0; c < 16; c += 4) {
+          float num[4] = {0.f, 0.f, 0.f, 0.f}, den[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 a00 = *reinterpret_cast<const float4*>(sA + pidx[j][0] + c0 + c);
+            const float4 a01 = *reinterpret_cast<const float4*>(sA + pidx[j][1] + c0 + c);
+            const float4 a10 = *reinterpret_cast<const float4*>(sA + pidx[j][2] + c0 + c);
+            const float4 a11 = *reinterpret_cast<const float4*>(sA + pidx[j][3] + c0 + c);
+            const float4 b00 = *reinterpret_cast<const float4*>(sB + pidx[j][0] + c0 + c);
+            const float4 b01 = *reinterpret_cast<const float4*>(sB + pidx[j][1] + c0 + c);
+            const float4 b10 = *reinterpret_cast<const float4*>(sB + pidx[j][2] + c0 + c);
+            const float4 b11 = *reinterpret_cast<const float4*>(sB + pidx[j][3] + c0 + c);
+            const float av00[4] = {a00.x, a00.y, a00.z, a00.w}, av01[4] = {a01.x, a01.y, a01.z, a01.w};
+            const float av10[4] = {a10.x, a10.y, a10.z, a10.w}, av11[4] = {a11.x, a11.y, a11.z, a11.w};
+            const float bv00[4] = {b00.x, b00.y, b00.z, b00.w}, bv01[4] = {b01.x, b01.y, b01.z, b01.w};
+            const float bv10[4] = {b10.x, b10.y, b10.z, b10.w}, bv11[4] = {b11.x, b11.y, b11.z, b11.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              // ATen order: h0*(w0*v00 + w1*v01) + h1*(w0*v10 + w1*v11)
+              const float s = ly0[j] * (lx0[j] * av00[e] + lx1[j] * av01[e]) +
+                              ly1[j] * (lx0[j] * av10[e] + lx1[j] * av11[e]);
+              const float u = ly0[j] * (lx0[j] * bv00[e] + lx1[j] * bv01[e]) +
+                              ly1[j] * (lx0[j] * bv10[e] + lx1[j] * bv11[e]);
+              const float z = u - __uint_as_float(r[j][c + e]);
+              const float wgt = 1.f / (1.f + __expf(-z));
+              num[e] = fmaf(wgt, s, num[e]);
+              den[e] += wgt;
+            }
+          }
+#pragma unroll
+          for (int e = 0; e < 4; ++e) fi[c + e] = num[e] / (den[e] + 1e-12f);
+        }
+        if (valid) store_bf16_planes<NSPLIT, 16>(obase + c0, p.out_plane, fi);
+      }
+    }
+    tc_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, BN < 32 ? 32 : BN);
+  }
+}
+
+}  // namespace canb

@@ -1,0 +1,207 @@
+// Weight-gradient GEMM on tcgen05/TMEM fed by TMA (sm_100a).
+//
+//   dW[co][tap][ci] = sum_{n,y,x} dZ[n,y,x,co] * X[n, y+dy(tap), x+dx(tap), ci]
+//
+// GEMM view: M = Cout tile (128), N = Cin tile (BN), K = pixels.  Both operands live in memory
+// as NHWC (channels contiguous), i.e. they are MN-major for this GEMM: a TMA box of
+// (64 channels x 64 pixels) lands as 64 rows of 128 B -- exactly the 128B-swizzled MN-major
+// canonical layout (8-pixel groups 1024 B apart = SBO, 64-channel groups one box apart = LBO).
+// One CTA owns (cout tile, cin tile, tap) and a contiguous slice of the pixel patches
+// (split-K); it writes an fp32 partial tile to the workspace, reduced deterministically by
+// wgrad_reduce_kernel.
+#pragma once
+#include "can_ptx.cuh"
+
+namespace canb {
+
+struct WgradTcParams {
+  int N, H, W;
+  int Cout, Cin;
+  int taps, dil;
+  int TW, TH;  // patch, TW*TH == 64
+  int tiles_x, tiles_y;
+  int m_tiles, n_tiles;
+  int patches_per_split;
+  int total_patches;
+  int stages;
+  int m_groups;  // 64-channel groups of dZ actually loaded (1 when Cout == 64)
+  float* ws;     // [split][tap][Cout][Cin]
+};
+
+template <int BN, int NSPLIT>
+struct WgradTcSmem {
+  static constexpr int kGroupBytes = 64 * 128;            // 64 pixels x 64 ch x bf16
+  static constexpr int kABytes = 2 * kGroupBytes;         // 128 cout
+  static constexpr int kBBytes = (BN / 64) * kGroupBytes;
+  static constexpr int kStageBytes = NSPLIT * (kABytes + kBBytes);
+  static __host__ __device__ constexpr int bytes(int stages) { return 1024 + stages * kStageBytes + 1024; }
+};
+
+template <int BN, int NSPLIT>
+__global__ void __launch_bounds__(192, 1)
+wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant__ CUtensorMap tmX,
+                const WgradTcParams p) {
+  using L = WgradTcSmem<BN, NSPLIT>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int stages = p.stages;
+  uint8_t* tail = smem + stages * L::kStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
+  uint64_t* empty_bar = full_bar + 8;
+  uint64_t* tmem_full_bar = empty_bar + 8;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  int t = blockIdx.x;
+  const int n_tile = t % p.n_tiles;
+  t /= p.n_tiles;
+  const int m_tile = t % p.m_tiles;
+  const int tap = t / p.m_tiles;
+  const int split = blockIdx.y;
+  const int patch_begin = split * p.patches_per_split;
+  const int patch_end = min(patch_begin + p.patches_per_split, p.total_patches);
+  int dy = 0, dx = 0;
+  if (p.taps == 9) {
+    dy = (tap / 3 - 1) * p.dil;
+    dx = (tap % 3 - 1) * p.dil;
+  }
+  const int m_groups = p.m_groups;  // 1 or 2
+  const uint32_t stage_tx = NSPLIT * (m_groups * L::kGroupBytes + L::kBBytes);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmDZ);
+    tma_prefetch_desc(&tmX);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < stages; ++s) {
+        mbar_init(&full_bar[s], 1);
+        mbar_init(&empty_bar[s], 1);
+      }
+      mbar_init(tmem_full_bar, 1);
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_ptr_smem, BN < 32 ? 32 : BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int pid = patch_begin; pid < patch_end; ++pid) {
+        int q = pid;
+        const int tx_i = q % p.tiles_x;
+        q /= p.tiles_x;
+        const int ty_i = q % p.tiles_y;
+        const int n_img = q / p.tiles_y;
+        const int x0 = tx_i * p.TW, y0 = ty_i * p.TH;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sa = smem + stage * L::kStageBytes;
+        uint8_t* sb = sa + NSPLIT * L::kABytes;
+        mbar_expect_tx(&full_bar[stage], stage_tx);
+#pragma unroll
+        for (int pl = 0; pl < NSPLIT; ++pl) {
+          for (int g = 0; g < m_groups; ++g)
+            tma_load_5d(sa + pl * L::kABytes + g * L::kGroupBytes, &tmDZ, &full_bar[stage],
+                        m_tile * 128 + g * 64, x0, y0, n_img, pl);
+#pragma unroll
+          for (int g = 0; g < BN / 64; ++g)
+            tma_load_5d(sb + pl * L::kBBytes + g * L::kGroupBytes, &tmX, &full_bar[stage], n_tile * BN + g * 64,
+                        x0 + dx, y0 + dy, n_img, pl);
+        }
+        if (++stage == stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 1, 1);  // both operands MN-major
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t accum = 0;
+      for (int pid = patch_begin; pid < patch_end; ++pid) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
+        const uint32_t sb = sa + NSPLIT * L::kABytes;
+#pragma unroll
+        for (int pa = 0; pa < NSPLIT; ++pa) {
+#pragma unroll
+          for (int pb = 0; pb < NSPLIT; ++pb) {
+            if (pa + pb < NSPLIT) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {  // 16 pixels (= 2 swizzle atoms of 8 rows) per MMA
+                const uint64_t da = umma_smem_desc(sa + pa * L::kABytes + k * 2048, L::kGroupBytes, 1024);
+                const uint64_t db = umma_smem_desc(sb + pb * L::kBBytes + k * 2048, L::kGroupBytes, 1024);
+                umma_bf16(tmem_base, da, db, idesc, accum);
+                accum = 1;
+              }
+            }
+          }
+        }
+        umma_commit(&empty_bar[stage]);
+        if (++stage == stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit(tmem_full_bar);
+    }
+  } else {
+    const int q = warp & 3;
+    const int co = m_tile * 128 + q * 32 + lane;
+    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    float* dst = p.ws + ((static_cast<long long>(split) * p.taps + tap) * p.Cout + co) * p.Cin + n_tile * BN;
+    const bool valid = (co < p.Cout) && (patch_end > patch_begin);
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      uint32_t r[32];
+      tmem_ld_32x32(taddr + c0, r);
+      tmem_ld_wait();
+      if (valid) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 4)
+          *reinterpret_cast<float4*>(dst + c0 + i) = make_float4(__uint_as_float(r[i]), __uint_as_float(r[i + 1]),
+                                                                 __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, BN < 32 ? 32 : BN);
+  }
+}
+
+// grad[co][ci][tap] (OIHW) (+)= sum_s ws[s][tap][co][ci]
+__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ grad, int splits, int taps,
+                                    int cout, int cin, int accumulate) {
+  const long long total = static_cast<long long>(cout) * cin * taps;
+  const long long slab = total;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    // i indexes ws-within-split order [tap][co][ci] so reads coalesce
+    const int ci = i % cin;
+    const int co = (i / cin) % cout;
+    const int tap = i / (static_cast<long long>(cin) * cout);
+    float acc = 0.f;
+    for (int s = 0; s < splits; ++s) acc += ws[s * slab + i];
+    float* g = grad + (static_cast<long long>(co) * cin + ci) * taps + tap;
+    *g = accumulate ? (*g + acc) : acc;
+  }
+}
+
+}  // namespace canb

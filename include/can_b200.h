@@ -1,0 +1,162 @@
+/* can_b200.h -- C ABI of the B200-native CANNet step kernels (libcan_b200.so).
+ *
+ * The reference (zgzhengSEU/CAN-distributed-pytorch) has no FFI of its own: every FLOP
+ * goes through torch.nn / torch.nn.functional.  Each entry point below therefore cites
+ * the reference call site(s) it replaces.  All pointers are DEVICE pointers owned by
+ * the caller (torch tensors on the Python side); the library never allocates or frees
+ * memory visible to the caller -- scratch comes from caller-provided workspaces sized
+ * by the *_workspace_bytes() queries.  Every launch is asynchronous on `stream`
+ * (a cudaStream_t passed as void*; NULL = legacy default stream).
+ *
+ * Return value: 0 = ok; negative = invalid argument (nothing was launched);
+ * positive = cudaError_t.  can_last_error_string() describes the last failure of the
+ * calling thread.
+ *
+ * Activation layout ("NHWC planes"): bf16 [plane][N][H][W][cs] where the tensor occupies
+ * channels [coff, coff+C) of a pixel stride `cs`.  nsplit = 1 is the bf16 path; nsplit = 2
+ * (3) is the fp32-parity path: value = plane0 + plane1 (+ plane2), each plane bf16, the
+ * products hi*hi + hi*lo + lo*hi (...) accumulated in fp32 on the tensor cores.
+ */
+#ifndef CAN_B200_H_
+#define CAN_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* can_last_error_string(void);
+int can_version(void);
+
+/* ---- modes of the tcgen05 implicit-GEMM kernel -------------------------------------- */
+enum {
+  CAN_MODE_STORE = 0,  /* y = [relu](acc + bias) [* (mask > 0)]                              */
+  CAN_MODE_POOL = 1,   /* y = maxpool2x2(relu(acc + bias)), optional argmax codes            */
+  CAN_MODE_HEAD = 2,   /* y = relu(acc + bias) and density = y . head_w + head_b (Cout == 64) */
+  CAN_MODE_UNPOOL = 3, /* g = acc * (mask > 0) scattered to the argmax slot of the 2x map    */
+  CAN_MODE_CTX = 4     /* contextual fusion epilogue                                         */
+};
+
+typedef struct can_conv_args {
+  int32_t N, H, W;       /* pixel grid of the GEMM (output grid == input grid; stride 1)     */
+  int32_t Cin, Cout;     /* Cin % 64 == 0; Cout in {64,128,256,512} (2048 for CAN_MODE_CTX)   */
+  int32_t taps;          /* 9 = 3x3, 1 = 1x1                                                  */
+  int32_t dil;           /* dilation == padding: 1 (frontend) or 2 (backend)                  */
+  int32_t nsplit;        /* 1 = bf16, 2 = split-bf16 fp32-parity path                         */
+  int32_t mode;          /* CAN_MODE_*                                                        */
+  int32_t relu;          /* CAN_MODE_STORE only                                               */
+  int32_t bn;            /* N-tile override (0 = auto): 64 | 128 | 256                        */
+  int32_t stages;        /* pipeline-depth override (0 = auto)                                */
+  const void* x;         /* input activation, NHWC planes                                     */
+  int64_t x_plane;
+  int32_t x_cs, x_coff;
+  const void* w;         /* packed weights [plane][Cout][taps][Cin] bf16 (can_pack_conv_weight) */
+  const float* bias;     /* [Cout] fp32 or NULL                                               */
+  void* out;             /* output NHWC planes (pooled grid for POOL, 2x grid for UNPOOL)     */
+  int64_t out_plane;
+  int32_t out_cs, out_coff;
+  float* out_f32;        /* optional fp32 NHWC copy of the output (STORE)                     */
+  const void* mask;      /* STORE/UNPOOL: activation whose sign gates the result (plane 0)    */
+  int32_t mask_cs, mask_coff;
+  uint8_t* arg;          /* POOL: argmax codes out (may be NULL); UNPOOL: codes in            */
+  int32_t arg_cs;
+  int32_t OH, OW;        /* UNPOOL: size of the upsampled map                                 */
+  const float* head_w;   /* HEAD: [64]                                                        */
+  const float* head_b;  /* HEAD: [1] (device pointer: no host sync to read the bias)             */
+  float* head_out;       /* HEAD: [N][H][W] fp32 density                                      */
+  const float* tabA;     /* CTX: [N][50][512] a_j = conv{S}_1(pool_S(fv))                     */
+  const float* tabB;     /* CTX: [N][50][512] b_j = conv{S}_2(a_j)                            */
+} can_conv_args;
+
+/* The dense contractions of the step on tcgen05/TMEM fed by TMA.
+ *   forward 3x3 / dilated 3x3 + bias + ReLU      model/CANNet.py:14-16 via make_layers :104-121
+ *   + fused MaxPool2d(2,2)                       model/CANNet.py:112
+ *   + fused output_layer (1x1, 64->1)            model/CANNet.py:17,90
+ *   dgrad (same kernel on dgrad-packed weights, ReLU mask / max-unpool fused):
+ *                                                autograd of the above, utils/train_eval_utils.py:38
+ *   CAN_MODE_CTX: contrast 1x1 convs + sigmoid + weighted fusion, written into the channel
+ *   half [512,1024) of the backend input (no torch.cat):   model/CANNet.py:45-49,54-58,63-67,
+ *                                                75-81,84,87                                 */
+int can_conv_tc(const can_conv_args* args, void* stream);
+
+/* conv weight [Cout][Cin][kh][kw] fp32 -> packed bf16 planes.
+ * dgrad = 0: dst[pl][co][tap][ci]; dgrad = 1: dst[pl][ci][taps-1-tap][co] (transposed, flipped).
+ * Replaces cuDNN's internal filter transforms for nn.Conv2d (model/CANNet.py:114).          */
+int can_pack_conv_weight(const float* w, void* dst, int cout, int cin, int taps, int nsplit, int dgrad,
+                         void* stream);
+/* conv{1,2,3,6}_2.weight -> stacked [plane][2048][512] in (channel-chunk, scale, channel) row
+ * order for CAN_MODE_CTX (model/CANNet.py:19,21,23,25).                                      */
+int can_pack_ctx_w2(const float* w1_2, const float* w2_2, const float* w3_2, const float* w6_2, void* dst,
+                    int nsplit, void* stream);
+int can_transpose_f32(const float* src, float* dst, int rows, int cols, void* stream);
+
+/* First convolution 3->64 + bias + ReLU on the caller's NCHW fp32 image
+ * (frontend.0 + frontend.1, model/CANNet.py:14,40). out: NHWC planes, cs = 64.               */
+int can_conv_first_fwd(const float* x_nchw, const float* w, const float* b, void* out, int64_t out_plane,
+                       int nsplit, int N, int H, int W, void* stream);
+
+/* K1: multi-scale adaptive average pooling (S = 1,2,3,6) in ONE pass over fv, then the
+ * per-position 1x1 convs.  Replaces 4x F.adaptive_avg_pool2d + conv{S}_1 (+ conv{S}_2 on the
+ * <=36 pooled positions, valid because a bias-free 1x1 conv commutes with bilinear upsampling):
+ * model/CANNet.py:42-43,51-52,60-61,70-72.
+ *   w1t / w2t : [4][512(ci)][512(co)] fp32 transposed conv{S}_1 / conv{S}_2 weights
+ *   pooled, tabA, tabB : [N][50][512] fp32; positions ordered S=1 | S=2 (4) | S=3 (9) | S=6 (36)
+ *   ws : can_ctx_pool_workspace_bytes(N, H) bytes                                            */
+int64_t can_ctx_pool_workspace_bytes(int N, int H);
+int can_ctx_pool_fwd(const void* fv, int64_t fv_plane, int nsplit, int cs, int coff, int N, int H, int W,
+                     const float* w1t, const float* w2t, float* pooled, float* tabA, float* tabB, void* ws,
+                     void* stream);
+
+/* Fused MSELoss(reduction='sum') + per-image counts + dL/d(et)
+ * (utils/train_eval_utils.py:20,37,83; test.py:32).  grad may be NULL (inference).
+ * ws: can_mse_count_workspace_bytes(N) bytes, zero-initialised once by the caller.           */
+int64_t can_mse_count_workspace_bytes(int N);
+int can_mse_count_fwd_bwd(const float* et, const float* gt, int N, int HW, float* loss, float* cnt_et,
+                          float* cnt_gt, float* grad, float grad_scale, void* ws, void* stream);
+
+/* torch.optim.SGD(momentum, dampening 0, no nesterov, wd 0) over a flat fp32 arena
+ * (train.py:63,125-126; utils/train_eval_utils.py:52).  g is multiplied by grad_scale first. */
+int can_sgd_momentum_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum,
+                          float grad_scale, int first_step, void* stream);
+
+/* Weight gradient of a 3x3 / dilated 3x3 / 1x1 convolution on tcgen05 (both operands MN-major,
+ * split-K over pixel patches, deterministic reduction):
+ *   grad[co][ci][tap] (+)= sum_{n,y,x} dz[n,y,x,co] * x[n, y+dy, x+dx, ci]
+ * Replaces cuDNN backward-filter under loss.backward() (utils/train_eval_utils.py:38) for the
+ * layers built at model/CANNet.py:14-16,19,21,23,25.  grad is fp32 in the parameter's own
+ * [Cout][Cin][kh][kw] layout; ws: can_conv_wgrad_workspace_bytes(...) bytes of scratch.        */
+int64_t can_conv_wgrad_workspace_bytes(int N, int H, int W, int Cin, int Cout, int taps, int nsplit);
+int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, const void* x, int64_t x_plane,
+                   int x_cs, int x_coff, int nsplit, int N, int H, int W, int Cin, int Cout, int taps, int dil,
+                   float* grad, int accumulate, void* ws, int64_t ws_bytes, void* stream);
+
+/* im2col of the 3-channel image: out[pl][n][y][x][64], k = ci*9 + r*3 + s (27 used, rest zero),
+ * which turns frontend.0 (model/CANNet.py:14) into a K=64 1x1 GEMM for its weight gradient.    */
+int can_im2col_first(const float* x_nchw, void* out, int64_t out_plane, int nsplit, int N, int H, int W,
+                     void* stream);
+
+/* db[c] += sum_pixels dz[pixel][c]  (bias gradient of every conv; db must be initialised).    */
+int can_bias_grad(const void* dz, int64_t plane, int nsplit, int cs, int coff, int C, int64_t npix, float* db,
+                  void* stream);
+
+/* Backward of output_layer (model/CANNet.py:17,90) fused with the ReLU mask of backend.10:
+ * dz[pix][c] = dout[pix] * head_w[c] * (y5 > 0); d_head_w += sum dout*y5; d_head_b += sum dout. */
+int can_head_bwd(const float* dout, const void* y5, int64_t y_plane, int nsplit, const float* head_w, void* dz,
+                 int64_t dz_plane, int64_t npix, float* d_head_w, float* d_head_b, void* stream);
+
+/* Index-table probes: the exact device arithmetic of the pooling windows and bilinear taps
+ * (ATen AdaptivePooling.h:32-38, UpSample.h:271-295,442-476 as used by model/CANNet.py:42-76). */
+int can_bilinear_taps(int in_size, int out_size, int32_t* i0, int32_t* i1, float* l0, float* l1, void* stream);
+int can_adaptive_windows(int in_size, int out_size, int32_t* start, int32_t* end, void* stream);
+
+/* Layout probes / boundary transposes between the caller's NCHW fp32 and NHWC planes.        */
+int can_nhwc_to_nchw_f32(const void* src, int64_t plane, int nsplit, int cs, int coff, float* dst, int N, int C,
+                         int H, int W, void* stream);
+int can_nchw_f32_to_nhwc(const float* src, void* dst, int64_t plane, int nsplit, int cs, int coff, int N, int C,
+                         int H, int W, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CAN_B200_H_ */
