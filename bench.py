@@ -1,0 +1,284 @@
+#!/usr/bin/env python
+"""bench.py -- CANNet step throughput on B200 (contract: see the task statement / DESIGN.md section 6).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload train|infer] [--impl reference]
+
+One JSON line on rank 0.  ``value`` = whole-job images/sec with inputs resident in HBM;
+``e2e`` = the same metric through the public API (``model(img)`` / ``train_step``) with pinned
+host inputs copied in and the result read back every step; ``roofline`` = the dominant kernel
+(tcgen05 implicit-GEMM conv) against the measured bf16 peak; ``cpu_baseline`` = the oracle's
+torch-CPU port of the reference on this box's host cores (bounded sample).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "can-distributed-pytorch_b200"))
+
+WORKLOADS = {
+    # BASELINE.json configs[3] (the config the metric "train imgs/sec @3x768x1024" is quoted on)
+    "train": dict(name="train_768x1024_b4_bf16", batch=4, H=768, W=1024, train=True),
+    # BASELINE.json configs[1]
+    "infer": dict(name="infer_768x1024_b16_bf16", batch=16, H=768, W=1024, train=False),
+}
+FWD_GFLOP_768 = 733.36  # SURVEY.md section 8d, algorithmic, per image
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("CAN_B200_WORKLOAD", "auto"))
+    ap.add_argument("--batch", type=int, default=0, help="override per-GPU batch")
+    ap.add_argument("--precision", default="bf16")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def pick_workload(args):
+    name = args.workload
+    if name == "auto":
+        from can_b200 import engine
+        name = "train" if hasattr(engine, "backward") else "infer"
+    wl = dict(WORKLOADS[name])
+    if args.batch:
+        wl["batch"] = args.batch
+        wl["name"] = wl["name"].replace("_b4_", f"_b{args.batch}_").replace("_b16_", f"_b{args.batch}_")
+    return wl
+
+
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return d.get("bf16_tflops_sustained", d.get("bf16_tflops")), d.get("hbm_gbs"), "measured (MEASURED_PEAKS.json, sustained)"
+    return 1400.0, 6650.0, "fallback (B200_PROFILING.md: ~1.4 PFLOP/s sustained, 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------------------------------
+def cpu_reference_images_per_sec(wl, n_timed, warm=1):
+    """The reference's CPU PyTorch path (oracle torch-CPU port; /root/reference is not on this box).
+    Sample: one image of the workload's shape per timed iteration."""
+    import torch
+    from oracle import cannet_torch_cpu as T
+    from oracle import harness
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = harness.make_state_dict("he")
+    x = harness.make_input(1, wl["H"], wl["W"])
+    gt = harness.make_gt(1, wl["H"], wl["W"])
+    bufs = {}
+    times = []
+    for it in range(warm + n_timed):
+        t0 = time.perf_counter()
+        if wl["train"]:
+            T.train_step(x, gt, sd, bufs, lr=1e-7)
+        else:
+            with torch.no_grad():
+                T.forward(x, sd)
+        if it >= warm:
+            times.append(time.perf_counter() - t0)
+    times.sort()
+    med = times[len(times) // 2]
+    return 1.0 / med, cores, torch.get_num_threads(), f"{warm}+{n_timed} x one {wl['H']}x{wl['W']} image ({'fwd+bwd+SGD' if wl['train'] else 'forward'}), fp32, median"
+
+
+def run_reference(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    ips, cores, threads, sample = cpu_reference_images_per_sec(wl, n_timed=max(1, min(args.steps, 5)), warm=max(1, min(args.warmup, 2)))
+    line = {
+        "impl": "reference", "metric": "images_per_sec", "value": ips, "unit": "img/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / ips, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["name"], "note": "reference CPU path = oracle torch-CPU port, one image per step"},
+        "cpu_baseline": {"value": ips, "unit": "img/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": ips, "unit": "img/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    wl = pick_workload(args)
+    if args.impl == "reference":
+        run_reference(args, wl)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from can_b200 import ops
+    from can_b200.model import CANNet
+    from oracle import harness  # weights/input generators only (test infrastructure, not on the timed path)
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    B, H, W = wl["batch"], wl["H"], wl["W"]
+    model = CANNet(load_weights=True)
+    model.load_state_dict(harness.make_state_dict("he"))
+    model = model.to(dev)
+    model.precision = args.precision
+
+    # resident inputs: distinct seed per rank
+    x_host = harness.make_input(B, H, W, seed=1234 + rank).pin_memory()
+    gt_host = harness.make_gt(B, H, W, seed=4321 + rank).pin_memory()
+    x_dev, gt_dev = x_host.to(dev), gt_host.to(dev)
+
+    if wl["train"]:
+        from can_b200.utils.train_eval_utils import FusedTrainer
+        trainer = FusedTrainer(model, lr=1e-7 * world, momentum=0.95)
+
+        def step_resident():
+            return trainer.step(x_dev, gt_dev)
+
+        def step_e2e():
+            xd = x_host.to(dev, non_blocking=True)
+            gd = gt_host.to(dev, non_blocking=True)
+            return trainer.step(xd, gd).cpu()   # device->host read of the step's loss
+    else:
+        def step_resident():
+            with torch.no_grad():
+                out = model(x_dev)
+                return ops.mse_count(out, gt_dev, want_grad=False)[1]
+
+        def step_e2e():
+            with torch.no_grad():
+                xd = x_host.to(dev, non_blocking=True)
+                out = model(xd)
+                return ops.mse_count(out, gt_host.to(dev, non_blocking=True), want_grad=False)[1].cpu()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms
+
+    for _ in range(max(3, args.warmup)):
+        step_resident()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ops.LAUNCHES = 0
+    ms = timed(step_resident, args.steps)
+    launches = ops.LAUNCHES
+    clocks = sampler.stop()
+    ips = world * B * args.steps / (ms * 1e-3)
+
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+    ips_e2e = world * B * args.steps / (ms_e2e * 1e-3)
+    h2d = x_host.numel() * 4 + gt_host.numel() * 4
+    d2h = 4 if wl["train"] else 4 * B
+
+    # roofline of the dominant kernel: a second pass of the same steps with an event pair around
+    # every conv_tc / wgrad launch (kept out of the timed region so it cannot perturb `value`)
+    ops.PROFILE = []
+    torch.cuda.synchronize()
+    for _ in range(min(args.steps, 5)):
+        step_resident()
+    torch.cuda.synchronize()
+    prof, ops.PROFILE = ops.PROFILE, None
+    k_ms = sum(a.elapsed_time(b) for a, b, _ in prof)
+    k_flop = sum(f for _, _, f in prof)
+    peak_tf, peak_hbm, peak_src = measured_peaks()
+    achieved = (k_flop / 1e12) / (k_ms * 1e-3) if k_ms > 0 else 0.0
+    roofline = {"bound": "tensor", "kernel": "conv_tc_kernel/wgrad_tc_kernel (tcgen05 implicit GEMM)",
+                "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
+                "traffic": None, "peak_source": peak_src, "launches_per_step": len(prof) // max(1, min(args.steps, 5)),
+                "share_of_step": (k_ms / max(1, min(args.steps, 5))) / (ms / args.steps)}
+
+    if rank == 0:
+        line = {
+            "metric": "images_per_sec", "value": ips, "unit": "img/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": args.precision if args.precision == "bf16" else "f32(split-bf16)",
+            "data": "synthetic",
+            "config": {"workload": wl["name"], "per_gpu_batch": B, "global_batch": B * world, "H": H, "W": W,
+                       "l2_policy": "inputs+activations per step exceed the 126 MB L2 (no explicit flush)",
+                       "parallelism": f"dp{world}"},
+            "clocks": clocks,
+            "e2e": {"value": ips_e2e, "unit": "img/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": launches,
+            "roofline": roofline,
+            "model_tflops": ips * FWD_GFLOP_768 * (3 if wl["train"] else 1) / 1e3 / world,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            v, cores, threads, sample = cpu_reference_images_per_sec(wl, n_timed=3 if not wl["train"] else 2)
+            line["cpu_baseline"] = {"value": v, "unit": "img/s", "cores": threads, "kind": "port", "sample": sample}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

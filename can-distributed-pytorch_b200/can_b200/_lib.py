@@ -11,7 +11,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libcan_b200.so")
 
-MODE_STORE, MODE_POOL, MODE_HEAD, MODE_UNPOOL, MODE_CTX = range(5)
+MODE_STORE, MODE_POOL, MODE_HEAD, MODE_UNPOOL, MODE_CTX, MODE_CTX_BWD, MODE_DFV = range(7)
 
 
 class ConvArgs(C.Structure):
@@ -25,7 +25,8 @@ class ConvArgs(C.Structure):
         ("w", C.c_void_p), ("bias", C.c_void_p),
         ("out", C.c_void_p), ("out_plane", C.c_int64), ("out_cs", C.c_int32), ("out_coff", C.c_int32),
         ("out_f32", C.c_void_p),
-        ("mask", C.c_void_p), ("mask_cs", C.c_int32), ("mask_coff", C.c_int32),
+        ("mask", C.c_void_p), ("mask_cs", C.c_int32), ("mask_coff", C.c_int32), ("mask_plane", C.c_int64),
+        ("add", C.c_void_p), ("add_plane", C.c_int64), ("add_cs", C.c_int32), ("add_coff", C.c_int32),
         ("arg", C.c_void_p), ("arg_cs", C.c_int32),
         ("OH", C.c_int32), ("OW", C.c_int32),
         ("head_w", C.c_void_p), ("head_b", C.c_void_p), ("head_out", C.c_void_p),
@@ -49,6 +50,19 @@ _SIGNATURES = {
                               + [C.c_float, C.c_void_p, C.c_void_p]),
     "can_sgd_momentum_step": (C.c_int, [C.c_void_p] * 3 + [C.c_int64, C.c_float, C.c_float, C.c_float, C.c_int,
                                                           C.c_void_p]),
+    "can_conv_wgrad_workspace_bytes": (C.c_int64, [C.c_int] * 7),
+    "can_conv_wgrad": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_int]
+                       + [C.c_int] * 8 + [C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_int64, C.c_void_p]),
+    "can_ctx_wint": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "can_ctx_pos_gemv": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
+                                   C.c_int, C.c_void_p]),
+    "can_ctx_outer": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int, C.c_void_p,
+                                C.c_float, C.c_int, C.c_void_p]),
+    "can_im2col_first": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "can_bias_grad": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_void_p,
+                                C.c_void_p]),
+    "can_head_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_int64,
+                               C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "can_bilinear_taps": (C.c_int, [C.c_int, C.c_int] + [C.c_void_p] * 5),
     "can_adaptive_windows": (C.c_int, [C.c_int, C.c_int] + [C.c_void_p] * 3),
     "can_nhwc_to_nchw_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p]

@@ -2,21 +2,27 @@
 
 ``forward`` runs model/CANNet.py:39-91 of the reference as 17 tcgen05 implicit-GEMM
 launches plus the small HBM-bound kernels; ``backward`` (autograd of the same graph,
-utils/train_eval_utils.py:38) reuses the saved NHWC activations.  Packed weights are cached
+utils/train_eval_utils.py:38) reuses the saved NHWC activations: per conv one dgrad launch
+(the same implicit-GEMM kernel on transposed/flipped weights with the ReLU mask or max-unpool
+fused) and one wgrad launch (MN-major tcgen05 GEMM over pixels).  Packed weights are cached
 per parameter version, so a training loop re-packs after every optimizer step and an
 inference loop packs once.
+
+Parameter order everywhere = ``model.parameters()`` = the reference's state_dict order:
+frontend (w,b) x10, backend (w,b) x6, output_layer (w,b), conv{1,2,3,6}_{1,2}.weight.
 """
 from __future__ import annotations
 
 import torch
 
 from . import ops
-from .ops import MODE_CTX, MODE_HEAD, MODE_POOL, MODE_STORE, MODE_UNPOOL, Act
+from .ops import (MODE_CTX, MODE_CTX_BWD, MODE_DFV, MODE_HEAD, MODE_POOL, MODE_STORE, MODE_UNPOOL, Act)
 
 FRONTEND_CONVS = (0, 2, 5, 7, 10, 12, 14, 17, 19, 21)  # Sequential indices, CANNet.py:104-121
-FRONTEND_POOL_AFTER = (2, 7, 14)                        # convs followed by MaxPool2d(2,2)
+POOLED_LAYERS = (1, 3, 6)                               # frontend convs followed by MaxPool2d(2,2)
 BACKEND_CONVS = (0, 2, 4, 6, 8, 10)
 SCALES = (1, 2, 3, 6)
+IDX_BACKEND, IDX_HEAD, IDX_CTX = 20, 32, 34             # offsets into the parameter list
 
 
 class WeightCache:
@@ -35,11 +41,22 @@ class WeightCache:
             self._store[key] = hit
         return hit[1]
 
+    def invalidate(self):
+        """Drop every entry derived from parameters (after an in-place arena update, which does
+        not bump version counters); shape-only entries (empty tag) are kept."""
+        self._store = {k: v for k, v in self._store.items() if v[0] == ()}
+
 
 def _conv_params(model):
     fr = [(model.frontend[i].weight, model.frontend[i].bias) for i in FRONTEND_CONVS]
     bk = [(model.backend[i].weight, model.backend[i].bias) for i in BACKEND_CONVS]
     return fr, bk
+
+
+def _ctx_weights(model):
+    w1s = [getattr(model, f"conv{s}_1").weight for s in SCALES]
+    w2s = [getattr(model, f"conv{s}_2").weight for s in SCALES]
+    return w1s, w2s
 
 
 def forward(model, x: torch.Tensor, nsplit: int, save: bool):
@@ -57,13 +74,13 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
     acts = [a]
     args = {}
     h, w = H, W
+    cat = None
     for li in range(1, 10):
         wt, bs = fr[li]
-        cout, cin = wt.shape[0], wt.shape[1]
+        cout = wt.shape[0]
         wp = cache.get(("f", li, nsplit), (wt,), lambda wt=wt: ops.pack_conv_weight(wt, nsplit))
         bias = bs.detach().float()
-        pool = FRONTEND_CONVS[li] in FRONTEND_POOL_AFTER
-        if pool:
+        if li in POOLED_LAYERS:
             h, w = h // 2, w // 2
             out = ops.new_act(nsplit, N, h, w, cout, dev)
             arg = torch.empty(N, h, w, cout, device=dev, dtype=torch.uint8) if save else None
@@ -82,12 +99,11 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
     fv = a
 
     # ---- contextual module (CANNet.py:42-87) --------------------------------------
-    w1s = [getattr(model, f"conv{s}_1").weight for s in SCALES]
-    w2s = [getattr(model, f"conv{s}_2").weight for s in SCALES]
-    w1t = cache.get(("w1t",), w1s, lambda: ops.transpose_stack(w1s))
-    w2t = cache.get(("w2t",), w2s, lambda: ops.transpose_stack(w2s))
+    w1s, w2s = _ctx_weights(model)
+    w1 = cache.get(("w1",), w1s, lambda: ops.stack_1x1(w1s))
+    w2 = cache.get(("w2",), w2s, lambda: ops.stack_1x1(w2s))
     w2stack = cache.get(("w2stack", nsplit), w2s, lambda: ops.pack_ctx_w2(w2s, nsplit))
-    pooled, tabA, tabB = ops.ctx_pool(fv, w1t, w2t)
+    pooled, tabA, tabB = ops.ctx_pool(fv, w1, w2)
     fi = cat.view(512, 512)
     ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX, out=fi, tabA=tabA, tabB=tabB)
 
@@ -113,3 +129,109 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
     if save:
         saved.update(acts=acts, args=args, cat=cat, bacts=bacts, pooled=pooled, tabA=tabA, tabB=tabB, nsplit=nsplit)
     return density, saved
+
+
+def new_grads(model):
+    """Gradient tensors in parameter order (biases and the head start at zero: they are
+    accumulated with atomics; weights are fully overwritten by the wgrad reduction)."""
+    out = []
+    for p in model.parameters():
+        out.append(torch.zeros_like(p) if p.dim() == 1 or p.shape[0] == 1 else torch.empty_like(p))
+    return out
+
+
+def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
+    """Gradients of every parameter given dL/d(density).  ``grads`` (optional) are the fp32
+    tensors to fill, in parameter order, with bias / head entries already zeroed.
+    ``on_ready(tag)`` is called after the gradients of 'backend', 'ctx' and 'frontend' have been
+    enqueued (used to start the bucketed all-reduce while the rest of backward still runs)."""
+    cache: WeightCache = model._wcache
+    nsplit = saved["nsplit"]
+    fr, bk = _conv_params(model)
+    acts, args, cat, bacts = saved["acts"], saved["args"], saved["cat"], saved["bacts"]
+    dev = cat.buf.device
+    N, h, w = cat.N, cat.H, cat.W
+    if grads is None:
+        grads = new_grads(model)
+    g = grad_out.contiguous().float()
+
+    # ---- head + backend -----------------------------------------------------------
+    hw = model.output_layer.weight.detach().float().reshape(64).contiguous()
+    dz = ops.head_bwd(g, bacts[6], hw, grads[IDX_HEAD], grads[IDX_HEAD + 1])
+    dcat = None
+    for li in range(5, -1, -1):
+        wt = bk[li][0]
+        cin = wt.shape[1]
+        X = bacts[li]
+        ops.conv_wgrad(dz, X, grads[IDX_BACKEND + 2 * li], dil=2)
+        ops.bias_grad(dz, grads[IDX_BACKEND + 2 * li + 1])
+        wd = cache.get(("bd", li, nsplit), (wt,), lambda wt=wt: ops.pack_conv_weight(wt, nsplit, dgrad=True))
+        ndz = ops.new_act(nsplit, N, h, w, cin, dev)
+        if li > 0:
+            ops.conv_tc(dz, wd, cin, dil=2, mode=MODE_STORE, relu=False, out=ndz, mask=X)
+            dz = ndz
+        else:
+            ops.conv_tc(dz, wd, cin, dil=2, mode=MODE_STORE, relu=False, out=ndz)
+            dcat = ndz
+    if on_ready:
+        on_ready("backend")
+
+    # ---- contextual module ----------------------------------------------------------
+    w1s, w2s = _ctx_weights(model)
+    fv = cat.view(512, 0)
+    w2stack = cache.get(("w2stack", nsplit), w2s, lambda: ops.pack_ctx_w2(w2s, nsplit))
+    w1t = cache.get(("w1t",), w1s, lambda: ops.transpose_stack(w1s))
+    w2t = cache.get(("w2t",), w2s, lambda: ops.transpose_stack(w2s))
+    D = ops.new_act(nsplit, N, h, w, 4096, dev)   # [dz_1..dz_6 | direct ds_1..ds_6], 512 channels each
+    ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX_BWD, out=D, mask=dcat.view(512, 512), tabA=saved["tabA"],
+                tabB=saved["tabB"])
+    wint = cache.get(("wint", nsplit, h, w), (), lambda: ops.ctx_wint(nsplit, 1, h, w, dev))
+    T = torch.empty(N, 64, 4096, device=dev, dtype=torch.float32)   # U^T [dz | ds] per image
+    for n in range(N):
+        ops.conv_wgrad(wint, D.image(n), T[n], taps=1)
+    # da_j = U^T ds_j + W_j2^T (U^T dz_j);  dpool_j = W_j1^T da_j
+    da = ops.ctx_pos_gemv(w2t, T, 64 * 4096, 4096, 512, T.view(-1)[2048:], N)
+    dpool = ops.ctx_pos_gemv(w1t, da, 50 * 512, 512, 0, None, N)
+    dW1 = torch.empty(4, 512, 512, device=dev, dtype=torch.float32)
+    dW2 = torch.empty(4, 512, 512, device=dev, dtype=torch.float32)
+    ops.ctx_outer(da, 50 * 512, 512, 0, saved["pooled"], N, dW1)          # dW_j1 = sum da_j pool_j^T
+    ops.ctx_outer(T, 64 * 4096, 4096, 512, saved["tabA"], N, dW2)         # dW_j2 = sum (U^T dz_j) a_j^T ...
+    for j in range(4):
+        ops.conv_wgrad(D.view(512, j * 512), fv, dW2[j], taps=1, accumulate=True, alpha=-1.0)  # ... - dz_j fv^T
+        grads[IDX_CTX + 2 * j].copy_(dW1[j].view(512, 512, 1, 1))
+        grads[IDX_CTX + 2 * j + 1].copy_(dW2[j].view(512, 512, 1, 1))
+    # dfv = dcat[:, :512] - sum_j W_j2^T dz_j + pool^T(dpool), gated by fv > 0  -> dZ of conv4_3
+    w2d = cache.get(("w2d", nsplit), w2s, lambda: ops.pack_conv_weight(
+        torch.cat([wj.detach().float().reshape(512, 512).t() for wj in w2s], dim=1).reshape(512, 2048, 1, 1), nsplit))
+    dz = ops.new_act(nsplit, N, h, w, 512, dev)
+    ops.conv_tc(D.view(2048, 0), w2d, 512, taps=1, mode=MODE_DFV, relu=False, out=dz, mask=fv, add=dcat.view(512, 0),
+                tabA=dpool)
+    if on_ready:
+        on_ready("ctx")
+
+    # ---- frontend -------------------------------------------------------------------
+    for li in range(9, 0, -1):
+        wt = fr[li][0]
+        cin = wt.shape[1]
+        X = acts[li - 1]
+        ops.conv_wgrad(dz, X, grads[2 * li], dil=1)
+        ops.bias_grad(dz, grads[2 * li + 1])
+        wd = cache.get(("fd", li, nsplit), (wt,), lambda wt=wt: ops.pack_conv_weight(wt, nsplit, dgrad=True))
+        if (li - 1) in POOLED_LAYERS:
+            pre = acts[li - 2]  # the pooled layer's input has its pre-pool resolution
+            OH, OW = pre.H, pre.W
+            ndz = ops.new_act(nsplit, N, OH, OW, cin, dev, zero=bool((OH | OW) & 1))
+            ops.conv_tc(dz, wd, cin, mode=MODE_UNPOOL, relu=False, out=ndz, mask=X, arg=args[li - 1], OH=OH, OW=OW)
+        else:
+            ndz = ops.new_act(nsplit, N, X.H, X.W, cin, dev)
+            ops.conv_tc(dz, wd, cin, mode=MODE_STORE, relu=False, out=ndz, mask=X)
+        dz = ndz
+    # first conv (3 -> 64): K = 27 padded to 64 through an im2col of the image
+    col = ops.im2col_first(saved["x"], nsplit)
+    g0 = torch.empty(64, 64, device=dev, dtype=torch.float32)
+    ops.conv_wgrad(dz, col, g0, taps=1)
+    grads[0].copy_(g0[:, :27].reshape(64, 3, 3, 3))
+    ops.bias_grad(dz, grads[1])
+    if on_ready:
+        on_ready("frontend")
+    return grads

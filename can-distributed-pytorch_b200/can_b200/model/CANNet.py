@@ -46,7 +46,9 @@ class _CANNetFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, model, x, *params):
-        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        # grad mode is always off inside Function.forward; needs_input_grad says whether autograd
+        # recorded this call (no_grad / eval-only callers get the activation-free path)
+        need_grad = any(ctx.needs_input_grad[2:])
         out, saved = engine.forward(model, x, model.nsplit, save=need_grad)
         ctx.model = model
         ctx.saved = saved
@@ -107,11 +109,13 @@ class CANNet(nn.Module):
 
     @property
     def nsplit(self) -> int:
-        if self.precision == "bf16":
-            return 1
-        if self.precision == "fp32":
-            return 2
-        raise ValueError(f"CANNet.precision must be 'bf16' or 'fp32', got {self.precision!r}")
+        # "fp32" = two bf16 planes per value (hi + lo, 16 mantissa bits), three tensor-core
+        # products, short accumulation chains spread over several TMEM accumulators;
+        # "bf16x3" = three planes / six products, kept for experiments.
+        try:
+            return {"bf16": 1, "fp32": 2, "bf16x3": 3}[self.precision]
+        except KeyError:
+            raise ValueError(f"CANNet.precision must be 'bf16', 'fp32' or 'bf16x3', got {self.precision!r}")
 
     def forward(self, x):
         if x.dim() != 4 or x.shape[1] != 3:

@@ -10,10 +10,35 @@ from dataclasses import dataclass
 
 import torch
 
-from . import _lib
 from ._lib import ConvArgs, check, lib
 
-MODE_STORE, MODE_POOL, MODE_HEAD, MODE_UNPOOL, MODE_CTX = range(5)
+MODE_STORE, MODE_POOL, MODE_HEAD, MODE_UNPOOL, MODE_CTX, MODE_CTX_BWD, MODE_DFV = range(7)
+
+#: number of kernels of this library launched so far (bench.py reports the count per timed region)
+LAUNCHES = 0
+#: when a list, every tensor-core launch appends (start_event, end_event, algorithmic_flops)
+PROFILE = None
+
+
+def _count(n=1):
+    global LAUNCHES
+    LAUNCHES += n
+
+
+class _Prof:
+    def __init__(self, flops):
+        self.flops = flops
+
+    def __enter__(self):
+        if PROFILE is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+
+    def __exit__(self, *a):
+        if PROFILE is not None:
+            self.e1.record()
+            PROFILE.append((self.e0, self.e1, self.flops))
 
 
 def _stream() -> int:
@@ -57,6 +82,10 @@ class Act:
     def view(self, C, coff):
         return Act(self.buf, C, coff)
 
+    def image(self, n):
+        """One image of the batch as its own Act (same planes, N = 1)."""
+        return Act(self.buf[:, n:n + 1], self.C, self.coff)
+
     def to_nchw(self) -> torch.Tensor:
         out = torch.empty(self.N, self.C, self.H, self.W, device=self.buf.device, dtype=torch.float32)
         check(lib().can_nhwc_to_nchw_f32(self.buf.data_ptr(), self.plane, self.nsplit, self.cs, self.coff,
@@ -79,6 +108,7 @@ def act_from_nchw(x: torch.Tensor, nsplit: int) -> Act:
     return a
 
 
+# ------------------------------------------------------------------------------ weights
 def pack_conv_weight(w: torch.Tensor, nsplit: int, dgrad: bool = False) -> torch.Tensor:
     """OIHW fp32 -> [plane][Cout][taps][Cin] bf16 (dgrad: [plane][Cin][taps flipped][Cout])."""
     co, ci, kh, kw = w.shape
@@ -88,6 +118,7 @@ def pack_conv_weight(w: torch.Tensor, nsplit: int, dgrad: bool = False) -> torch
     dst = torch.empty(nsplit, rows, k, device=w.device, dtype=torch.bfloat16)
     check(lib().can_pack_conv_weight(w.data_ptr(), dst.data_ptr(), co, ci, taps, nsplit, int(dgrad), _stream()),
           "pack_conv_weight")
+    _count()
     return dst
 
 
@@ -95,7 +126,13 @@ def pack_ctx_w2(ws, nsplit: int) -> torch.Tensor:
     ws = [w.detach().contiguous().float() for w in ws]
     dst = torch.empty(nsplit, 2048, 512, device=ws[0].device, dtype=torch.bfloat16)
     check(lib().can_pack_ctx_w2(*[w.data_ptr() for w in ws], dst.data_ptr(), nsplit, _stream()), "pack_ctx_w2")
+    _count()
     return dst
+
+
+def stack_1x1(ws) -> torch.Tensor:
+    """[4] x [512(co),512(ci),1,1] -> [4][co][ci] fp32 (weights as stored)."""
+    return torch.stack([w.detach().float().reshape(512, 512) for w in ws]).contiguous()
 
 
 def transpose_stack(ws) -> torch.Tensor:
@@ -104,20 +141,23 @@ def transpose_stack(ws) -> torch.Tensor:
     for j, w in enumerate(ws):
         w = w.detach().contiguous().float()
         check(lib().can_transpose_f32(w.data_ptr(), out[j].data_ptr(), 512, 512, _stream()), "transpose_f32")
+        _count()
     return out
 
 
+# ------------------------------------------------------------------------------ forward
 def conv_first(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, nsplit: int) -> Act:
     N, _, H, W = x.shape
     out = new_act(nsplit, N, H, W, 64, x.device)
     check(lib().can_conv_first_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), out.buf.data_ptr(), out.plane, nsplit,
                                    N, H, W, _stream()), "conv_first_fwd")
+    _count()
     return out
 
 
 def conv_tc(x: Act, wp: torch.Tensor, Cout: int, *, taps=9, dil=1, mode=MODE_STORE, relu=True, bias=None, out: Act = None,
             out_f32=None, mask: Act = None, arg=None, head_w=None, head_b=None, head_out=None, tabA=None, tabB=None,
-            OH=0, OW=0, bn=0, stages=0):
+            OH=0, OW=0, bn=0, stages=0, add: Act = None):
     a = ConvArgs()
     a.N, a.H, a.W = x.N, x.H, x.W
     a.Cin, a.Cout = x.C, Cout
@@ -129,25 +169,31 @@ def conv_tc(x: Act, wp: torch.Tensor, Cout: int, *, taps=9, dil=1, mode=MODE_STO
         a.out, a.out_plane, a.out_cs, a.out_coff = out.buf.data_ptr(), out.plane, out.cs, out.coff
     a.out_f32 = _ptr(out_f32)
     if mask is not None:
-        a.mask, a.mask_cs, a.mask_coff = mask.buf.data_ptr(), mask.cs, mask.coff
+        a.mask, a.mask_cs, a.mask_coff, a.mask_plane = mask.buf.data_ptr(), mask.cs, mask.coff, mask.plane
+    if add is not None:
+        a.add, a.add_plane, a.add_cs, a.add_coff = add.buf.data_ptr(), add.plane, add.cs, add.coff
     if arg is not None:
         a.arg, a.arg_cs = arg.data_ptr(), arg.shape[-1]
     a.OH, a.OW = OH, OW
     a.head_w, a.head_b, a.head_out = _ptr(head_w), _ptr(head_b), _ptr(head_out)
     a.tabA, a.tabB = _ptr(tabA), _ptr(tabB)
-    check(lib().can_conv_tc(C.byref(a), _stream()), "conv_tc")
+    _count()
+    with _Prof(2.0 * taps * x.C * Cout * x.N * x.H * x.W):
+        check(lib().can_conv_tc(C.byref(a), _stream()), "conv_tc")
 
 
-def ctx_pool(fv: Act, w1t: torch.Tensor, w2t: torch.Tensor):
+def ctx_pool(fv: Act, w1: torch.Tensor, w2: torch.Tensor):
+    """K1: pooled [N,50,512], tabA = conv{S}_1(pooled), tabB = conv{S}_2(tabA); w1/w2 = stack_1x1(...)"""
     N, H, W = fv.N, fv.H, fv.W
     dev = fv.buf.device
     pooled = torch.empty(N, 50, 512, device=dev, dtype=torch.float32)
     tabA = torch.empty_like(pooled)
     tabB = torch.empty_like(pooled)
     ws = torch.empty(lib().can_ctx_pool_workspace_bytes(N, H), device=dev, dtype=torch.uint8)
-    check(lib().can_ctx_pool_fwd(fv.buf.data_ptr(), fv.plane, fv.nsplit, fv.cs, fv.coff, N, H, W, w1t.data_ptr(),
-                                 w2t.data_ptr(), pooled.data_ptr(), tabA.data_ptr(), tabB.data_ptr(), ws.data_ptr(),
+    check(lib().can_ctx_pool_fwd(fv.buf.data_ptr(), fv.plane, fv.nsplit, fv.cs, fv.coff, N, H, W, w1.data_ptr(),
+                                 w2.data_ptr(), pooled.data_ptr(), tabA.data_ptr(), tabB.data_ptr(), ws.data_ptr(),
                                  _stream()), "ctx_pool_fwd")
+    _count(4)
     return pooled, tabA, tabB
 
 
@@ -171,14 +217,83 @@ def mse_count(et: torch.Tensor, gt: torch.Tensor, want_grad: bool, grad_scale: f
     check(lib().can_mse_count_fwd_bwd(et.data_ptr(), gt.data_ptr(), N, HW, loss.data_ptr(), ce.data_ptr(),
                                       cg.data_ptr(), _ptr(grad), grad_scale, _mse_ws[key].data_ptr(), _stream()),
           "mse_count")
+    _count()
     return loss, ce, cg, grad
 
 
 def sgd_momentum_step(p, g, buf, lr, momentum=0.95, grad_scale=1.0, first=False):
     check(lib().can_sgd_momentum_step(p.data_ptr(), g.data_ptr(), buf.data_ptr(), p.numel(), lr, momentum, grad_scale,
                                       int(first), _stream()), "sgd_momentum_step")
+    _count()
 
 
+# ------------------------------------------------------------------------------ backward
+_wgrad_ws = {}
+
+
+def conv_wgrad(dz: Act, x: Act, grad: torch.Tensor, *, taps=9, dil=1, accumulate=False, alpha=1.0):
+    """grad[co][ci][kh][kw] (+)= alpha * sum_pixels dz[pix][co] * x[pix + tap][ci]   (fp32, parameter layout)."""
+    N, H, W = dz.N, dz.H, dz.W
+    need = lib().can_conv_wgrad_workspace_bytes(N, H, W, x.C, dz.C, taps, dz.nsplit)
+    dev = dz.buf.device
+    ws = _wgrad_ws.get(dev)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(max(need, 64 << 20), device=dev, dtype=torch.uint8)
+        _wgrad_ws[dev] = ws
+    assert grad.is_contiguous() and grad.dtype == torch.float32 and grad.numel() == dz.C * x.C * taps
+    _count(2)
+    with _Prof(2.0 * taps * x.C * dz.C * N * H * W):
+        check(lib().can_conv_wgrad(dz.buf.data_ptr(), dz.plane, dz.cs, dz.coff, x.buf.data_ptr(), x.plane, x.cs, x.coff,
+                                   dz.nsplit, N, H, W, x.C, dz.C, taps, dil, grad.data_ptr(), int(accumulate),
+                                   float(alpha), ws.data_ptr(), ws.numel(), _stream()), "conv_wgrad")
+
+
+def im2col_first(x: torch.Tensor, nsplit: int) -> Act:
+    N, _, H, W = x.shape
+    out = new_act(nsplit, N, H, W, 64, x.device)
+    check(lib().can_im2col_first(x.data_ptr(), out.buf.data_ptr(), out.plane, nsplit, N, H, W, _stream()), "im2col_first")
+    _count()
+    return out
+
+
+def bias_grad(dz: Act, db: torch.Tensor):
+    """db[c] += sum_pixels dz[pix][c]; db fp32 [C], already initialised."""
+    check(lib().can_bias_grad(dz.buf.data_ptr(), dz.plane, dz.nsplit, dz.cs, dz.coff, dz.C, dz.N * dz.H * dz.W,
+                              db.data_ptr(), _stream()), "bias_grad")
+    _count()
+
+
+def head_bwd(dout: torch.Tensor, y5: Act, head_w: torch.Tensor, d_hw: torch.Tensor, d_hb: torch.Tensor) -> Act:
+    dz = new_act(y5.nsplit, y5.N, y5.H, y5.W, 64, y5.buf.device)
+    assert y5.cs == 64 and y5.coff == 0
+    check(lib().can_head_bwd(dout.data_ptr(), y5.buf.data_ptr(), y5.plane, y5.nsplit, head_w.data_ptr(), dz.buf.data_ptr(),
+                             dz.plane, y5.N * y5.H * y5.W, d_hw.data_ptr(), d_hb.data_ptr(), _stream()), "head_bwd")
+    _count()
+    return dz
+
+
+def ctx_wint(nsplit, N, H, W, device) -> Act:
+    out = new_act(nsplit, N, H, W, 64, device)
+    check(lib().can_ctx_wint(out.buf.data_ptr(), out.plane, nsplit, N, H, W, _stream()), "ctx_wint")
+    _count()
+    return out
+
+
+def ctx_pos_gemv(Wm, inp, in_ns, in_ps, in_js, add, N):
+    out = torch.empty(N, 50, 512, device=Wm.device, dtype=torch.float32)
+    check(lib().can_ctx_pos_gemv(Wm.data_ptr(), inp.data_ptr(), in_ns, in_ps, in_js, _ptr(add), out.data_ptr(), N,
+                                 _stream()), "ctx_pos_gemv")
+    _count()
+    return out
+
+
+def ctx_outer(A, a_ns, a_ps, a_js, B, N, dW, alpha=1.0, accumulate=False):
+    check(lib().can_ctx_outer(A.data_ptr(), a_ns, a_ps, a_js, B.data_ptr(), N, dW.data_ptr(), float(alpha),
+                              int(accumulate), _stream()), "ctx_outer")
+    _count()
+
+
+# ------------------------------------------------------------------------------ probes
 def bilinear_taps(in_size, out_size, device):
     i0 = torch.empty(out_size, device=device, dtype=torch.int32)
     i1 = torch.empty_like(i0)

@@ -1,0 +1,140 @@
+"""Mirror of ``utils/train_eval_utils.py`` for the hot path: the training-step body
+(:28-52) and the evaluation count (:83), on the fused kernels.
+
+``FusedTrainer.step`` is one optimizer step: forward -> fused MSE(sum)+count+dL/det ->
+backward into a flat fp32 gradient arena -> bucketed NCCL all-reduce overlapped with the rest
+of backward (replacing DistributedDataParallel, train.py:121-122) -> one fused SGD-momentum
+kernel over the flat parameter arena (torch.optim.SGD semantics, train.py:63,125-126).
+Nothing in the step reads a value back to the host: the loss stays on the device.
+
+``train_one_epoch`` / ``evaluate`` keep the reference signatures and return values.
+"""
+from __future__ import annotations
+
+import sys
+
+import torch
+import torch.distributed as dist
+
+from .. import engine, ops
+from .distributed_utils import get_world_size, is_dist_avail_and_initialized, is_main_process, reduce_value
+
+
+class FusedTrainer:
+    """Flat-arena SGD(momentum) trainer for a ``can_b200.model.CANNet``.
+
+    DDP semantics are preserved: the loss is a SUM over the local batch, gradients are AVERAGED
+    over ranks (train.py:121), the caller multiplies lr by world_size (train.py:25)."""
+
+    def __init__(self, model, lr, momentum=0.95, process_group=None):
+        self.model = model
+        self.lr = float(lr)
+        self.momentum = float(momentum)
+        self.pg = process_group
+        self.world = get_world_size()
+        params = list(model.parameters())
+        dev = params[0].device
+        total = sum(p.numel() for p in params)
+        self.arena = torch.empty(total, device=dev, dtype=torch.float32)
+        self.garena = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.buf = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.gviews = []
+        self.zero_ranges = []  # bias / head slices that the backward accumulates into
+        off = 0
+        with torch.no_grad():
+            for p in params:
+                n = p.numel()
+                view = self.arena[off:off + n].view_as(p)
+                view.copy_(p)
+                p.data = view           # parameters now live in the arena (state_dict unchanged)
+                self.gviews.append(self.garena[off:off + n].view_as(p))
+                if p.dim() == 1 or p.shape[0] == 1:
+                    self.zero_ranges.append((off, off + n))
+                off += n
+        self.total = total
+        # buckets in the order backward produces them: backend+head, ctx, frontend
+        n_front = sum(p.numel() for p in params[:engine.IDX_BACKEND])
+        n_back = sum(p.numel() for p in params[engine.IDX_BACKEND:engine.IDX_CTX])
+        self.buckets = {"backend": (n_front, n_front + n_back), "ctx": (n_front + n_back, total), "frontend": (0, n_front)}
+        self.first = True
+        self._works = []
+        model._wcache.invalidate()
+        if self.world > 1:  # identical initial weights on every rank (train.py:104-114 / DDP broadcast)
+            dist.broadcast(self.arena, src=0, group=self.pg)
+
+    def _on_ready(self, tag):
+        if self.world > 1:
+            a, b = self.buckets[tag]
+            self._works.append(dist.all_reduce(self.garena[a:b], group=self.pg, async_op=True))
+
+    def step(self, img: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
+        """One training step; returns the rank-mean of the local sum-losses as a device tensor [1]."""
+        m = self.model
+        for a, b in self.zero_ranges:
+            self.garena[a:b].zero_()
+        out, saved = engine.forward(m, img, m.nsplit, save=True)
+        loss, _, _, grad = ops.mse_count(out, gt, want_grad=True)
+        self._works = []
+        engine.backward(m, saved, grad, grads=self.gviews, on_ready=self._on_ready)
+        if self.world > 1:
+            self._works.append(dist.all_reduce(loss, group=self.pg, async_op=True))
+            for wk in self._works:
+                wk.wait()
+            loss = loss / self.world
+        ops.sgd_momentum_step(self.arena, self.garena, self.buf, self.lr, self.momentum, 1.0 / self.world,
+                              first=self.first)
+        self.first = False
+        m._wcache.invalidate()  # the arena changed in place: packed weights must be rebuilt
+        return loss
+
+
+def train_one_epoch(model, optimizer, train_loader, device, epoch):
+    """utils/train_eval_utils.py:13-58.  ``optimizer`` may be a FusedTrainer (fused path) or any
+    torch optimizer (stock path through the autograd.Function).  Returns the mean loss."""
+    model.train()
+    mean_loss = torch.zeros(1, device=device)
+    if is_main_process():
+        try:
+            from tqdm import tqdm
+            train_loader = tqdm(train_loader, file=sys.stdout)
+        except Exception:
+            pass
+    fused = isinstance(optimizer, FusedTrainer)
+    for step, (img, gt_dmap) in enumerate(train_loader):
+        img = img.to(device, non_blocking=True)
+        gt_dmap = gt_dmap.to(device, non_blocking=True)
+        if fused:
+            loss = optimizer.step(img, gt_dmap)
+        else:
+            optimizer.zero_grad()
+            et_dmap = model(img)
+            loss = torch.nn.functional.mse_loss(et_dmap, gt_dmap, reduction="sum")
+            loss.backward()
+            loss = reduce_value(loss.detach().reshape(1), average=True)
+            optimizer.step()
+        mean_loss = (mean_loss * step + loss.detach()) / (step + 1)
+    if not torch.isfinite(mean_loss).all():  # checked once per epoch instead of a host sync per step
+        print("WARNING: non-finite loss, ending training ", mean_loss)
+        sys.exit(1)
+    if device != torch.device("cpu"):
+        torch.cuda.synchronize(device)
+    return mean_loss.item()
+
+
+@torch.no_grad()
+def evaluate(model, test_loader, device, epoch=0, show_images=False, use_wandb=False):
+    """utils/train_eval_utils.py:61-138 without the plotting: returns sum |count(et) - count(gt)|
+    over this rank's samples, reduced (summed) over ranks.  Counts come from the fused kernel, per
+    image; like the reference (:83) the absolute difference is taken over the whole batch tensor."""
+    model.eval()
+    mae = torch.zeros(1, device=device)
+    for img, gt_dmap in test_loader:
+        img = img.to(device, non_blocking=True)
+        gt_dmap = gt_dmap.to(device, non_blocking=True)
+        et = model(img)
+        _, ce, cg, _ = ops.mse_count(et, gt_dmap, want_grad=False)
+        mae += (ce.sum() - cg.sum()).abs()
+    if device != torch.device("cpu"):
+        torch.cuda.synchronize(device)
+    mae = reduce_value(mae, average=False)
+    return mae.item()

@@ -71,8 +71,8 @@ constexpr int kMaxSmem = 232448;  // 227 KB opt-in limit per CTA on sm_100
 template <int BN, int NSPLIT, int MODE>
 int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p, dim3 grid, int stages_override,
                 cudaStream_t st) {
-  using L = ConvTcSmem<BN, NSPLIT>;
-  const bool ctx = (MODE == MODE_CTX);
+  using L = ConvTcSmem<BN, gemm_planes(NSPLIT, MODE)>;
+  const bool ctx = (MODE == MODE_CTX || MODE == MODE_CTX_BWD);
   int stages = (kMaxSmem - L::bytes(0, ctx)) / L::kStageBytes;
   if (stages > 8) stages = 8;
   if (stages_override > 0 && stages_override < stages) stages = stages_override;
@@ -100,6 +100,7 @@ int dispatch_mode(int mode, const CUtensorMap& a, const CUtensorMap& b, ConvTcPa
     case MODE_STORE: return launch_conv<BN, NSPLIT, MODE_STORE>(a, b, p, grid, so, st);
     case MODE_POOL: return launch_conv<BN, NSPLIT, MODE_POOL>(a, b, p, grid, so, st);
     case MODE_UNPOOL: return launch_conv<BN, NSPLIT, MODE_UNPOOL>(a, b, p, grid, so, st);
+    case MODE_DFV: return launch_conv<BN, NSPLIT, MODE_DFV>(a, b, p, grid, so, st);
     default: return fail(-21, "conv_tc: mode %d not available for BN=%d", mode, BN);
   }
 }
@@ -157,6 +158,20 @@ int make_act_tmap(CUtensorMap* m, const void* base, int coff, int C, int cs, int
   return make_tmap(m, static_cast<const __nv_bfloat16*>(base) + coff, 5, dims, str, box);
 }
 
+
+int launch_ctx_gemv(const float* Wm, const float* in, long long in_ns, long long in_ps, long long in_js,
+                    const float* add, float* out, int N, cudaStream_t st) {
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(ctx_pos_gemv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 36 * 512 * 4);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(ctx_pos_gemv)");
+    attr = true;
+  }
+  ctx_pos_gemv_kernel<<<dim3(8, 4, N), 256, 36 * 512 * 4, st>>>(Wm, in, in_ns, in_ps, in_js, add, out);
+  CAN_CHECK_LAUNCH("ctx_pos_gemv");
+  return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -167,12 +182,12 @@ int can_version(void) { return 100; }
 int can_conv_tc(const can_conv_args* a, void* stream) {
   if (!a) return fail(-1, "conv_tc: null args");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const bool ctx = a->mode == CAN_MODE_CTX;
+  const bool ctx = a->mode == CAN_MODE_CTX || a->mode == CAN_MODE_CTX_BWD;
   if (a->N <= 0 || a->H <= 0 || a->W <= 0) return fail(-2, "conv_tc: bad shape N=%d H=%d W=%d", a->N, a->H, a->W);
   if (a->Cin <= 0 || a->Cin % 64) return fail(-3, "conv_tc: Cin=%d must be a positive multiple of 64", a->Cin);
   if (a->taps != 1 && a->taps != 9) return fail(-4, "conv_tc: taps=%d (want 1 or 9)", a->taps);
   if (a->dil < 1 || a->dil > 4) return fail(-5, "conv_tc: dil=%d", a->dil);
-  if (a->nsplit < 1 || a->nsplit > 2) return fail(-6, "conv_tc: nsplit=%d (want 1 or 2)", a->nsplit);
+  if (a->nsplit < 1 || a->nsplit > 3) return fail(-6, "conv_tc: nsplit=%d (want 1, 2 or 3)", a->nsplit);
   if (!a->x || !a->w) return fail(-7, "conv_tc: null x/w");
   if (a->x_cs % 8 || a->x_coff % 8 || a->out_cs % 8 || a->out_coff % 8)
     return fail(-8, "conv_tc: channel strides/offsets must be multiples of 8 (16-byte alignment)");
@@ -183,22 +198,26 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   if (ctx) {
     if (a->Cout != 2048 || a->Cin != 512 || a->taps != 1) return fail(-10, "conv_tc: CTX wants Cin=512 Cout=2048 taps=1");
     if (!a->tabA || !a->tabB || !a->out) return fail(-10, "conv_tc: CTX needs tabA/tabB/out");
+    if (a->mode == CAN_MODE_CTX_BWD && (!a->mask || a->out_cs != 4096))
+      return fail(-10, "conv_tc: CTX_BWD needs the fi-gradient in `mask` and a 4096-channel output");
     bn = 256;
   } else if (a->mode == CAN_MODE_HEAD) {
     if (a->Cout != 64 || !a->head_w || !a->head_b || !a->head_out) return fail(-11, "conv_tc: HEAD wants Cout=64, head_w, head_out");
     bn = 64;
   } else {
-    if (a->Cout != 64 && a->Cout != 128 && a->Cout != 256 && a->Cout != 512)
+    if (a->Cout != 64 && a->Cout != 128 && a->Cout != 256 && a->Cout != 512 && a->Cout != 1024)
       return fail(-12, "conv_tc: Cout=%d unsupported", a->Cout);
     if (!a->out) return fail(-12, "conv_tc: null out");
     if (bn == 0) bn = env_int("CAN_B200_BN", 0);
     if (bn == 0) bn = a->Cout < 256 ? a->Cout : (a->nsplit > 1 ? 128 : 256);
+    if (a->nsplit == 3 && bn > 128) bn = 128;  // 3 planes x (A + B) must leave >= 2 pipeline stages
     if (bn > a->Cout) bn = a->Cout;
     if (bn != 64 && bn != 128 && bn != 256) return fail(-13, "conv_tc: bn=%d", bn);
   }
   if (a->mode == CAN_MODE_UNPOOL && (!a->mask || !a->arg || a->OH < 2 * a->H || a->OW < 2 * a->W))
     return fail(-14, "conv_tc: UNPOOL needs mask, arg and OH>=2H, OW>=2W");
-  if (a->mode < 0 || a->mode > CAN_MODE_CTX) return fail(-15, "conv_tc: mode=%d", a->mode);
+  if (a->mode == CAN_MODE_DFV && (!a->mask || !a->add || !a->tabA)) return fail(-14, "conv_tc: DFV needs mask, add and tabA");
+  if (a->mode < 0 || a->mode > CAN_MODE_DFV) return fail(-15, "conv_tc: mode=%d", a->mode);
 
   ConvTcParams p;
   memset(&p, 0, sizeof(p));
@@ -217,7 +236,9 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   p.out_cs = a->out_cs; p.out_coff = a->out_coff;
   p.out_f32 = a->out_f32;
   p.mask = static_cast<const __nv_bfloat16*>(a->mask);
-  p.mask_cs = a->mask_cs; p.mask_coff = a->mask_coff;
+  p.mask_cs = a->mask_cs; p.mask_coff = a->mask_coff; p.mask_plane = a->mask_plane;
+  p.add = static_cast<const __nv_bfloat16*>(a->add);
+  p.add_plane = a->add_plane; p.add_cs = a->add_cs; p.add_coff = a->add_coff;
   p.arg = a->arg; p.arg_cs = a->arg_cs;
   p.OH = a->OH; p.OW = a->OW;
   p.head_w = a->head_w; p.head_b = a->head_b; p.head_out = a->head_out;
@@ -248,17 +269,28 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   const int so = a->stages > 0 ? a->stages : env_int("CAN_B200_STAGES", 0);
   const int ns = a->nsplit;
   if (ctx) {
-    return ns == 1 ? launch_conv<256, 1, MODE_CTX>(tmA, tmB, p, grid, so, st)
-                   : launch_conv<256, 2, MODE_CTX>(tmA, tmB, p, grid, so, st);
+    if (a->mode == CAN_MODE_CTX)
+      return ns == 1   ? launch_conv<256, 1, MODE_CTX>(tmA, tmB, p, grid, so, st)
+             : ns == 2 ? launch_conv<256, 2, MODE_CTX>(tmA, tmB, p, grid, so, st)
+                       : launch_conv<256, 3, MODE_CTX>(tmA, tmB, p, grid, so, st);
+    return ns == 1   ? launch_conv<256, 1, MODE_CTX_BWD>(tmA, tmB, p, grid, so, st)
+           : ns == 2 ? launch_conv<256, 2, MODE_CTX_BWD>(tmA, tmB, p, grid, so, st)
+                     : launch_conv<256, 3, MODE_CTX_BWD>(tmA, tmB, p, grid, so, st);
   }
   if (a->mode == CAN_MODE_HEAD) {
-    return ns == 1 ? launch_conv<64, 1, MODE_HEAD>(tmA, tmB, p, grid, so, st)
-                   : launch_conv<64, 2, MODE_HEAD>(tmA, tmB, p, grid, so, st);
+    return ns == 1   ? launch_conv<64, 1, MODE_HEAD>(tmA, tmB, p, grid, so, st)
+           : ns == 2 ? launch_conv<64, 2, MODE_HEAD>(tmA, tmB, p, grid, so, st)
+                     : launch_conv<64, 3, MODE_HEAD>(tmA, tmB, p, grid, so, st);
   }
-  if (bn == 64) return ns == 1 ? dispatch_mode<64, 1>(a->mode, tmA, tmB, p, grid, so, st)
-                               : dispatch_mode<64, 2>(a->mode, tmA, tmB, p, grid, so, st);
-  if (bn == 128) return ns == 1 ? dispatch_mode<128, 1>(a->mode, tmA, tmB, p, grid, so, st)
-                                : dispatch_mode<128, 2>(a->mode, tmA, tmB, p, grid, so, st);
+  if (bn == 64)
+    return ns == 1   ? dispatch_mode<64, 1>(a->mode, tmA, tmB, p, grid, so, st)
+           : ns == 2 ? dispatch_mode<64, 2>(a->mode, tmA, tmB, p, grid, so, st)
+                     : dispatch_mode<64, 3>(a->mode, tmA, tmB, p, grid, so, st);
+  if (bn == 128)
+    return ns == 1   ? dispatch_mode<128, 1>(a->mode, tmA, tmB, p, grid, so, st)
+           : ns == 2 ? dispatch_mode<128, 2>(a->mode, tmA, tmB, p, grid, so, st)
+                     : dispatch_mode<128, 3>(a->mode, tmA, tmB, p, grid, so, st);
+  if (ns == 3) return fail(-13, "conv_tc: bn=256 does not fit with 3 planes");
   return ns == 1 ? dispatch_mode<256, 1>(a->mode, tmA, tmB, p, grid, so, st)
                  : dispatch_mode<256, 2>(a->mode, tmA, tmB, p, grid, so, st);
 }
@@ -321,17 +353,9 @@ int can_ctx_pool_fwd(const void* fv, int64_t fv_plane, int nsplit, int cs, int c
   CAN_CHECK_LAUNCH("ctx_pool_rows");
   ctx_pool_finalize_kernel<<<dim3(50, N), 512, 0, st>>>(R, pooled, H, W);
   CAN_CHECK_LAUNCH("ctx_pool_finalize");
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(ctx_pos_gemv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 36 * 512 * 4);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(ctx_pos_gemv)");
-    attr = true;
-  }
-  ctx_pos_gemv_kernel<<<dim3(8, 4, N), 256, 36 * 512 * 4, st>>>(w1t, pooled, tabA);
-  CAN_CHECK_LAUNCH("ctx_pos_gemv(A)");
-  ctx_pos_gemv_kernel<<<dim3(8, 4, N), 256, 36 * 512 * 4, st>>>(w2t, tabA, tabB);
-  CAN_CHECK_LAUNCH("ctx_pos_gemv(B)");
-  return 0;
+  int rc = launch_ctx_gemv(w1t, pooled, 50 * 512, 512, 0, nullptr, tabA, N, st);
+  if (rc) return rc;
+  return launch_ctx_gemv(w2t, tabA, 50 * 512, 512, 0, nullptr, tabB, N, st);
 }
 
 int64_t can_mse_count_workspace_bytes(int N) { return static_cast<int64_t>(N) * 4 + 16; }
@@ -404,14 +428,14 @@ int64_t can_conv_wgrad_workspace_bytes(int N, int H, int W, int Cin, int Cout, i
 
 int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, const void* x, int64_t x_plane, int x_cs,
                    int x_coff, int nsplit, int N, int H, int W, int Cin, int Cout, int taps, int dil, float* grad,
-                   int accumulate, void* ws, int64_t ws_bytes, void* stream) {
+                   int accumulate, float alpha, void* ws, int64_t ws_bytes, void* stream) {
   if (!dz || !x || !grad || !ws) return fail(-1, "conv_wgrad: null pointer");
   if (N <= 0 || H <= 0 || W <= 0) return fail(-2, "conv_wgrad: bad shape");
   if (Cin <= 0 || Cin % 64 || Cout <= 0 || Cout % 64) return fail(-3, "conv_wgrad: Cin/Cout must be multiples of 64");
   if (Cout > 128 && Cout % 128) return fail(-3, "conv_wgrad: Cout must be 64 or a multiple of 128");
   if (Cin > 256 && Cin % 256) return fail(-3, "conv_wgrad: Cin must be 64, 128 or a multiple of 256");
   if (taps != 1 && taps != 9) return fail(-4, "conv_wgrad: taps=%d", taps);
-  if (nsplit < 1 || nsplit > 2) return fail(-5, "conv_wgrad: nsplit=%d", nsplit);
+  if (nsplit < 1 || nsplit > 3) return fail(-5, "conv_wgrad: nsplit=%d", nsplit);
   if (dz_cs % 8 || dz_coff % 8 || x_cs % 8 || x_coff % 8) return fail(-6, "conv_wgrad: strides/offsets must be multiples of 8");
   const WgradPlan pl = wgrad_plan(N, H, W, Cin, Cout, taps, nsplit);
   const int64_t need = static_cast<int64_t>(pl.ksplit) * taps * Cout * Cin * sizeof(float);
@@ -431,13 +455,20 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
   p.m_groups = Cout >= 128 ? 2 : 1;
   p.ws = static_cast<float*>(ws);
   dim3 grid(pl.m_tiles * pl.n_tiles * taps, pl.ksplit);
-  if (pl.bn == 64) rc = nsplit == 1 ? launch_wgrad<64, 1>(tmDZ, tmX, p, grid, st) : launch_wgrad<64, 2>(tmDZ, tmX, p, grid, st);
-  else if (pl.bn == 128) rc = nsplit == 1 ? launch_wgrad<128, 1>(tmDZ, tmX, p, grid, st) : launch_wgrad<128, 2>(tmDZ, tmX, p, grid, st);
-  else rc = nsplit == 1 ? launch_wgrad<256, 1>(tmDZ, tmX, p, grid, st) : launch_wgrad<256, 2>(tmDZ, tmX, p, grid, st);
+  if (pl.bn == 64)
+    rc = nsplit == 1   ? launch_wgrad<64, 1>(tmDZ, tmX, p, grid, st)
+         : nsplit == 2 ? launch_wgrad<64, 2>(tmDZ, tmX, p, grid, st)
+                       : launch_wgrad<64, 3>(tmDZ, tmX, p, grid, st);
+  else if (pl.bn == 128)
+    rc = nsplit == 1   ? launch_wgrad<128, 1>(tmDZ, tmX, p, grid, st)
+         : nsplit == 2 ? launch_wgrad<128, 2>(tmDZ, tmX, p, grid, st)
+                       : launch_wgrad<128, 3>(tmDZ, tmX, p, grid, st);
+  else
+    rc = launch_wgrad<256, 1>(tmDZ, tmX, p, grid, st);
   if (rc) return rc;
   const long long total = static_cast<long long>(Cout) * Cin * taps;
   const int blocks = static_cast<int>((total + 255) / 256 > 2368 ? 2368 : (total + 255) / 256);
-  wgrad_reduce_kernel<<<blocks, 256, 0, st>>>(p.ws, grad, pl.ksplit, taps, Cout, Cin, accumulate);
+  wgrad_reduce_kernel<<<blocks, 256, 0, st>>>(p.ws, grad, pl.ksplit, taps, Cout, Cin, accumulate, alpha);
   CAN_CHECK_LAUNCH("wgrad_reduce");
   return 0;
 }
@@ -470,6 +501,30 @@ int can_head_bwd(const float* dout, const void* y5, int64_t y_plane, int nsplit,
       dout, static_cast<const __nv_bfloat16*>(y5), y_plane, nsplit, head_w, static_cast<__nv_bfloat16*>(dz), dz_plane,
       npix, d_head_w, d_head_b);
   CAN_CHECK_LAUNCH("head_bwd");
+  return 0;
+}
+
+int can_ctx_wint(void* out, int64_t out_plane, int nsplit, int N, int H, int W, void* stream) {
+  if (!out || nsplit < 1 || nsplit > 3 || N <= 0 || H <= 0 || W <= 0) return fail(-1, "ctx_wint: bad arguments");
+  ctx_wint_kernel<<<148 * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<__nv_bfloat16*>(out), out_plane,
+                                                                         nsplit, N, H, W);
+  CAN_CHECK_LAUNCH("ctx_wint");
+  return 0;
+}
+
+int can_ctx_pos_gemv(const float* Wm, const float* in, int64_t in_ns, int64_t in_ps, int64_t in_js, const float* add,
+                     float* out, int N, void* stream) {
+  if (!Wm || !in || !out || N <= 0 || N > 65535) return fail(-1, "ctx_pos_gemv: bad arguments");
+  if (in_ps % 4 || in_ns % 4 || in_js % 4) return fail(-2, "ctx_pos_gemv: strides must be multiples of 4 floats");
+  return launch_ctx_gemv(Wm, in, in_ns, in_ps, in_js, add, out, N, static_cast<cudaStream_t>(stream));
+}
+
+int can_ctx_outer(const float* A, int64_t a_ns, int64_t a_ps, int64_t a_js, const float* B, int N, float* dW,
+                  float alpha, int accumulate, void* stream) {
+  if (!A || !B || !dW || N <= 0) return fail(-1, "ctx_outer: bad arguments");
+  ctx_outer_kernel<<<dim3(32, 4), 256, 0, static_cast<cudaStream_t>(stream)>>>(A, a_ns, a_ps, a_js, B, N, dW, alpha,
+                                                                              accumulate);
+  CAN_CHECK_LAUNCH("ctx_outer");
   return 0;
 }
 

@@ -23,7 +23,9 @@ enum ConvMode : int {
   MODE_POOL = 1,    // y = maxpool2x2(relu(acc + bias))        -> pooled NHWC (+ argmax codes)
   MODE_HEAD = 2,    // y = relu(acc + bias) stored, and density = y . head_w + head_b (BN == Cout == 64)
   MODE_UNPOOL = 3,  // g = acc * (mask > 0); scatter to the arg-max position of a 2x upsampled map
-  MODE_CTX = 4,     // contextual fusion epilogue (see can_ctx.cuh comments in can_api.cu)
+  MODE_CTX = 4,     // contextual fusion epilogue: fi from the stacked contrast GEMM
+  MODE_CTX_BWD = 5, // same GEMM recomputed; writes dz_j and the direct ds_j (backward of the fusion)
+  MODE_DFV = 6,     // dfv = (add - acc + pooled-gradient spread) * (mask > 0)
 };
 
 struct ConvTcParams {
@@ -44,6 +46,11 @@ struct ConvTcParams {
   // mask source (dgrad): activation whose sign gates the gradient, NHWC bf16 (plane 0)
   const __nv_bfloat16* mask;
   int mask_cs, mask_coff;
+  long long mask_plane;
+  // additive source (MODE_DFV: upstream gradient that reaches fv through the concat)
+  const __nv_bfloat16* add;
+  long long add_plane;
+  int add_cs, add_coff;
   // pool / unpool
   uint8_t* arg;         // [N][H/2][W/2][C] argmax codes (MODE_POOL writes if non-null, MODE_UNPOOL reads)
   int arg_cs;
@@ -56,6 +63,12 @@ struct ConvTcParams {
   const float* tabA;    // [N][50][512] a_j  = W_j1 pool_j
   const float* tabB;    // [N][50][512] b_j  = W_j2 a_j
 };
+
+// Planes that enter the GEMM.  The contextual GEMMs feed a sigmoid, where two planes (16
+// mantissa bits) are already far below the fp32 tolerance; everything else uses all planes.
+__host__ __device__ constexpr int gemm_planes(int nsplit, int mode) {
+  return ((mode == MODE_CTX || mode == MODE_CTX_BWD) && nsplit > 2) ? 2 : nsplit;
+}
 
 template <int BN, int NSPLIT>
 struct ConvTcSmem {
@@ -104,11 +117,51 @@ __device__ __forceinline__ void store_bf16_planes(__nv_bfloat16* base, long long
   }
 }
 
+
+// fp32 accumulation inside the tensor core truncates: every tcgen05.mma that adds into a TMEM
+// accumulator loses ~2^-25 of the accumulator's magnitude, biased, so a chain of n MMAs drifts
+// by ~n * 3e-8 (measured: 1.5e-5 after 864 MMAs).  The fp32-parity path therefore spreads the
+// dominant hi*hi products of successive k-blocks over NACC accumulators (short chains), keeps
+// the small cross products (hi*lo, lo*hi, ...) in one more, and adds them up here in fp32 with
+// round-to-nearest.  GS == 1 (bf16 path): one accumulator, one load.
+template <int BN, int GS>
+struct AccLayout {
+  static constexpr int kNacc = (GS >= 2) ? (512 / BN - 1) : 1;   // hi*hi accumulators
+  static constexpr int kCols = (GS >= 2) ? 512 : (BN < 32 ? 32 : BN);
+};
+
+template <int NV>
+__device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, uint32_t* r) {
+  if (NV == 32) tmem_ld_32x32(taddr, r);
+  else if (NV == 16) tmem_ld_32x16(taddr, r);
+  else tmem_ld_32x8(taddr, r);
+}
+
+template <int BN, int GS, int NV>
+__device__ __forceinline__ void load_acc(uint32_t taddr, int col, int nact, float* v) {
+  uint32_t r[NV];
+  tmem_ld_cols<NV>(taddr + col, r);
+  tmem_ld_wait();
+#pragma unroll
+  for (int i = 0; i < NV; ++i) v[i] = __uint_as_float(r[i]);
+  if (GS >= 2) {
+    for (int a = 1; a <= nact; ++a) {
+      // a < nact: further hi*hi accumulators; a == nact: the cross-product accumulator
+      const int idx = (a < nact) ? a : AccLayout<BN, GS>::kNacc;
+      tmem_ld_cols<NV>(taddr + idx * BN + col, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < NV; ++i) v[i] += __uint_as_float(r[i]);
+    }
+  }
+}
+
 template <int BN, int NSPLIT, int MODE>
 __global__ void __launch_bounds__(192, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const ConvTcParams p) {
-  using L = ConvTcSmem<BN, NSPLIT>;
+  constexpr int GS = gemm_planes(NSPLIT, MODE);  // planes that enter the GEMM
+  using L = ConvTcSmem<BN, GS>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int stages = p.stages;
@@ -147,7 +200,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       fence_mbar_init();
     }
     __syncwarp();
-    tmem_alloc(tmem_ptr_smem, BN < 32 ? 32 : BN);
+    tmem_alloc(tmem_ptr_smem, AccLayout<BN, GS>::kCols);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -170,10 +223,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           dx = (tap % 3 - 1) * p.dil;
         }
         uint8_t* sa = smem + stage * L::kStageBytes;
-        uint8_t* sb = sa + NSPLIT * L::kABytes;
+        uint8_t* sb = sa + GS * L::kABytes;
         mbar_expect_tx(&full_bar[stage], L::kStageBytes);
 #pragma unroll
-        for (int pl = 0; pl < NSPLIT; ++pl) {
+        for (int pl = 0; pl < GS; ++pl) {
           tma_load_5d(sa + pl * L::kABytes, &tmA, &full_bar[stage], chunk * 64, x0 + dx, y0 + dy, n_img, pl);
           tma_load_3d(sb + pl * L::kBBytes, &tmB, &full_bar[stage], kb * 64, n0, pl);
         }
@@ -189,23 +242,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
-      uint32_t accum = 0;
+      constexpr int NACC = AccLayout<BN, GS>::kNacc;
+      uint32_t used = 0;  // bit a: accumulator a already holds a partial sum
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
-        const uint32_t sb = sa + NSPLIT * L::kABytes;
+        const uint32_t sb = sa + GS * L::kABytes;
 #pragma unroll
-        for (int pa = 0; pa < NSPLIT; ++pa) {
+        for (int pa = 0; pa < GS; ++pa) {
 #pragma unroll
-          for (int pb = 0; pb < NSPLIT; ++pb) {
-            if (pa + pb < NSPLIT) {
+          for (int pb = 0; pb < GS; ++pb) {
+            if (pa + pb < GS) {
+              const int acc = (GS == 1) ? 0 : ((pa + pb == 0) ? (kb % NACC) : NACC);
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
                 const uint64_t da = umma_smem_desc(sa + pa * L::kABytes + k * 32, 16, 1024);
                 const uint64_t db = umma_smem_desc(sb + pb * L::kBBytes + k * 32, 16, 1024);
-                umma_bf16(tmem_base, da, db, idesc, accum);
-                accum = 1;
+                umma_bf16(tmem_base + acc * BN, da, db, idesc, (used >> acc) & 1u);
+                used |= 1u << acc;
               }
             }
           }
@@ -223,7 +278,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     const int etid = threadIdx.x - 64;
     for (int i = etid; i < BN; i += 128) s_bias[i] = p.bias ? p.bias[n0 + i] : 0.f;
-    if (MODE == MODE_CTX) {
+    if (MODE == MODE_CTX || MODE == MODE_CTX_BWD) {
       // tables of this image for the 64 channels of this n-tile: [2][50][64]
       const float* ga = p.tabA + (static_cast<long long>(n_img) * 50) * 512 + blockIdx.y * 64;
       const float* gb = p.tabB + (static_cast<long long>(n_img) * 50) * 512 + blockIdx.y * 64;
@@ -244,6 +299,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
+    const int nact = min(AccLayout<BN, GS>::kNacc, num_kb);  // hi*hi accumulators actually written
 
     if (MODE == MODE_STORE) {
       const long long pix = (static_cast<long long>(n_img) * p.H + y) * p.W + x;
@@ -252,13 +308,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       float* fbase = p.out_f32 ? p.out_f32 + pix * p.out_cs + p.out_coff + n0 : nullptr;
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32(taddr + c0, r);
-        tmem_ld_wait();
+        float r[32];
+        load_acc<BN, GS, 32>(taddr, c0, nact, r);
         float v[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          v[i] = __uint_as_float(r[i]) + s_bias[c0 + i];
+          v[i] = r[i] + s_bias[c0 + i];
           if (p.relu) v[i] = fmaxf(v[i], 0.f);
         }
         if (valid) {
@@ -291,9 +346,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint8_t* abase = p.arg ? p.arg + ppix * p.arg_cs + n0 : nullptr;
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32(taddr + c0, r);
-        tmem_ld_wait();
+        float r[32];
+        load_acc<BN, GS, 32>(taddr, c0, nact, r);
         float v[32];
         uint32_t codes[8];
 #pragma unroll
@@ -302,7 +356,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int i = 0; i < 32; ++i) {
           // floor-mode pooling only writes windows that lie fully inside the image, so the
           // garbage computed for out-of-image tile pixels never reaches a written window.
-          float a = fmaxf(__uint_as_float(r[i]) + s_bias[c0 + i], 0.f);
+          float a = fmaxf(r[i] + s_bias[c0 + i], 0.f);
           if (NSPLIT == 1) a = bf16_round(a);  // ties are decided on the stored precision
           float mx = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, 1));
           mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, p.TW));
@@ -326,13 +380,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       float dot = 0.f;
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32(taddr + c0, r);
-        tmem_ld_wait();
+        float r[32];
+        load_acc<BN, GS, 32>(taddr, c0, nact, r);
         float v[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          v[i] = fmaxf(__uint_as_float(r[i]) + s_bias[c0 + i], 0.f);
+          v[i] = fmaxf(r[i] + s_bias[c0 + i], 0.f);
           dot = fmaf(v[i], __ldg(p.head_w + c0 + i), dot);
         }
         if (valid && obase) store_bf16_planes<NSPLIT, 32>(obase + c0, p.out_plane, v);
@@ -345,9 +398,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint8_t* abase = p.arg + pix * p.arg_cs + n0;
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32(taddr + c0, r);
-        tmem_ld_wait();
+        float r[32];
+        load_acc<BN, GS, 32>(taddr, c0, nact, r);
         if (valid) {
           float g[32];
           uint32_t code[8];
@@ -363,7 +415,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mq);
 #pragma unroll
             for (int e = 0; e < 8; ++e)
-              g[i + e] = (__bfloat162float(mb[e]) > 0.f) ? __uint_as_float(r[i + e]) : 0.f;
+              g[i + e] = (__bfloat162float(mb[e]) > 0.f) ? r[i + e] : 0.f;
           }
 #pragma unroll
           for (int wpos = 0; wpos < 4; ++wpos) {
@@ -403,10 +455,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const float* sB = s_tab + 3200;
 #pragma unroll 1
       for (int c0 = 0; c0 < 64; c0 += 16) {
-        uint32_t r[4][16];
+        float r[4][16];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) tmem_ld_32x16(taddr + j * 64 + c0, r[j]);
-        tmem_ld_wait();
+        for (int j = 0; j < 4; ++j) load_acc<BN, GS, 16>(taddr, j * 64 + c0, nact, r[j]);
         float fi[16];
 #pragma unroll
         for (int c = 0; c < 16; c += 4) {
@@ -432,7 +483,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                               ly1[j] * (lx0[j] * av10[e] + lx1[j] * av11[e]);
               const float u = ly0[j] * (lx0[j] * bv00[e] + lx1[j] * bv01[e]) +
                               ly1[j] * (lx0[j] * bv10[e] + lx1[j] * bv11[e]);
-              const float z = u - __uint_as_float(r[j][c + e]);
+              const float z = u - r[j][c + e];
               const float wgt = 1.f / (1.f + __expf(-z));
               num[e] = fmaf(wgt, s, num[e]);
               den[e] += wgt;
@@ -443,6 +494,179 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         if (valid) store_bf16_planes<NSPLIT, 16>(obase + c0, p.out_plane, fi);
       }
+    } else if (MODE == MODE_CTX_BWD) {
+      // Backward of the fusion (CANNet.py:84) and of sigmoid(conv{S}_2(s_j - fv)) w.r.t. z_j.
+      // With D = sum_j w_j + 1e-12 and g = dL/dfi:
+      //   dL/ds_j (direct) = g w_j / D ;  dL/dw_j = g (s_j - fi) / D ;  dz_j = dL/dw_j w_j (1 - w_j)
+      // out (cs = 4096): channel j*512 + c <- dz_j ; 2048 + j*512 + c <- direct ds_j.
+      const int SS[4] = {1, 2, 3, 6};
+      const int OFF[4] = {0, 1, 5, 14};
+      int pidx[4][4];
+      float ly0[4], ly1[4], lx0[4], lx1[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        int yi0, yi1, xi0, xi1;
+        bilinear_tap(min(y, p.H - 1), SS[j], p.H, yi0, yi1, ly0[j], ly1[j]);
+        bilinear_tap(min(x, p.W - 1), SS[j], p.W, xi0, xi1, lx0[j], lx1[j]);
+        pidx[j][0] = (OFF[j] + yi0 * SS[j] + xi0) * 64;
+        pidx[j][1] = (OFF[j] + yi0 * SS[j] + xi1) * 64;
+        pidx[j][2] = (OFF[j] + yi1 * SS[j] + xi0) * 64;
+        pidx[j][3] = (OFF[j] + yi1 * SS[j] + xi1) * 64;
+      }
+      const long long pix = valid ? (static_cast<long long>(n_img) * p.H + y) * p.W + x : 0;
+      __nv_bfloat16* obase = p.out + pix * p.out_cs + blockIdx.y * 64;
+      const __nv_bfloat16* gbase = p.mask + pix * p.mask_cs + p.mask_coff + blockIdx.y * 64;
+      const float* sA = s_tab;
+      const float* sB = s_tab + 3200;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 64; c0 += 8) {
+        float r[4][8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) load_acc<BN, GS, 8>(taddr, j * 64 + c0, nact, r[j]);
+        float g[8];
+        {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) g[e] = 0.f;
+#pragma unroll
+          for (int pl = 0; pl < NSPLIT; ++pl) {
+            const uint4 gq = *reinterpret_cast<const uint4*>(gbase + pl * p.mask_plane + c0);
+            const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(&gq);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) g[e] += __bfloat162float(gb[e]);
+          }
+        }
+        float dz[4][8], ds[4][8];
+#pragma unroll
+        for (int c = 0; c < 8; c += 4) {
+          float sj[4][4], wj[4][4];
+          float num[4] = {0.f, 0.f, 0.f, 0.f}, den[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 a00 = *reinterpret_cast<const float4*>(sA + pidx[j][0] + c0 + c);
+            const float4 a01 = *reinterpret_cast<const float4*>(sA + pidx[j][1] + c0 + c);
+            const float4 a10 = *reinterpret_cast<const float4*>(sA + pidx[j][2] + c0 + c);
+            const float4 a11 = *reinterpret_cast<const float4*>(sA + pidx[j][3] + c0 + c);
+            const float4 b00 = *reinterpret_cast<const float4*>(sB + pidx[j][0] + c0 + c);
+            const float4 b01 = *reinterpret_cast<const float4*>(sB + pidx[j][1] + c0 + c);
+            const float4 b10 = *reinterpret_cast<const float4*>(sB + pidx[j][2] + c0 + c);
+            const float4 b11 = *reinterpret_cast<const float4*>(sB + pidx[j][3] + c0 + c);
+            const float av00[4] = {a00.x, a00.y, a00.z, a00.w}, av01[4] = {a01.x, a01.y, a01.z, a01.w};
+            const float av10[4] = {a10.x, a10.y, a10.z, a10.w}, av11[4] = {a11.x, a11.y, a11.z, a11.w};
+            const float bv00[4] = {b00.x, b00.y, b00.z, b00.w}, bv01[4] = {b01.x, b01.y, b01.z, b01.w};
+            const float bv10[4] = {b10.x, b10.y, b10.z, b10.w}, bv11[4] = {b11.x, b11.y, b11.z, b11.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float sv = ly0[j] * (lx0[j] * av00[e] + lx1[j] * av01[e]) +
+                               ly1[j] * (lx0[j] * av10[e] + lx1[j] * av11[e]);
+              const float u = ly0[j] * (lx0[j] * bv00[e] + lx1[j] * bv01[e]) +
+                              ly1[j] * (lx0[j] * bv10[e] + lx1[j] * bv11[e]);
+              const float z = u - r[j][c + e];
+              const float wgt = 1.f / (1.f + __expf(-z));
+              sj[j][e] = sv;
+              wj[j][e] = wgt;
+              num[e] = fmaf(wgt, sv, num[e]);
+              den[e] += wgt;
+            }
+          }
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float dinv = 1.f / (den[e] + 1e-12f);
+            const float fiv = num[e] * dinv;
+            const float gd = g[c + e] * dinv;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              ds[j][c + e] = gd * wj[j][e];
+              dz[j][c + e] = gd * (sj[j][e] - fiv) * wj[j][e] * (1.f - wj[j][e]);
+            }
+          }
+        }
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            store_bf16_planes<NSPLIT, 8>(obase + j * 512 + c0, p.out_plane, dz[j]);
+            store_bf16_planes<NSPLIT, 8>(obase + 2048 + j * 512 + c0, p.out_plane, ds[j]);
+          }
+        }
+      }
+    } else if (MODE == MODE_DFV) {
+      // dfv[p][c] = ( add[p][c] - acc[p][c] + sum_j sum_{windows of scale j containing p}
+      //               dpool_j[window][c] / area(window) ) * (fv[p][c] > 0)
+      // acc = sum_j W_j2^T dz_j (this GEMM); add = gradient reaching fv through the concat;
+      // the last term is the transpose of the adaptive average pooling (overlapping windows).
+      const int SS[4] = {1, 2, 3, 6};
+      const int OFF[4] = {0, 1, 5, 14};
+      int spos[13];
+      float swgt[13];
+      {
+        const int yy = min(y, p.H - 1), xx = min(x, p.W - 1);
+        int k = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int S = SS[j];
+          int iy0 = 0, ix0 = 0;
+          while (adaptive_end(iy0, p.H, S) <= yy) ++iy0;
+          while (adaptive_end(ix0, p.W, S) <= xx) ++ix0;
+          const bool y2 = (iy0 + 1 < S) && (adaptive_start(iy0 + 1, p.H, S) <= yy);
+          const bool x2 = (ix0 + 1 < S) && (adaptive_start(ix0 + 1, p.W, S) <= xx);
+          const int ny = (j == 0) ? 1 : 2, nx = (j == 0) ? 1 : 2;
+#pragma unroll
+          for (int a = 0; a < ny; ++a)
+#pragma unroll
+            for (int b = 0; b < nx; ++b) {
+              const int iy = min(iy0 + a, S - 1), ix = min(ix0 + b, S - 1);
+              const bool on = (a == 0 || y2) && (b == 0 || x2);
+              const int hh = adaptive_end(iy, p.H, S) - adaptive_start(iy, p.H, S);
+              const int ww = adaptive_end(ix, p.W, S) - adaptive_start(ix, p.W, S);
+              spos[k] = (OFF[j] + iy * S + ix) * 512;
+              swgt[k] = on ? 1.f / static_cast<float>(hh * ww) : 0.f;
+              ++k;
+            }
+        }
+      }
+      const long long pix = valid ? (static_cast<long long>(n_img) * p.H + y) * p.W + x : 0;
+      __nv_bfloat16* obase = p.out + pix * p.out_cs + p.out_coff + n0;
+      const __nv_bfloat16* mbase = p.mask + pix * p.mask_cs + p.mask_coff + n0;
+      const __nv_bfloat16* abase = p.add + pix * p.add_cs + p.add_coff + n0;
+      const float* tab = p.tabA + static_cast<long long>(n_img) * 50 * 512 + n0;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        float r[32];
+        load_acc<BN, GS, 32>(taddr, c0, nact, r);
+        if (valid) {
+          float v[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = -r[i];
+#pragma unroll
+          for (int k = 0; k < 13; ++k) {
+            const float wk = swgt[k];
+            const float* tp = tab + spos[k] + c0;
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              const float4 t4 = __ldg(reinterpret_cast<const float4*>(tp + i));
+              v[i] = fmaf(wk, t4.x, v[i]);
+              v[i + 1] = fmaf(wk, t4.y, v[i + 1]);
+              v[i + 2] = fmaf(wk, t4.z, v[i + 2]);
+              v[i + 3] = fmaf(wk, t4.w, v[i + 3]);
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 32; i += 8) {
+#pragma unroll
+            for (int pl = 0; pl < NSPLIT; ++pl) {
+              const uint4 aq = *reinterpret_cast<const uint4*>(abase + pl * p.add_plane + c0 + i);
+              const __nv_bfloat16* ab = reinterpret_cast<const __nv_bfloat16*>(&aq);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[i + e] += __bfloat162float(ab[e]);
+            }
+            const uint4 mq = *reinterpret_cast<const uint4*>(mbase + c0 + i);
+            const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mq);
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+              if (!(__bfloat162float(mb[e]) > 0.f)) v[i + e] = 0.f;
+          }
+          store_bf16_planes<NSPLIT, 32>(obase + c0, p.out_plane, v);
+        }
+      }
     }
     tc_fence_before();
   }
@@ -450,7 +674,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, BN < 32 ? 32 : BN);
+    tmem_dealloc(tmem_base, AccLayout<BN, GS>::kCols);
   }
 }
 

@@ -262,40 +262,6 @@ ctx_pool_finalize_kernel(const float* __restrict__ R, float* __restrict__ pooled
   pooled[(static_cast<long long>(n) * 50 + p) * 512 + c] = acc / static_cast<float>((ye - ys) * (xe - xs));
 }
 
-// tiny per-position 1x1 conv: out[n][p][co] = sum_ci WT[j(p)][ci][co] * in[n][p][ci]
-// grid (8 co-slabs of 64, 4 scales, N); 256 threads = 64 co x 4 position groups.
-__global__ void __launch_bounds__(256)
-ctx_pos_gemv_kernel(const float* __restrict__ WT, const float* __restrict__ in, float* __restrict__ out) {
-  extern __shared__ float s_in[];  // [S*S][512]
-  const int SS[4] = {1, 2, 3, 6};
-  const int OFF[4] = {0, 1, 5, 14};
-  const int j = blockIdx.y, n = blockIdx.z;
-  const int S2 = SS[j] * SS[j];
-  const float* gin = in + (static_cast<long long>(n) * 50 + OFF[j]) * 512;
-  for (int i = threadIdx.x; i < S2 * 512; i += blockDim.x) s_in[i] = gin[i];
-  __syncthreads();
-  const int co = blockIdx.x * 64 + (threadIdx.x & 63);
-  const int pg = threadIdx.x >> 6;  // positions pg, pg+4, ...
-  float acc[9];
-#pragma unroll
-  for (int q = 0; q < 9; ++q) acc[q] = 0.f;
-  const float* wt = WT + static_cast<long long>(j) * 512 * 512 + co;
-  for (int ci = 0; ci < 512; ++ci) {
-    const float wv = __ldg(wt + static_cast<long long>(ci) * 512);
-#pragma unroll
-    for (int q = 0; q < 9; ++q) {
-      const int p = pg + q * 4;
-      if (p < S2) acc[q] = fmaf(wv, s_in[p * 512 + ci], acc[q]);
-    }
-  }
-  float* gout = out + (static_cast<long long>(n) * 50 + OFF[j]) * 512 + co;
-#pragma unroll
-  for (int q = 0; q < 9; ++q) {
-    const int p = pg + q * 4;
-    if (p < S2) gout[p * 512] = acc[q];
-  }
-}
-
 // --------------------------------------------------------------------------------
 // fused MSE(sum) + per-image counts + dL/det   (train_eval_utils.py:20,37,83)
 // one CTA per image; ws = [N*3 partials | 1 counter]; the last CTA to finish adds the
@@ -515,6 +481,130 @@ head_bwd_kernel(const float* __restrict__ dout, const __nv_bfloat16* __restrict_
   __syncthreads();
   if (threadIdx.x < 64) atomicAdd(d_hw + threadIdx.x, s_acc[threadIdx.x]);
   if (threadIdx.x == 64) atomicAdd(d_hb, s_acc[64]);
+}
+
+// --------------------------------------------------------------------------------
+// contextual-module tables: tiny per-position 1x1 convs and their gradients
+// --------------------------------------------------------------------------------
+// out[n][OFF_j + p][r] = (add ? add(n, OFF_j + p, r) : 0) + sum_k Wm[j][r][k] * in(n, OFF_j + p, k)
+//   Wm : [4][512 rows][512] row-major (conv weights as stored -> forward; their transposes -> backward)
+//   in(n, pos, k) = in[n*in_ns + pos*in_ps + j*in_js + k]   (same addressing for `add`)
+// grid (8 row slabs of 64, 4 scales, N); 256 threads = 64 rows x 4 quarter-rows of 128 k.
+template <int S2>
+__device__ __forceinline__ void ctx_gemv_body(const float* __restrict__ wrow, const float* s_in, float* __restrict__ o,
+                                              const float* __restrict__ addp, long long in_ps, int q) {
+  float acc[S2];
+#pragma unroll
+  for (int p = 0; p < S2; ++p) acc[p] = 0.f;
+#pragma unroll 4
+  for (int i = 0; i < 32; ++i) {
+    const float4 w4 = __ldg(reinterpret_cast<const float4*>(wrow + q * 128 + i * 4));
+#pragma unroll
+    for (int p = 0; p < S2; ++p) {
+      const float4 x4 = *reinterpret_cast<const float4*>(s_in + p * 512 + q * 128 + i * 4);
+      acc[p] = fmaf(w4.x, x4.x, acc[p]);
+      acc[p] = fmaf(w4.y, x4.y, acc[p]);
+      acc[p] = fmaf(w4.z, x4.z, acc[p]);
+      acc[p] = fmaf(w4.w, x4.w, acc[p]);
+    }
+  }
+#pragma unroll
+  for (int p = 0; p < S2; ++p) {
+    float v = acc[p];
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    if (q == 0) o[p * 512] = v + (addp ? addp[p * in_ps] : 0.f);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+ctx_pos_gemv_kernel(const float* __restrict__ Wm, const float* __restrict__ in, long long in_ns, long long in_ps,
+                    long long in_js, const float* __restrict__ add, float* __restrict__ out) {
+  extern __shared__ float s_in[];  // [S*S][512]
+  const int SS[4] = {1, 2, 3, 6};
+  const int OFF[4] = {0, 1, 5, 14};
+  const int j = blockIdx.y, n = blockIdx.z;
+  const int S2 = SS[j] * SS[j];
+  const float* gin = in + n * in_ns + OFF[j] * in_ps + j * in_js;
+  for (int i = threadIdx.x; i < S2 * 128; i += blockDim.x) {
+    const int p = i >> 7, k4 = (i & 127) * 4;
+    *reinterpret_cast<float4*>(s_in + p * 512 + k4) = *reinterpret_cast<const float4*>(gin + p * in_ps + k4);
+  }
+  __syncthreads();
+  const int row = blockIdx.x * 64 + (threadIdx.x >> 2);
+  const int q = threadIdx.x & 3;
+  const float* wrow = Wm + (static_cast<long long>(j) * 512 + row) * 512;
+  float* o = out + (static_cast<long long>(n) * 50 + OFF[j]) * 512 + row;
+  const float* addp = add ? add + n * in_ns + OFF[j] * in_ps + j * in_js + row : nullptr;
+  if (j == 0) ctx_gemv_body<1>(wrow, s_in, o, addp, in_ps, q);
+  else if (j == 1) ctx_gemv_body<4>(wrow, s_in, o, addp, in_ps, q);
+  else if (j == 2) ctx_gemv_body<9>(wrow, s_in, o, addp, in_ps, q);
+  else ctx_gemv_body<36>(wrow, s_in, o, addp, in_ps, q);
+}
+
+// dW[j][r][c] (+)= alpha * sum_{n, p in scale j} A(n, OFF_j + p, r) * B[n][OFF_j + p][c]
+//   A(n, pos, r) = A[n*a_ns + pos*a_ps + j*a_js + r];  B: [N][50][512]
+// grid (32 row blocks of 16, 4 scales); 256 threads, 2 columns each.
+__global__ void __launch_bounds__(256)
+ctx_outer_kernel(const float* __restrict__ A, long long a_ns, long long a_ps, long long a_js,
+                 const float* __restrict__ B, int N, float* __restrict__ dW, float alpha, int accumulate) {
+  const int SS[4] = {1, 2, 3, 6};
+  const int OFF[4] = {0, 1, 5, 14};
+  const int j = blockIdx.y;
+  const int S2 = SS[j] * SS[j];
+  const int r0 = blockIdx.x * 16;
+  const int c = threadIdx.x;
+  float acc0[16], acc1[16];
+#pragma unroll
+  for (int r = 0; r < 16; ++r) acc0[r] = acc1[r] = 0.f;
+  for (int n = 0; n < N; ++n) {
+    for (int p = 0; p < S2; ++p) {
+      const float* ap = A + n * a_ns + (OFF[j] + p) * a_ps + j * a_js + r0;
+      const float* bp = B + (static_cast<long long>(n) * 50 + OFF[j] + p) * 512;
+      const float b0 = bp[c], b1 = bp[c + 256];
+#pragma unroll
+      for (int r = 0; r < 16; ++r) {
+        const float a = __ldg(ap + r);
+        acc0[r] = fmaf(a, b0, acc0[r]);
+        acc1[r] = fmaf(a, b1, acc1[r]);
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < 16; ++r) {
+    float* d = dW + (static_cast<long long>(j) * 512 + r0 + r) * 512;
+    d[c] = (accumulate ? d[c] : 0.f) + alpha * acc0[r];
+    d[c + 256] = (accumulate ? d[c + 256] : 0.f) + alpha * acc1[r];
+  }
+}
+
+// Bilinear interpolation matrix of the four scales as an NHWC "activation":
+//   out[pl][n][y][x][pos] = weight of pooled position pos (0..49, scale-major) in pixel (y, x);
+//   positions 50..63 are zero.  U^T applied to a full-resolution tensor is then a GEMM with
+//   K = pixels on the tensor cores (can_conv_wgrad with this tensor as the "dz" operand).
+__global__ void __launch_bounds__(256)
+ctx_wint_kernel(__nv_bfloat16* __restrict__ out, long long out_plane, int nsplit, int N, int H, int W) {
+  const long long total = static_cast<long long>(N) * H * W * 64;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int pos = i & 63;
+    const long long pix = i >> 6;
+    const int x = pix % W;
+    const int y = (pix / W) % H;
+    float wv = 0.f;
+    if (pos < 50) {
+      int j, S, wy, wx, xwin;
+      ctx_pos_decode(pos, j, S, wy, wx, xwin);
+      int yi0, yi1, xi0, xi1;
+      float ly0, ly1, lx0, lx1;
+      bilinear_tap(y, S, H, yi0, yi1, ly0, ly1);
+      bilinear_tap(x, S, W, xi0, xi1, lx0, lx1);
+      const float wyv = (wy == yi0 ? ly0 : 0.f) + ((wy == yi1 && yi1 != yi0) ? ly1 : 0.f);
+      const float wxv = (wx == xi0 ? lx0 : 0.f) + ((wx == xi1 && xi1 != xi0) ? lx1 : 0.f);
+      wv = wyv * wxv;
+    }
+    split_store(out + i, out_plane, nsplit, wv);
+  }
 }
 
 // --------------------------------------------------------------------------------

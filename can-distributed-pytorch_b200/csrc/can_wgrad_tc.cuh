@@ -186,9 +186,9 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
   }
 }
 
-// grad[co][ci][tap] (OIHW) (+)= sum_s ws[s][tap][co][ci]
+// grad[co][ci][tap] (OIHW) (+)= alpha * sum_s ws[s][tap][co][ci]
 __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ grad, int splits, int taps,
-                                    int cout, int cin, int accumulate) {
+                                    int cout, int cin, int accumulate, float alpha) {
   const long long total = static_cast<long long>(cout) * cin * taps;
   const long long slab = total;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
@@ -200,7 +200,7 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
     float acc = 0.f;
     for (int s = 0; s < splits; ++s) acc += ws[s * slab + i];
     float* g = grad + (static_cast<long long>(co) * cin + ci) * taps + tap;
-    *g = accumulate ? (*g + acc) : acc;
+    *g = (accumulate ? *g : 0.f) + alpha * acc;
   }
 }
 

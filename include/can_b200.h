@@ -35,7 +35,9 @@ enum {
   CAN_MODE_POOL = 1,   /* y = maxpool2x2(relu(acc + bias)), optional argmax codes            */
   CAN_MODE_HEAD = 2,   /* y = relu(acc + bias) and density = y . head_w + head_b (Cout == 64) */
   CAN_MODE_UNPOOL = 3, /* g = acc * (mask > 0) scattered to the argmax slot of the 2x map    */
-  CAN_MODE_CTX = 4     /* contextual fusion epilogue                                         */
+  CAN_MODE_CTX = 4,    /* contextual fusion epilogue                                         */
+  CAN_MODE_CTX_BWD = 5,/* backward of the fusion: writes dz_j and the direct ds_j (4096 channels)  */
+  CAN_MODE_DFV = 6     /* dfv = (add - acc + adaptive-pool^T spread) * (mask > 0)              */
 };
 
 typedef struct can_conv_args {
@@ -43,7 +45,7 @@ typedef struct can_conv_args {
   int32_t Cin, Cout;     /* Cin % 64 == 0; Cout in {64,128,256,512} (2048 for CAN_MODE_CTX)   */
   int32_t taps;          /* 9 = 3x3, 1 = 1x1                                                  */
   int32_t dil;           /* dilation == padding: 1 (frontend) or 2 (backend)                  */
-  int32_t nsplit;        /* 1 = bf16, 2 = split-bf16 fp32-parity path                         */
+  int32_t nsplit;        /* 1 = bf16; 2 or 3 = split-bf16 planes (3 = the fp32-parity path)    */
   int32_t mode;          /* CAN_MODE_*                                                        */
   int32_t relu;          /* CAN_MODE_STORE only                                               */
   int32_t bn;            /* N-tile override (0 = auto): 64 | 128 | 256                        */
@@ -59,6 +61,10 @@ typedef struct can_conv_args {
   float* out_f32;        /* optional fp32 NHWC copy of the output (STORE)                     */
   const void* mask;      /* STORE/UNPOOL: activation whose sign gates the result (plane 0)    */
   int32_t mask_cs, mask_coff;
+  int64_t mask_plane;    /* CTX_BWD: `mask` carries dL/dfi as NHWC planes                     */
+  const void* add;       /* DFV: gradient that reaches fv through the concat, NHWC planes     */
+  int64_t add_plane;
+  int32_t add_cs, add_coff;
   uint8_t* arg;          /* POOL: argmax codes out (may be NULL); UNPOOL: codes in            */
   int32_t arg_cs;
   int32_t OH, OW;        /* UNPOOL: size of the upsampled map                                 */
@@ -100,12 +106,12 @@ int can_conv_first_fwd(const float* x_nchw, const float* w, const float* b, void
  * per-position 1x1 convs.  Replaces 4x F.adaptive_avg_pool2d + conv{S}_1 (+ conv{S}_2 on the
  * <=36 pooled positions, valid because a bias-free 1x1 conv commutes with bilinear upsampling):
  * model/CANNet.py:42-43,51-52,60-61,70-72.
- *   w1t / w2t : [4][512(ci)][512(co)] fp32 transposed conv{S}_1 / conv{S}_2 weights
+ *   w1 / w2 : [4][512(co)][512(ci)] fp32 stacks of the conv{S}_1 / conv{S}_2 weights as stored
  *   pooled, tabA, tabB : [N][50][512] fp32; positions ordered S=1 | S=2 (4) | S=3 (9) | S=6 (36)
  *   ws : can_ctx_pool_workspace_bytes(N, H) bytes                                            */
 int64_t can_ctx_pool_workspace_bytes(int N, int H);
 int can_ctx_pool_fwd(const void* fv, int64_t fv_plane, int nsplit, int cs, int coff, int N, int H, int W,
-                     const float* w1t, const float* w2t, float* pooled, float* tabA, float* tabB, void* ws,
+                     const float* w1, const float* w2, float* pooled, float* tabA, float* tabB, void* ws,
                      void* stream);
 
 /* Fused MSELoss(reduction='sum') + per-image counts + dL/d(et)
@@ -122,14 +128,14 @@ int can_sgd_momentum_step(float* p, const float* g, float* buf, int64_t n, float
 
 /* Weight gradient of a 3x3 / dilated 3x3 / 1x1 convolution on tcgen05 (both operands MN-major,
  * split-K over pixel patches, deterministic reduction):
- *   grad[co][ci][tap] (+)= sum_{n,y,x} dz[n,y,x,co] * x[n, y+dy, x+dx, ci]
+ *   grad[co][ci][tap] (+)= alpha * sum_{n,y,x} dz[n,y,x,co] * x[n, y+dy, x+dx, ci]
  * Replaces cuDNN backward-filter under loss.backward() (utils/train_eval_utils.py:38) for the
  * layers built at model/CANNet.py:14-16,19,21,23,25.  grad is fp32 in the parameter's own
  * [Cout][Cin][kh][kw] layout; ws: can_conv_wgrad_workspace_bytes(...) bytes of scratch.        */
 int64_t can_conv_wgrad_workspace_bytes(int N, int H, int W, int Cin, int Cout, int taps, int nsplit);
 int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, const void* x, int64_t x_plane,
                    int x_cs, int x_coff, int nsplit, int N, int H, int W, int Cin, int Cout, int taps, int dil,
-                   float* grad, int accumulate, void* ws, int64_t ws_bytes, void* stream);
+                   float* grad, int accumulate, float alpha, void* ws, int64_t ws_bytes, void* stream);
 
 /* im2col of the 3-channel image: out[pl][n][y][x][64], k = ci*9 + r*3 + s (27 used, rest zero),
  * which turns frontend.0 (model/CANNet.py:14) into a K=64 1x1 GEMM for its weight gradient.    */
@@ -144,6 +150,21 @@ int can_bias_grad(const void* dz, int64_t plane, int nsplit, int cs, int coff, i
  * dz[pix][c] = dout[pix] * head_w[c] * (y5 > 0); d_head_w += sum dout*y5; d_head_b += sum dout. */
 int can_head_bwd(const float* dout, const void* y5, int64_t y_plane, int nsplit, const float* head_w, void* dz,
                  int64_t dz_plane, int64_t npix, float* d_head_w, float* d_head_b, void* stream);
+
+/* Backward of the contextual module's small pieces (autograd of model/CANNet.py:42-84).
+ * can_ctx_wint: the bilinear-interpolation matrix of the four scales as an NHWC tensor
+ *   out[pl][n][y][x][pos], pos < 50 (scale-major), zero for 50..63; U^T of a full-resolution tensor
+ *   is then a tensor-core GEMM over pixels (can_conv_wgrad with this tensor as `dz`).
+ * can_ctx_pos_gemv: out[n][pos][r] = add(n,pos,r) + sum_k Wm[scale(pos)][r][k] * in(n,pos,k), with
+ *   in(n,pos,k) = in[n*in_ns + pos*in_ps + scale*in_js + k]; Wm = [4][512][512] (weights as stored
+ *   for the forward 1x1 convs on pooled positions, their transposes for the backward).
+ * can_ctx_outer: dW[scale][r][c] (+)= alpha * sum_{n,pos in scale} A(n,pos,r) * B[n][pos][c]
+ *   (weight gradients of conv{S}_1 and the pooled-position part of conv{S}_2).                  */
+int can_ctx_wint(void* out, int64_t out_plane, int nsplit, int N, int H, int W, void* stream);
+int can_ctx_pos_gemv(const float* Wm, const float* in, int64_t in_ns, int64_t in_ps, int64_t in_js,
+                     const float* add, float* out, int N, void* stream);
+int can_ctx_outer(const float* A, int64_t a_ns, int64_t a_ps, int64_t a_js, const float* B, int N, float* dW,
+                  float alpha, int accumulate, void* stream);
 
 /* Index-table probes: the exact device arithmetic of the pooling windows and bilinear taps
  * (ATen AdaptivePooling.h:32-38, UpSample.h:271-295,442-476 as used by model/CANNet.py:42-76). */
