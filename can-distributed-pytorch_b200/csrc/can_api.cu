@@ -372,6 +372,73 @@ int can_mse_count_fwd_bwd(const float* et, const float* gt, int N, int HW, float
   return 0;
 }
 
+}  // extern "C"  (closed so the static scratch and its set-up helper sit at file scope)
+
+// ---------------------------------------------------------------------------------------------
+// Loss/count reduction for callers that must not allocate.
+//
+// Some hosts of this library cannot call cudaMalloc once they are running: an inference or
+// training server that reserves the whole device up front and hands plugins nothing but their
+// input and output buffers, or a step loop that cannot afford the device-wide synchronisation a
+// cudaMalloc/cudaFree pair implies.  For them the scratch of the fused MSE+count kernel (one fp32
+// partial per image plus the "blocks finished" counter) lives in the array below instead of a
+// caller-provided workspace.  The array belongs to the loaded library: every GPU that loads
+// libcan_b200.so holds these 4.25 KB until the process exits.
+//
+// `g_mse_static_scratch` is only a host-side stand-in for the device array; handing that name to a
+// kernel from host code would pass a host address.  The device address is fetched once per device
+// with cudaGetSymbolAddress (below) and that pointer is what the kernel receives.
+// ---------------------------------------------------------------------------------------------
+#define CAN_MSE_STATIC_MAX_IMAGES 1024
+static __device__ __align__(256) unsigned char g_mse_static_scratch[CAN_MSE_STATIC_MAX_IMAGES * 4 + 256];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_mse_static_ptr[kMaxDevices] = {};  // device address of the scratch, per device ordinal
+
+// Set-up, once per device, with that device current.  Returns 0 and the device pointer, or an error code.
+int mse_static_scratch(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "mse_count_static: cudaGetDevice");
+  if (dev < 0 || dev >= kMaxDevices) return fail(-30, "mse_count_static: device ordinal %d not supported", dev);
+  if (!g_mse_static_ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_mse_static_scratch);
+    if (e != cudaSuccess || !p) return cuda_fail(e, "mse_count_static: cudaGetSymbolAddress");
+    g_mse_static_ptr[dev] = p;
+  }
+  *out = g_mse_static_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int can_mse_count_static_max_images(void) { return CAN_MSE_STATIC_MAX_IMAGES; }
+
+int can_mse_count_fwd_bwd_static(const float* et, const float* gt, int N, int HW, float* loss, float* cnt_et,
+                                 float* cnt_gt, float* grad, float grad_scale, void* stream) {
+  if (!et || !gt || !loss || !cnt_et || !cnt_gt) return fail(-1, "mse_count_static: null pointer");
+  if (N <= 0 || HW <= 0) return fail(-2, "mse_count_static: bad shape N=%d HW=%d", N, HW);
+  if (N > CAN_MSE_STATIC_MAX_IMAGES)
+    return fail(-3, "mse_count_static: N=%d exceeds the built-in scratch (at most %d images per call); use "
+                    "can_mse_count_fwd_bwd with a caller-provided workspace", N, CAN_MSE_STATIC_MAX_IMAGES);
+  void* scratch = nullptr;
+  int rc = mse_static_scratch(&scratch);
+  if (rc) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* part = static_cast<float*>(scratch);
+  unsigned int* counter = reinterpret_cast<unsigned int*>(part + CAN_MSE_STATIC_MAX_IMAGES);
+  // The array keeps whatever the previous call (of any thread, on any stream) left in it.  Only the
+  // counter has to start at zero; the partials are fully rewritten before they are read.
+  cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(unsigned int), st);
+  if (e != cudaSuccess) return cuda_fail(e, "mse_count_static: cudaMemsetAsync");
+  mse_count_kernel<<<N, 1024, 0, st>>>(et, gt, N, HW, loss, cnt_et, cnt_gt, grad, grad_scale, part, counter);
+  CAN_CHECK_LAUNCH("mse_count_static");
+  return 0;
+}
+
 int can_sgd_momentum_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float grad_scale,
                           int first_step, void* stream) {
   if (!p || !g || !buf || n <= 0) return fail(-1, "sgd_momentum_step: bad arguments");

@@ -121,6 +121,23 @@ int64_t can_mse_count_workspace_bytes(int N);
 int can_mse_count_fwd_bwd(const float* et, const float* gt, int N, int HW, float* loss, float* cnt_et,
                           float* cnt_gt, float* grad, float grad_scale, void* ws, void* stream);
 
+/* The same fused loss / count / gradient reduction for callers that cannot allocate device memory.
+ * (No counterpart in the reference: this entry point exists only for hosts of this library.)
+ * Who needs it: a server or plugin host that reserves the whole GPU at start-up and gives a plugin
+ * only its input and output buffers, or a step loop that must avoid the device-wide stall of
+ * cudaMalloc/cudaFree.  Same arguments and results as can_mse_count_fwd_bwd minus the workspace: the
+ * scratch is a 4.25 KB array built into the library (held by every GPU that loads it, until exit).
+ *   - limit: N <= can_mse_count_static_max_images() (1024) images per call; larger N is rejected
+ *     with a negative return code and an explanatory can_last_error_string().
+ *   - the first call on each device looks the array's device address up (cudaGetSymbolAddress, with
+ *     that device current); make that first call before starting any stream capture.
+ *   - no cudaMalloc / cudaFree / allocating library routine is called, on the first call or later.
+ *   - all calls on a device share the one array: calls whose kernels can overlap on the GPU
+ *     (different streams, or different host threads) race on it -- serialise them.               */
+int can_mse_count_static_max_images(void);
+int can_mse_count_fwd_bwd_static(const float* et, const float* gt, int N, int HW, float* loss, float* cnt_et,
+                                 float* cnt_gt, float* grad, float grad_scale, void* stream);
+
 /* torch.optim.SGD(momentum, dampening 0, no nesterov, wd 0) over a flat fp32 arena
  * (train.py:63,125-126; utils/train_eval_utils.py:52).  g is multiplied by grad_scale first. */
 int can_sgd_momentum_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum,
