@@ -11,7 +11,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libcan_b200.so")
 
-MODE_STORE, MODE_POOL, MODE_HEAD, MODE_UNPOOL, MODE_CTX, MODE_CTX_BWD, MODE_DFV = range(7)
+MODE_STORE, MODE_POOL, MODE_HEAD, MODE_UNPOOL, MODE_CTX, MODE_CTX_BWD, MODE_DFV, MODE_CTX2 = range(8)
 
 
 class ConvArgs(C.Structure):
@@ -31,6 +31,7 @@ class ConvArgs(C.Structure):
         ("OH", C.c_int32), ("OW", C.c_int32),
         ("head_w", C.c_void_p), ("head_b", C.c_void_p), ("head_out", C.c_void_p),
         ("tabA", C.c_void_p), ("tabB", C.c_void_p),
+        ("ctx_wint", C.c_void_p), ("ctx_ttab", C.c_void_p),
     ]
 
 
@@ -39,6 +40,8 @@ _SIGNATURES = {
     "can_version": (C.c_int, []),
     "can_conv_tc": (C.c_int, [C.POINTER(ConvArgs), C.c_void_p]),
     "can_pack_conv_weight": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "can_pack_conv_weight_both": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                            C.c_void_p]),
     "can_pack_ctx_w2": (C.c_int, [C.c_void_p] * 5 + [C.c_int, C.c_void_p]),
     "can_transpose_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "can_conv_first_fwd": (C.c_int, [C.c_void_p] * 4 + [C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
@@ -57,6 +60,7 @@ _SIGNATURES = {
     "can_conv_wgrad": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_int]
                        + [C.c_int] * 8 + [C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_int64, C.c_void_p]),
     "can_ctx_wint": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "can_ctx_ttab": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "can_ctx_pos_gemv": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                    C.c_int, C.c_void_p]),
     "can_ctx_outer": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int, C.c_void_p,

@@ -13,10 +13,12 @@ frontend (w,b) x10, backend (w,b) x6, output_layer (w,b), conv{1,2,3,6}_{1,2}.we
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import ops
-from .ops import (MODE_CTX, MODE_CTX_BWD, MODE_DFV, MODE_HEAD, MODE_POOL, MODE_STORE, MODE_UNPOOL, Act)
+from .ops import (MODE_CTX, MODE_CTX2, MODE_CTX_BWD, MODE_DFV, MODE_HEAD, MODE_POOL, MODE_STORE, MODE_UNPOOL, Act)
 
 FRONTEND_CONVS = (0, 2, 5, 7, 10, 12, 14, 17, 19, 21)  # Sequential indices, CANNet.py:104-121
 POOLED_LAYERS = (1, 3, 6)                               # frontend convs followed by MaxPool2d(2,2)
@@ -45,6 +47,13 @@ class WeightCache:
         """Drop every entry derived from parameters (after an in-place arena update, which does
         not bump version counters); shape-only entries (empty tag) are kept."""
         self._store = {k: v for k, v in self._store.items() if v[0] == ()}
+
+
+def _packed(cache, tag, li, wt, nsplit, both):
+    """(fwd pack[, dgrad pack]) of one conv weight; a training step builds both in one pass."""
+    if both:
+        return cache.get((tag, li, nsplit, "both"), (wt,), lambda: ops.pack_conv_weight_both(wt, nsplit))
+    return (cache.get((tag, li, nsplit), (wt,), lambda: ops.pack_conv_weight(wt, nsplit)),)
 
 
 def _conv_params(model):
@@ -78,7 +87,7 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
     for li in range(1, 10):
         wt, bs = fr[li]
         cout = wt.shape[0]
-        wp = cache.get(("f", li, nsplit), (wt,), lambda wt=wt: ops.pack_conv_weight(wt, nsplit))
+        wp = _packed(cache, "f", li, wt, nsplit, save)[0]
         bias = bs.detach().float()
         if li in POOLED_LAYERS:
             h, w = h // 2, w // 2
@@ -105,7 +114,12 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
     w2stack = cache.get(("w2stack", nsplit), w2s, lambda: ops.pack_ctx_w2(w2s, nsplit))
     pooled, tabA, tabB = ops.ctx_pool(fv, w1, w2)
     fi = cat.view(512, 512)
-    ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX, out=fi, tabA=tabA, tabB=tabB)
+    if nsplit == 1 and os.environ.get("CAN_B200_CTX2", "1") != "0":
+        # bf16 path: the bilinear interpolation of both tables is two extra k-blocks of the same GEMM
+        wint1 = cache.get(("wint", 1, h, w), (), lambda: ops.ctx_wint(1, 1, h, w, dev))
+        ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX2, out=fi, ctx_wint=wint1.buf, ctx_ttab=ops.ctx_ttab(tabA, tabB))
+    else:
+        ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX, out=fi, tabA=tabA, tabB=tabB)
 
     # ---- backend + head (CANNet.py:89-90) -----------------------------------------
     a = cat.view(1024, 0)
@@ -114,7 +128,7 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
     for li in range(6):
         wt, bs = bk[li]
         cout = wt.shape[0]
-        wp = cache.get(("b", li, nsplit), (wt,), lambda wt=wt: ops.pack_conv_weight(wt, nsplit))
+        wp = _packed(cache, "b", li, wt, nsplit, save)[0]
         bias = bs.detach().float()
         out = ops.new_act(nsplit, N, h, w, cout, dev)
         if li == 5:
@@ -165,7 +179,7 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
         X = bacts[li]
         ops.conv_wgrad(dz, X, grads[IDX_BACKEND + 2 * li], dil=2)
         ops.bias_grad(dz, grads[IDX_BACKEND + 2 * li + 1])
-        wd = cache.get(("bd", li, nsplit), (wt,), lambda wt=wt: ops.pack_conv_weight(wt, nsplit, dgrad=True))
+        wd = _packed(cache, "b", li, wt, nsplit, True)[1]
         ndz = ops.new_act(nsplit, N, h, w, cin, dev)
         if li > 0:
             ops.conv_tc(dz, wd, cin, dil=2, mode=MODE_STORE, relu=False, out=ndz, mask=X)
@@ -216,7 +230,7 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
         X = acts[li - 1]
         ops.conv_wgrad(dz, X, grads[2 * li], dil=1)
         ops.bias_grad(dz, grads[2 * li + 1])
-        wd = cache.get(("fd", li, nsplit), (wt,), lambda wt=wt: ops.pack_conv_weight(wt, nsplit, dgrad=True))
+        wd = _packed(cache, "f", li, wt, nsplit, True)[1]
         if (li - 1) in POOLED_LAYERS:
             pre = acts[li - 2]  # the pooled layer's input has its pre-pool resolution
             OH, OW = pre.H, pre.W

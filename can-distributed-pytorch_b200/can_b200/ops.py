@@ -12,7 +12,7 @@ import torch
 
 from ._lib import ConvArgs, check, lib
 
-MODE_STORE, MODE_POOL, MODE_HEAD, MODE_UNPOOL, MODE_CTX, MODE_CTX_BWD, MODE_DFV = range(7)
+MODE_STORE, MODE_POOL, MODE_HEAD, MODE_UNPOOL, MODE_CTX, MODE_CTX_BWD, MODE_DFV, MODE_CTX2 = range(8)
 
 #: number of kernels of this library launched so far (bench.py reports the count per timed region)
 LAUNCHES = 0
@@ -122,6 +122,19 @@ def pack_conv_weight(w: torch.Tensor, nsplit: int, dgrad: bool = False) -> torch
     return dst
 
 
+def pack_conv_weight_both(w: torch.Tensor, nsplit: int):
+    """(fwd pack, dgrad pack) of one OIHW fp32 weight in a single pass over it."""
+    co, ci, kh, kw = w.shape
+    taps = kh * kw
+    w = w.detach().contiguous().float()
+    fwd = torch.empty(nsplit, co, taps * ci, device=w.device, dtype=torch.bfloat16)
+    dg = torch.empty(nsplit, ci, taps * co, device=w.device, dtype=torch.bfloat16)
+    check(lib().can_pack_conv_weight_both(w.data_ptr(), fwd.data_ptr(), dg.data_ptr(), co, ci, taps, nsplit, _stream()),
+          "pack_conv_weight_both")
+    _count()
+    return fwd, dg
+
+
 def pack_ctx_w2(ws, nsplit: int) -> torch.Tensor:
     ws = [w.detach().contiguous().float() for w in ws]
     dst = torch.empty(nsplit, 2048, 512, device=ws[0].device, dtype=torch.bfloat16)
@@ -157,7 +170,7 @@ def conv_first(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, nsplit: int) -
 
 def conv_tc(x: Act, wp: torch.Tensor, Cout: int, *, taps=9, dil=1, mode=MODE_STORE, relu=True, bias=None, out: Act = None,
             out_f32=None, mask: Act = None, arg=None, head_w=None, head_b=None, head_out=None, tabA=None, tabB=None,
-            OH=0, OW=0, bn=0, stages=0, add: Act = None):
+            OH=0, OW=0, bn=0, stages=0, add: Act = None, ctx_wint=None, ctx_ttab=None):
     a = ConvArgs()
     a.N, a.H, a.W = x.N, x.H, x.W
     a.Cin, a.Cout = x.C, Cout
@@ -177,6 +190,7 @@ def conv_tc(x: Act, wp: torch.Tensor, Cout: int, *, taps=9, dil=1, mode=MODE_STO
     a.OH, a.OW = OH, OW
     a.head_w, a.head_b, a.head_out = _ptr(head_w), _ptr(head_b), _ptr(head_out)
     a.tabA, a.tabB = _ptr(tabA), _ptr(tabB)
+    a.ctx_wint, a.ctx_ttab = _ptr(ctx_wint), _ptr(ctx_ttab)
     _count()
     with _Prof(2.0 * taps * x.C * Cout * x.N * x.H * x.W):
         check(lib().can_conv_tc(C.byref(a), _stream()), "conv_tc")
@@ -277,6 +291,14 @@ def ctx_wint(nsplit, N, H, W, device) -> Act:
     check(lib().can_ctx_wint(out.buf.data_ptr(), out.plane, nsplit, N, H, W, _stream()), "ctx_wint")
     _count()
     return out
+
+
+def ctx_ttab(tabA, tabB):
+    N = tabA.shape[0]
+    T = torch.empty(2, N, 2048, 64, device=tabA.device, dtype=torch.bfloat16)
+    check(lib().can_ctx_ttab(tabA.data_ptr(), tabB.data_ptr(), T.data_ptr(), N, _stream()), "ctx_ttab")
+    _count()
+    return T
 
 
 def ctx_pos_gemv(Wm, inp, in_ns, in_ps, in_js, add, N):

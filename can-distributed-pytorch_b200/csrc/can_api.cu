@@ -12,6 +12,7 @@
 #include "can_conv_tc.cuh"
 #include "can_simple.cuh"
 #include "can_wgrad_tc.cuh"
+#include "can_aux.cuh"
 
 using namespace canb;
 
@@ -68,6 +69,10 @@ int env_int(const char* name, int dflt) {
 
 constexpr int kMaxSmem = 232448;  // 227 KB opt-in limit per CTA on sm_100
 
+// extra tensor maps of MODE_CTX2 (interpolation matrix, per-image tables); other modes pass copies of tmA
+thread_local const CUtensorMap* g_tmW = nullptr;
+thread_local const CUtensorMap* g_tmT = nullptr;
+
 template <int BN, int NSPLIT, int MODE>
 int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p, dim3 grid, int stages_override,
                 cudaStream_t st) {
@@ -88,7 +93,7 @@ int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p,
     attr_done = true;
     attr_smem = kMaxSmem;
   }
-  kern<<<grid, 192, smem, st>>>(tmA, tmB, p);
+  kern<<<grid, 192, smem, st>>>(tmA, tmB, g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA, p);
   CAN_CHECK_LAUNCH("conv_tc launch");
   return 0;
 }
@@ -167,7 +172,7 @@ int launch_ctx_gemv(const float* Wm, const float* in, long long in_ns, long long
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(ctx_pos_gemv)");
     attr = true;
   }
-  ctx_pos_gemv_kernel<<<dim3(8, 4, N), 256, 36 * 512 * 4, st>>>(Wm, in, in_ns, in_ps, in_js, add, out);
+  ctx_pos_gemv_kernel<<<dim3(32, 4, N), 256, 9 * 512 * 4, st>>>(Wm, in, in_ns, in_ps, in_js, add, out);
   CAN_CHECK_LAUNCH("ctx_pos_gemv");
   return 0;
 }
@@ -182,7 +187,7 @@ int can_version(void) { return 100; }
 int can_conv_tc(const can_conv_args* a, void* stream) {
   if (!a) return fail(-1, "conv_tc: null args");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const bool ctx = a->mode == CAN_MODE_CTX || a->mode == CAN_MODE_CTX_BWD;
+  const bool ctx = a->mode == CAN_MODE_CTX || a->mode == CAN_MODE_CTX_BWD || a->mode == CAN_MODE_CTX2;
   if (a->N <= 0 || a->H <= 0 || a->W <= 0) return fail(-2, "conv_tc: bad shape N=%d H=%d W=%d", a->N, a->H, a->W);
   if (a->Cin <= 0 || a->Cin % 64) return fail(-3, "conv_tc: Cin=%d must be a positive multiple of 64", a->Cin);
   if (a->taps != 1 && a->taps != 9) return fail(-4, "conv_tc: taps=%d (want 1 or 9)", a->taps);
@@ -197,7 +202,12 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   int bn = a->bn;
   if (ctx) {
     if (a->Cout != 2048 || a->Cin != 512 || a->taps != 1) return fail(-10, "conv_tc: CTX wants Cin=512 Cout=2048 taps=1");
-    if (!a->tabA || !a->tabB || !a->out) return fail(-10, "conv_tc: CTX needs tabA/tabB/out");
+    if (a->mode == CAN_MODE_CTX2) {
+      if (a->nsplit != 1 || !a->ctx_wint || !a->ctx_ttab || !a->out)
+        return fail(-10, "conv_tc: CTX2 is the bf16 path (nsplit 1) and needs ctx_wint, ctx_ttab and out");
+    } else if (!a->tabA || !a->tabB || !a->out) {
+      return fail(-10, "conv_tc: CTX needs tabA/tabB/out");
+    }
     if (a->mode == CAN_MODE_CTX_BWD && (!a->mask || a->out_cs != 4096))
       return fail(-10, "conv_tc: CTX_BWD needs the fi-gradient in `mask` and a 4096-channel output");
     bn = 256;
@@ -217,7 +227,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   if (a->mode == CAN_MODE_UNPOOL && (!a->mask || !a->arg || a->OH < 2 * a->H || a->OW < 2 * a->W))
     return fail(-14, "conv_tc: UNPOOL needs mask, arg and OH>=2H, OW>=2W");
   if (a->mode == CAN_MODE_DFV && (!a->mask || !a->add || !a->tabA)) return fail(-14, "conv_tc: DFV needs mask, add and tabA");
-  if (a->mode < 0 || a->mode > CAN_MODE_DFV) return fail(-15, "conv_tc: mode=%d", a->mode);
+  if (a->mode < 0 || a->mode > CAN_MODE_CTX2) return fail(-15, "conv_tc: mode=%d", a->mode);
 
   ConvTcParams p;
   memset(&p, 0, sizeof(p));
@@ -265,9 +275,41 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     int rc = make_tmap(&tmB, a->w, 3, dims, str, box);
     if (rc) return rc;
   }
-  dim3 grid(p.tiles_x * p.tiles_y * a->N, a->Cout / bn);
+  // persistent CTAs: one per SM (or fewer when there are fewer tiles), striding over the tile list
+  p.n_tiles = a->Cout / bn;
+  p.num_tiles = p.tiles_x * p.tiles_y * a->N * p.n_tiles;
+  static int sm_count = 0;
+  if (!sm_count) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
+      sm_count = 148;
+  }
+  const int ctas_env = env_int("CAN_B200_CTAS", 0);
+  int ctas = ctas_env > 0 ? ctas_env : sm_count;
+  if (ctas > p.num_tiles) ctas = p.num_tiles;
+  dim3 grid(ctas);
   const int so = a->stages > 0 ? a->stages : env_int("CAN_B200_STAGES", 0);
   const int ns = a->nsplit;
+  g_tmW = nullptr;
+  g_tmT = nullptr;
+  if (a->mode == CAN_MODE_CTX2) {
+    CUtensorMap tmW, tmT;
+    int rc = make_act_tmap(&tmW, a->ctx_wint, 0, 64, 64, 0, 1, 1, a->H, a->W, p.TW, p.TH);
+    if (rc) return rc;
+    const uint64_t dimsT[5] = {64, 2048, static_cast<uint64_t>(a->N), 2, 1};
+    const uint64_t rowb = 128, imgb = rowb * 2048, tabb = imgb * a->N;
+    const uint64_t strT[4] = {rowb, imgb, tabb, tabb * 2};
+    const uint32_t boxT[5] = {64, 256, 1, 1, 1};
+    rc = make_tmap(&tmT, a->ctx_ttab, 5, dimsT, strT, boxT);
+    if (rc) return rc;
+    g_tmW = &tmW;
+    g_tmT = &tmT;
+    rc = launch_conv<256, 1, MODE_CTX2>(tmA, tmB, p, grid, so, st);
+    g_tmW = nullptr;
+    g_tmT = nullptr;
+    return rc;
+  }
   if (ctx) {
     if (a->mode == CAN_MODE_CTX)
       return ns == 1   ? launch_conv<256, 1, MODE_CTX>(tmA, tmB, p, grid, so, st)
@@ -299,10 +341,17 @@ int can_pack_conv_weight(const float* w, void* dst, int cout, int cin, int taps,
                          void* stream) {
   if (!w || !dst || cout <= 0 || cin <= 0 || taps <= 0 || nsplit < 1 || nsplit > 3)
     return fail(-1, "pack_conv_weight: bad arguments");
-  const long long total = static_cast<long long>(cout) * cin * taps;
-  const int blocks = static_cast<int>((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256);
-  pack_conv_weight_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      w, static_cast<__nv_bfloat16*>(dst), cout, cin, taps, nsplit, dgrad);
+  if (cout % 32 == 0 && cin % 32 == 0 && taps <= 9) {
+    __nv_bfloat16* d = static_cast<__nv_bfloat16*>(dst);
+    pack_conv_weight_kernel_v2<<<dim3(cin / 32, cout / 32), 256, 32 * (32 * taps + 1) * sizeof(float),
+                                 static_cast<cudaStream_t>(stream)>>>(w, dgrad ? nullptr : d, dgrad ? d : nullptr, cout,
+                                                                      cin, taps, nsplit);
+  } else {
+    const long long total = static_cast<long long>(cout) * cin * taps;
+    const int blocks = static_cast<int>((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256);
+    pack_conv_weight_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        w, static_cast<__nv_bfloat16*>(dst), cout, cin, taps, nsplit, dgrad);
+  }
   CAN_CHECK_LAUNCH("pack_conv_weight");
   return 0;
 }
@@ -533,9 +582,8 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
   else
     rc = launch_wgrad<256, 1>(tmDZ, tmX, p, grid, st);
   if (rc) return rc;
-  const long long total = static_cast<long long>(Cout) * Cin * taps;
-  const int blocks = static_cast<int>((total + 255) / 256 > 2368 ? 2368 : (total + 255) / 256);
-  wgrad_reduce_kernel<<<blocks, 256, 0, st>>>(p.ws, grad, pl.ksplit, taps, Cout, Cin, accumulate, alpha);
+  wgrad_reduce_kernel_v2<<<dim3(Cin / 32, Cout), 32 * taps, 0, st>>>(p.ws, grad, pl.ksplit, taps, Cout, Cin, accumulate,
+                                                                     alpha);
   CAN_CHECK_LAUNCH("wgrad_reduce");
   return 0;
 }
@@ -553,8 +601,15 @@ int can_bias_grad(const void* dz, int64_t plane, int nsplit, int cs, int coff, i
   if (!dz || !db || C <= 0 || C > 1024 || C % 2 || npix <= 0 || cs % 2 || coff % 2) return fail(-1, "bias_grad: bad arguments");
   long long blocks = (npix + 63) / 64;
   if (blocks > 148 * 4) blocks = 148 * 4;
-  bias_grad_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(dz), plane, nsplit, cs, coff, C, npix, db);
+  if (C % 8 == 0 && 256 % (C / 8) == 0 && cs % 8 == 0 && coff % 8 == 0) {
+    long long b2 = (npix + 255) / 256;
+    if (b2 > 148 * 8) b2 = 148 * 8;
+    bias_grad_kernel_v2<<<static_cast<int>(b2), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(dz), plane, nsplit, cs, coff, C, npix, db);
+  } else {
+    bias_grad_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(dz), plane, nsplit, cs, coff, C, npix, db);
+  }
   CAN_CHECK_LAUNCH("bias_grad");
   return 0;
 }
@@ -592,6 +647,26 @@ int can_ctx_outer(const float* A, int64_t a_ns, int64_t a_ps, int64_t a_js, cons
   ctx_outer_kernel<<<dim3(32, 4), 256, 0, static_cast<cudaStream_t>(stream)>>>(A, a_ns, a_ps, a_js, B, N, dW, alpha,
                                                                               accumulate);
   CAN_CHECK_LAUNCH("ctx_outer");
+  return 0;
+}
+
+int can_pack_conv_weight_both(const float* w, void* dst_fwd, void* dst_dgrad, int cout, int cin, int taps, int nsplit,
+                              void* stream) {
+  if (!w || (!dst_fwd && !dst_dgrad) || cout <= 0 || cin <= 0 || taps <= 0 || taps > 9 || nsplit < 1 || nsplit > 3)
+    return fail(-1, "pack_conv_weight_both: bad arguments");
+  if (cout % 32 || cin % 32) return fail(-2, "pack_conv_weight_both: cout and cin must be multiples of 32");
+  pack_conv_weight_kernel_v2<<<dim3(cin / 32, cout / 32), 256, 32 * (32 * taps + 1) * sizeof(float),
+                               static_cast<cudaStream_t>(stream)>>>(w, static_cast<__nv_bfloat16*>(dst_fwd),
+                                                                    static_cast<__nv_bfloat16*>(dst_dgrad), cout, cin,
+                                                                    taps, nsplit);
+  CAN_CHECK_LAUNCH("pack_conv_weight_both");
+  return 0;
+}
+
+int can_ctx_ttab(const float* tabA, const float* tabB, void* T, int N, void* stream) {
+  if (!tabA || !tabB || !T || N <= 0) return fail(-1, "ctx_ttab: bad arguments");
+  ctx_ttab_kernel<<<148 * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(tabA, tabB, static_cast<__nv_bfloat16*>(T), N);
+  CAN_CHECK_LAUNCH("ctx_ttab");
   return 0;
 }
 

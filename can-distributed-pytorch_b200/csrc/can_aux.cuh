@@ -1,0 +1,129 @@
+// Second-generation HBM-bound helpers (coalesced, vectorised): bias gradient, split-K wgrad
+// reduction into the parameter layout, and weight packing for both GEMM orientations.
+#pragma once
+#include "can_ptx.cuh"
+
+namespace canb {
+
+// db[c] += sum over pixels of dz[pix][c]   (dz: NHWC bf16 planes, C % 8 == 0, C <= 1024)
+// 256 threads = G channel groups (8 channels = one 16-byte load each) x PL pixel lanes.
+// Each block owns a contiguous pixel range, keeps 4 loads in flight per thread, combines the
+// pixel lanes in shared memory and issues one atomicAdd per channel.
+__global__ void __launch_bounds__(256)
+bias_grad_kernel_v2(const __nv_bfloat16* __restrict__ dz, long long plane, int nsplit, int cs, int coff, int C,
+                    long long npix, float* __restrict__ db) {
+  __shared__ float s_part[256 * 8];
+  const int G = C >> 3;
+  const int PL = 256 / G;          // G in {8,16,32,64,128} -> PL in {32,...,2}
+  const int cg = threadIdx.x % G, pl = threadIdx.x / G;
+  const long long per = (npix + gridDim.x - 1) / gridDim.x;
+  const long long p0 = blockIdx.x * per, p1 = min(p0 + per, npix);
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+  if (pl < PL) {
+    const __nv_bfloat16* base = dz + coff + cg * 8;
+    for (int s = 0; s < nsplit; ++s) {
+      const __nv_bfloat16* b = base + s * plane;
+      long long px = p0 + pl;
+      for (; px + 3LL * PL < p1; px += 4LL * PL) {
+        uint4 q[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) q[u] = *reinterpret_cast<const uint4*>(b + (px + static_cast<long long>(u) * PL) * cs);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q[u]);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            acc[2 * e] += __low2float(h[e]);
+            acc[2 * e + 1] += __high2float(h[e]);
+          }
+        }
+      }
+      for (; px < p1; px += PL) {
+        const uint4 q = *reinterpret_cast<const uint4*>(b + px * cs);
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          acc[2 * e] += __low2float(h[e]);
+          acc[2 * e + 1] += __high2float(h[e]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) s_part[threadIdx.x * 8 + e] = acc[e];
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += 256) {
+    const int g = c >> 3, e = c & 7;
+    float t = 0.f;
+    for (int l = 0; l < PL; ++l) t += s_part[(l * G + g) * 8 + e];
+    atomicAdd(db + c, t);
+  }
+}
+
+// grad[co][ci][tap] (parameter layout) = (accumulate ? grad : 0) + alpha * sum_s ws[s][tap][co][ci]
+// grid (cin/32, cout), block 32*taps: coalesced reads per tap, transposed through shared memory,
+// coalesced 32*taps-float write.
+__global__ void wgrad_reduce_kernel_v2(const float* __restrict__ ws, float* __restrict__ grad, int splits, int taps,
+                                       int cout, int cin, int accumulate, float alpha) {
+  __shared__ float s_t[32 * 9];
+  const int co = blockIdx.y, ci0 = blockIdx.x * 32;
+  const int c = threadIdx.x & 31, tap = threadIdx.x >> 5;
+  const long long slab = static_cast<long long>(taps) * cout * cin;
+  const float* src = ws + (static_cast<long long>(tap) * cout + co) * cin + ci0 + c;
+  float acc = 0.f;
+  for (int s = 0; s < splits; ++s) acc += src[s * slab];
+  s_t[c * taps + tap] = acc;
+  __syncthreads();
+  float* g = grad + (static_cast<long long>(co) * cin + ci0) * taps + threadIdx.x;
+  *g = (accumulate ? *g : 0.f) + alpha * s_t[threadIdx.x];
+}
+
+// Pack one conv weight [cout][cin][taps] fp32 into the K-major bf16 planes of BOTH GEMM
+// orientations in one pass (either destination may be null):
+//   fwd  [pl][co][tap][ci]           dgrad [pl][ci][taps-1-tap][co]
+// grid (cin/32, cout/32); block 256.  Reads are contiguous runs of 32*taps floats per output
+// channel; writes are 64-byte runs.
+__global__ void __launch_bounds__(256)
+pack_conv_weight_kernel_v2(const float* __restrict__ w, __nv_bfloat16* __restrict__ fwd,
+                           __nv_bfloat16* __restrict__ dgrad, int cout, int cin, int taps, int nsplit) {
+  extern __shared__ float s_w[];  // [32 co][32*taps + 1]
+  const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 32;
+  const int row = 32 * taps + 1;
+  for (int i = threadIdx.x; i < 32 * 32 * taps; i += 256) {
+    const int r = i / (32 * taps), o = i - r * 32 * taps;
+    s_w[r * row + o] = w[(static_cast<long long>(co0 + r) * cin + ci0) * taps + o];
+  }
+  __syncthreads();
+  const long long total = static_cast<long long>(cout) * cin * taps;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (fwd) {
+    // one warp per (co, tap): lanes = ci
+    for (int i = wid; i < 32 * taps; i += 8) {
+      const int r = i / taps, tap = i - r * taps;
+      float v = s_w[r * row + lane * taps + tap];
+      __nv_bfloat16* d = fwd + (static_cast<long long>(co0 + r) * taps + tap) * cin + ci0 + lane;
+      for (int pl = 0; pl < nsplit; ++pl) {
+        const __nv_bfloat16 h = __float2bfloat16_rn(v);
+        d[pl * total] = h;
+        v -= __bfloat162float(h);
+      }
+    }
+  }
+  if (dgrad) {
+    // one warp per (ci, tap): lanes = co
+    for (int i = wid; i < 32 * taps; i += 8) {
+      const int ci = i / taps, tap = i - ci * taps;
+      float v = s_w[lane * row + ci * taps + tap];
+      __nv_bfloat16* d = dgrad + (static_cast<long long>(ci0 + ci) * taps + (taps - 1 - tap)) * cout + co0 + lane;
+      for (int pl = 0; pl < nsplit; ++pl) {
+        const __nv_bfloat16 h = __float2bfloat16_rn(v);
+        d[pl * total] = h;
+        v -= __bfloat162float(h);
+      }
+    }
+  }
+}
+
+}  // namespace canb

@@ -26,6 +26,7 @@ enum ConvMode : int {
   MODE_CTX = 4,     // contextual fusion epilogue: fi from the stacked contrast GEMM
   MODE_CTX_BWD = 5, // same GEMM recomputed; writes dz_j and the direct ds_j (backward of the fusion)
   MODE_DFV = 6,     // dfv = (add - acc + pooled-gradient spread) * (mask > 0)
+  MODE_CTX2 = 7,    // contextual fusion with the bilinear interpolation folded into the GEMM (bf16 path)
 };
 
 struct ConvTcParams {
@@ -35,6 +36,8 @@ struct ConvTcParams {
   int dil;             // tap spacing (1 | 2); padding == dil
   int TW, TH;          // spatial tile, TW*TH == 128, TW in {8,16}
   int tiles_x, tiles_y;
+  int n_tiles;         // Cout / BN
+  int num_tiles;       // tiles_x * tiles_y * N * n_tiles (persistent CTAs stride over them)
   int stages;
   int relu;
   const float* bias;   // [Cout] or null
@@ -76,7 +79,7 @@ struct ConvTcSmem {
   static constexpr int kBBytes = BN * 128;        // BN rows x 64 k x bf16
   static constexpr int kStageBytes = NSPLIT * (kABytes + kBBytes);
   static constexpr int kCtxTabBytes = 2 * 50 * 64 * 4;
-  static constexpr int kTailBytes = 1024 + BN * 4;  // barriers + tmem ptr, bias
+  static constexpr int kTailBytes = 1024 + 2 * BN * 4;  // barriers + tmem ptr, bias (double-buffered)
   static __host__ __device__ constexpr int bytes(int stages, bool ctx) {
     return 1024 /*align slack*/ + stages * kStageBytes + kTailBytes + (ctx ? kCtxTabBytes : 0);
   }
@@ -128,6 +131,9 @@ template <int BN, int GS>
 struct AccLayout {
   static constexpr int kNacc = (GS >= 2) ? (512 / BN - 1) : 1;   // hi*hi accumulators
   static constexpr int kCols = (GS >= 2) ? 512 : (BN < 32 ? 32 : BN);
+  static constexpr int cols(int mode) { return mode == MODE_CTX2 ? 512 : kCols; }
+  // two accumulator stages when they fit: the epilogue of tile i overlaps the MMAs of tile i+1
+  static constexpr int acc_stages(int mode) { return cols(mode) * 2 <= 512 ? 2 : 1; }
 };
 
 template <int NV>
@@ -159,6 +165,7 @@ __device__ __forceinline__ void load_acc(uint32_t taddr, int col, int nact, floa
 template <int BN, int NSPLIT, int MODE>
 __global__ void __launch_bounds__(192, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmT,
                const ConvTcParams p) {
   constexpr int GS = gemm_planes(NSPLIT, MODE);  // planes that enter the GEMM
   using L = ConvTcSmem<BN, GS>;
@@ -168,27 +175,40 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint8_t* tail = smem + stages * L::kStageBytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
   uint64_t* empty_bar = full_bar + 8;
-  uint64_t* tmem_full_bar = empty_bar + 8;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
-  float* s_bias = reinterpret_cast<float*>(tail + 1024);
-  float* s_tab = s_bias + BN;  // MODE_CTX only: [2][50][64]
+  uint64_t* tmem_full_bar = empty_bar + 8;    // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;  // [2]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+  float* s_bias2 = reinterpret_cast<float*>(tail + 1024);  // [2][BN]
+  float* s_tab = s_bias2 + 2 * BN;  // MODE_CTX / MODE_CTX_BWD only: [2][50][64]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // tile coordinates
-  int t = blockIdx.x;
-  const int tx_i = t % p.tiles_x;
-  t /= p.tiles_x;
-  const int ty_i = t % p.tiles_y;
-  const int n_img = t / p.tiles_y;
-  const int x0 = tx_i * p.TW, y0 = ty_i * p.TH;
-  const int n0 = blockIdx.y * BN;
-  const int num_kb = p.taps * p.kchunks;
+  constexpr int ACC_COLS = AccLayout<BN, GS>::cols(MODE);
+  constexpr int ACC_STAGES = AccLayout<BN, GS>::acc_stages(MODE);
+  const int base_kb = p.taps * p.kchunks;
+  // MODE_CTX2: two extra k-blocks whose A operand is the interpolation matrix Wint[pixel][64 positions]
+  // and whose B operands are the per-image tables (-U-side of z, then s) -- see the epilogue.
+  const int num_kb = base_kb + (MODE == MODE_CTX2 ? 2 : 0);
+  // Persistent CTA: tiles blockIdx.x, blockIdx.x + gridDim.x, ...; the n-tile index varies fastest so
+  // that CTAs working at the same time share the activation patch in L2.
+#define CAN_TILE_DECODE(tile)                                   \
+  const int n_tile = (tile) % p.n_tiles;                        \
+  int t_ = (tile) / p.n_tiles;                                  \
+  const int tx_i = t_ % p.tiles_x;                              \
+  t_ /= p.tiles_x;                                              \
+  const int ty_i = t_ % p.tiles_y;                              \
+  const int n_img = t_ / p.tiles_y;                             \
+  const int x0 = tx_i * p.TW, y0 = ty_i * p.TH;                 \
+  const int n0 = n_tile * BN;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (MODE == MODE_CTX2) {
+      tma_prefetch_desc(&tmW);
+      tma_prefetch_desc(&tmT);
+    }
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -196,11 +216,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_init(&full_bar[s], 1);
         mbar_init(&empty_bar[s], 1);
       }
-      mbar_init(tmem_full_bar, 1);
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&tmem_full_bar[a], 1);
+        mbar_init(&tmem_empty_bar[a], 128);  // every epilogue thread arrives
+      }
       fence_mbar_init();
     }
     __syncwarp();
-    tmem_alloc(tmem_ptr_smem, AccLayout<BN, GS>::kCols);
+    tmem_alloc(tmem_ptr_smem, ACC_COLS * ACC_STAGES);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -213,26 +236,34 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        const int tap = kb / p.kchunks;
-        const int chunk = kb - tap * p.kchunks;
-        int dy = 0, dx = 0;
-        if (p.taps == 9) {
-          dy = (tap / 3 - 1) * p.dil;
-          dx = (tap % 3 - 1) * p.dil;
-        }
-        uint8_t* sa = smem + stage * L::kStageBytes;
-        uint8_t* sb = sa + GS * L::kABytes;
-        mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        CAN_TILE_DECODE(tile)
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          const int tap = kb / p.kchunks;
+          const int chunk = kb - tap * p.kchunks;
+          int dy = 0, dx = 0;
+          if (p.taps == 9) {
+            dy = (tap / 3 - 1) * p.dil;
+            dx = (tap % 3 - 1) * p.dil;
+          }
+          uint8_t* sa = smem + stage * L::kStageBytes;
+          uint8_t* sb = sa + GS * L::kABytes;
+          mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+          if (MODE == MODE_CTX2 && kb >= base_kb) {
+            tma_load_5d(sa, &tmW, &full_bar[stage], 0, x0, y0, 0, 0);
+            tma_load_5d(sb, &tmT, &full_bar[stage], 0, n0, n_img, kb - base_kb, 0);
+          } else {
 #pragma unroll
-        for (int pl = 0; pl < GS; ++pl) {
-          tma_load_5d(sa + pl * L::kABytes, &tmA, &full_bar[stage], chunk * 64, x0 + dx, y0 + dy, n_img, pl);
-          tma_load_3d(sb + pl * L::kBBytes, &tmB, &full_bar[stage], kb * 64, n0, pl);
-        }
-        if (++stage == stages) {
-          stage = 0;
-          phase ^= 1;
+            for (int pl = 0; pl < GS; ++pl) {
+              tma_load_5d(sa + pl * L::kABytes, &tmA, &full_bar[stage], chunk * 64, x0 + dx, y0 + dy, n_img, pl);
+              tma_load_3d(sb + pl * L::kBBytes, &tmB, &full_bar[stage], kb * 64, n0, pl);
+            }
+          }
+          if (++stage == stages) {
+            stage = 0;
+            phase ^= 1;
+          }
         }
       }
     }
@@ -243,45 +274,66 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int stage = 0;
       uint32_t phase = 0;
       constexpr int NACC = AccLayout<BN, GS>::kNacc;
-      uint32_t used = 0;  // bit a: accumulator a already holds a partial sum
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(&full_bar[stage], phase);
+      int it = 0;  // tiles processed by this CTA
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        const int as = it % ACC_STAGES;
+        const uint32_t aphase = static_cast<uint32_t>(it / ACC_STAGES) & 1u;
+        mbar_wait(&tmem_empty_bar[as], aphase ^ 1);  // epilogue drained this accumulator stage
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
-        const uint32_t sb = sa + GS * L::kABytes;
+        const uint32_t tacc = tmem_base + as * ACC_COLS;
+        uint32_t used = 0;  // bit a: accumulator a already holds a partial sum
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
+          const uint32_t sb = sa + GS * L::kABytes;
 #pragma unroll
-        for (int pa = 0; pa < GS; ++pa) {
+          for (int pa = 0; pa < GS; ++pa) {
 #pragma unroll
-          for (int pb = 0; pb < GS; ++pb) {
-            if (pa + pb < GS) {
-              const int acc = (GS == 1) ? 0 : ((pa + pb == 0) ? (kb % NACC) : NACC);
+            for (int pb = 0; pb < GS; ++pb) {
+              if (pa + pb < GS) {
+                // CTX2: the last k-block (Wint x a-table) goes to the second 256-column region (S)
+                const int acc = (MODE == MODE_CTX2) ? (kb == base_kb + 1 ? 1 : 0)
+                                : (GS == 1)         ? 0
+                                                    : ((pa + pb == 0) ? (kb % NACC) : NACC);
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                const uint64_t da = umma_smem_desc(sa + pa * L::kABytes + k * 32, 16, 1024);
-                const uint64_t db = umma_smem_desc(sb + pb * L::kBBytes + k * 32, 16, 1024);
-                umma_bf16(tmem_base + acc * BN, da, db, idesc, (used >> acc) & 1u);
-                used |= 1u << acc;
+                for (int k = 0; k < 4; ++k) {
+                  const uint64_t da = umma_smem_desc(sa + pa * L::kABytes + k * 32, 16, 1024);
+                  const uint64_t db = umma_smem_desc(sb + pb * L::kBBytes + k * 32, 16, 1024);
+                  umma_bf16(tacc + acc * BN, da, db, idesc, (used >> acc) & 1u);
+                  used |= 1u << acc;
+                }
               }
             }
           }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+          if (++stage == stages) {
+            stage = 0;
+            phase ^= 1;
+          }
         }
-        umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
-        if (++stage == stages) {
-          stage = 0;
-          phase ^= 1;
-        }
+        umma_commit(&tmem_full_bar[as]);  // accumulator of this tile complete
       }
-      umma_commit(tmem_full_bar);  // accumulator complete
     }
   } else {
     // ===================== epilogue (warps 2..5) =====================
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     const int etid = threadIdx.x - 64;
+    const int m = q * 32 + lane;
+    const int ty = m / p.TW, tx = m - ty * p.TW;
+    const int nact = min(AccLayout<BN, GS>::kNacc, num_kb);  // hi*hi accumulators actually written
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+    CAN_TILE_DECODE(tile)
+    const int as = it % ACC_STAGES;
+    const uint32_t aphase = static_cast<uint32_t>(it / ACC_STAGES) & 1u;
+    float* s_bias = s_bias2 + (it & 1) * BN;
     for (int i = etid; i < BN; i += 128) s_bias[i] = p.bias ? p.bias[n0 + i] : 0.f;
     if (MODE == MODE_CTX || MODE == MODE_CTX_BWD) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // everyone finished reading the previous tile's tables
       // tables of this image for the 64 channels of this n-tile: [2][50][64]
-      const float* ga = p.tabA + (static_cast<long long>(n_img) * 50) * 512 + blockIdx.y * 64;
-      const float* gb = p.tabB + (static_cast<long long>(n_img) * 50) * 512 + blockIdx.y * 64;
+      const float* ga = p.tabA + (static_cast<long long>(n_img) * 50) * 512 + n_tile * 64;
+      const float* gb = p.tabB + (static_cast<long long>(n_img) * 50) * 512 + n_tile * 64;
       for (int i = etid; i < 50 * 16; i += 128) {
         const int pos = i >> 4, c4 = (i & 15) * 4;
         *reinterpret_cast<float4*>(s_tab + pos * 64 + c4) = *reinterpret_cast<const float4*>(ga + pos * 512 + c4);
@@ -291,15 +343,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     asm volatile("bar.sync 1, 128;" ::: "memory");
 
-    const int m = q * 32 + lane;
-    const int ty = m / p.TW, tx = m - ty * p.TW;
     const int y = y0 + ty, x = x0 + tx;
     const bool valid = (y < p.H) && (x < p.W);
-    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    const uint32_t taddr = tmem_base + as * ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
 
-    mbar_wait(tmem_full_bar, 0);
+    mbar_wait(&tmem_full_bar[as], aphase);
     tc_fence_after();
-    const int nact = min(AccLayout<BN, GS>::kNacc, num_kb);  // hi*hi accumulators actually written
 
     if (MODE == MODE_STORE) {
       const long long pix = (static_cast<long long>(n_img) * p.H + y) * p.W + x;
@@ -450,7 +499,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         pidx[j][3] = (OFF[j] + yi1 * SS[j] + xi1) * 64;
       }
       const long long pix = (static_cast<long long>(n_img) * p.H + y) * p.W + x;
-      __nv_bfloat16* obase = p.out + pix * p.out_cs + p.out_coff + blockIdx.y * 64;
+      __nv_bfloat16* obase = p.out + pix * p.out_cs + p.out_coff + n_tile * 64;
       const float* sA = s_tab;
       const float* sB = s_tab + 3200;
 #pragma unroll 1
@@ -494,6 +543,35 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         if (valid) store_bf16_planes<NSPLIT, 16>(obase + c0, p.out_plane, fi);
       }
+    } else if (MODE == MODE_CTX2) {
+      // TMEM columns [0,256): -z_j = W_j2 fv - U(W_j2 a_j)   (8 k-blocks of fv + 1 k-block Wint x (-b tables))
+      //              [256,512): s_j = U a_j                   (1 k-block Wint x a tables)
+      // column j*64 + c for the 64 channels of n-tile blockIdx.y.  w_j = sigmoid(z_j) = 1/(1+exp(-z_j)).
+      const long long pix = valid ? (static_cast<long long>(n_img) * p.H + y) * p.W + x : 0;
+      __nv_bfloat16* obase = p.out + pix * p.out_cs + p.out_coff + n_tile * 64;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 64; c0 += 16) {
+        uint32_t zr[4][16], sr[4][16];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          tmem_ld_32x16(taddr + j * 64 + c0, zr[j]);
+          tmem_ld_32x16(taddr + 256 + j * 64 + c0, sr[j]);
+        }
+        tmem_ld_wait();
+        float fi[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+          float num = 0.f, den = 0.f;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float wgt = 1.f / (1.f + __expf(__uint_as_float(zr[j][c])));
+            num = fmaf(wgt, __uint_as_float(sr[j][c]), num);
+            den += wgt;
+          }
+          fi[c] = num / (den + 1e-12f);
+        }
+        if (valid) store_bf16_planes<NSPLIT, 16>(obase + c0, p.out_plane, fi);
+      }
     } else if (MODE == MODE_CTX_BWD) {
       // Backward of the fusion (CANNet.py:84) and of sigmoid(conv{S}_2(s_j - fv)) w.r.t. z_j.
       // With D = sum_j w_j + 1e-12 and g = dL/dfi:
@@ -514,8 +592,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         pidx[j][3] = (OFF[j] + yi1 * SS[j] + xi1) * 64;
       }
       const long long pix = valid ? (static_cast<long long>(n_img) * p.H + y) * p.W + x : 0;
-      __nv_bfloat16* obase = p.out + pix * p.out_cs + blockIdx.y * 64;
-      const __nv_bfloat16* gbase = p.mask + pix * p.mask_cs + p.mask_coff + blockIdx.y * 64;
+      __nv_bfloat16* obase = p.out + pix * p.out_cs + n_tile * 64;
+      const __nv_bfloat16* gbase = p.mask + pix * p.mask_cs + p.mask_coff + n_tile * 64;
       const float* sA = s_tab;
       const float* sB = s_tab + 3200;
 #pragma unroll 1
@@ -668,13 +746,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
     }
+    // this accumulator stage may be overwritten by the MMAs of the tile after next
     tc_fence_before();
+    mbar_arrive(&tmem_empty_bar[as]);
+    }  // tile loop
   }
+#undef CAN_TILE_DECODE
 
+  tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, AccLayout<BN, GS>::kCols);
+    tmem_dealloc(tmem_base, ACC_COLS * ACC_STAGES);
   }
 }
 

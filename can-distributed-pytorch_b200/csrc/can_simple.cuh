@@ -217,10 +217,22 @@ ctx_pool_rows_kernel(const __nv_bfloat16* __restrict__ fv, long long fv_plane, i
   for (int sgi = 0; sgi < nseg; ++sgi) {
     const int xs = s_bound[sgi], xe = s_bound[sgi + 1];
     float a0 = 0.f, a1 = 0.f;
-    for (int x = xs; x < xe; ++x) {
-      for (int pl = 0; pl < nsplit; ++pl) {
-        const __nv_bfloat162 v =
-            *reinterpret_cast<const __nv_bfloat162*>(row + pl * fv_plane + static_cast<long long>(x) * cs);
+    for (int pl = 0; pl < nsplit; ++pl) {
+      const __nv_bfloat16* rp = row + pl * fv_plane;
+      int x = xs;
+      for (; x + 8 <= xe; x += 8) {  // 8 independent loads in flight
+        __nv_bfloat162 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          v[u] = *reinterpret_cast<const __nv_bfloat162*>(rp + static_cast<long long>(x + u) * cs);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          a0 += __low2float(v[u]);
+          a1 += __high2float(v[u]);
+        }
+      }
+      for (; x < xe; ++x) {
+        const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(rp + static_cast<long long>(x) * cs);
         a0 += __low2float(v);
         a1 += __high2float(v);
       }
@@ -258,7 +270,15 @@ ctx_pool_finalize_kernel(const float* __restrict__ R, float* __restrict__ pooled
   const int ys = adaptive_start(wy, H, S), ye = adaptive_end(wy, H, S);
   const int xs = adaptive_start(wx, W, S), xe = adaptive_end(wx, W, S);
   float acc = 0.f;
-  for (int y = ys; y < ye; ++y) acc += R[((static_cast<long long>(n) * H + y) * 12 + xwin) * 512 + c];
+  int y = ys;
+  for (; y + 8 <= ye; y += 8) {  // 8 independent loads in flight
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = R[((static_cast<long long>(n) * H + y + u) * 12 + xwin) * 512 + c];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) acc += v[u];
+  }
+  for (; y < ye; ++y) acc += R[((static_cast<long long>(n) * H + y) * 12 + xwin) * 512 + c];
   pooled[(static_cast<long long>(n) * 50 + p) * 512 + c] = acc / static_cast<float>((ye - ys) * (xe - xs));
 }
 
@@ -489,7 +509,7 @@ head_bwd_kernel(const float* __restrict__ dout, const __nv_bfloat16* __restrict_
 // out[n][OFF_j + p][r] = (add ? add(n, OFF_j + p, r) : 0) + sum_k Wm[j][r][k] * in(n, OFF_j + p, k)
 //   Wm : [4][512 rows][512] row-major (conv weights as stored -> forward; their transposes -> backward)
 //   in(n, pos, k) = in[n*in_ns + pos*in_ps + j*in_js + k]   (same addressing for `add`)
-// grid (8 row slabs of 64, 4 scales, N); 256 threads = 64 rows x 4 quarter-rows of 128 k.
+// grid (8 row slabs of 64 x 4 position groups, 4 scales, N); 256 threads = 64 rows x 4 quarter-rows of 128 k.
 template <int S2>
 __device__ __forceinline__ void ctx_gemv_body(const float* __restrict__ wrow, const float* s_in, float* __restrict__ o,
                                               const float* __restrict__ addp, long long in_ps, int q) {
@@ -520,26 +540,28 @@ __device__ __forceinline__ void ctx_gemv_body(const float* __restrict__ wrow, co
 __global__ void __launch_bounds__(256)
 ctx_pos_gemv_kernel(const float* __restrict__ Wm, const float* __restrict__ in, long long in_ns, long long in_ps,
                     long long in_js, const float* __restrict__ add, float* __restrict__ out) {
-  extern __shared__ float s_in[];  // [S*S][512]
+  extern __shared__ float s_in[];  // [positions of this CTA][512]
   const int SS[4] = {1, 2, 3, 6};
   const int OFF[4] = {0, 1, 5, 14};
   const int j = blockIdx.y, n = blockIdx.z;
-  const int S2 = SS[j] * SS[j];
-  const float* gin = in + n * in_ns + OFF[j] * in_ps + j * in_js;
-  for (int i = threadIdx.x; i < S2 * 128; i += blockDim.x) {
+  const int slab = blockIdx.x & 7, pg = blockIdx.x >> 3;   // the 36 positions of S=6 are cut into 4 groups of 9
+  if (j < 3 && pg > 0) return;
+  const int cnt = (j == 3) ? 9 : SS[j] * SS[j];
+  const int pos0 = OFF[j] + ((j == 3) ? pg * 9 : 0);
+  const float* gin = in + n * in_ns + pos0 * in_ps + j * in_js;
+  for (int i = threadIdx.x; i < cnt * 128; i += blockDim.x) {
     const int p = i >> 7, k4 = (i & 127) * 4;
     *reinterpret_cast<float4*>(s_in + p * 512 + k4) = *reinterpret_cast<const float4*>(gin + p * in_ps + k4);
   }
   __syncthreads();
-  const int row = blockIdx.x * 64 + (threadIdx.x >> 2);
+  const int row = slab * 64 + (threadIdx.x >> 2);
   const int q = threadIdx.x & 3;
   const float* wrow = Wm + (static_cast<long long>(j) * 512 + row) * 512;
-  float* o = out + (static_cast<long long>(n) * 50 + OFF[j]) * 512 + row;
-  const float* addp = add ? add + n * in_ns + OFF[j] * in_ps + j * in_js + row : nullptr;
+  float* o = out + (static_cast<long long>(n) * 50 + pos0) * 512 + row;
+  const float* addp = add ? add + n * in_ns + pos0 * in_ps + j * in_js + row : nullptr;
   if (j == 0) ctx_gemv_body<1>(wrow, s_in, o, addp, in_ps, q);
   else if (j == 1) ctx_gemv_body<4>(wrow, s_in, o, addp, in_ps, q);
-  else if (j == 2) ctx_gemv_body<9>(wrow, s_in, o, addp, in_ps, q);
-  else ctx_gemv_body<36>(wrow, s_in, o, addp, in_ps, q);
+  else ctx_gemv_body<9>(wrow, s_in, o, addp, in_ps, q);
 }
 
 // dW[j][r][c] (+)= alpha * sum_{n, p in scale j} A(n, OFF_j + p, r) * B[n][OFF_j + p][c]
@@ -604,6 +626,34 @@ ctx_wint_kernel(__nv_bfloat16* __restrict__ out, long long out_plane, int nsplit
       wv = wyv * wxv;
     }
     split_store(out + i, out_plane, nsplit, wv);
+  }
+}
+
+// Per-image B operands of the two extra k-blocks of MODE_CTX2 (K-major, 64 positions per row):
+//   T[0][n][(cc*4 + j)*64 + c][pos] = -tabB[n][pos][cc*64 + c]  if pos belongs to scale j, else 0
+//   T[1][n][(cc*4 + j)*64 + c][pos] =  tabA[n][pos][cc*64 + c]  if pos belongs to scale j, else 0
+// (positions 50..63 are zero).  512 KB per image.
+__global__ void __launch_bounds__(256)
+ctx_ttab_kernel(const float* __restrict__ tabA, const float* __restrict__ tabB, __nv_bfloat16* __restrict__ T, int N) {
+  const long long per = 2048LL * 64;
+  const long long total = 2LL * N * per;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int pos = i & 63;
+    const int row = (i >> 6) & 2047;
+    const int n = (i / per) % N;
+    const int which = i / (per * N);
+    const int c = row & 63, j = (row >> 6) & 3, cc = row >> 8;
+    float v = 0.f;
+    if (pos < 50) {
+      int pj, S, wy, wx, xwin;
+      ctx_pos_decode(pos, pj, S, wy, wx, xwin);
+      if (pj == j) {
+        const long long src = (static_cast<long long>(n) * 50 + pos) * 512 + cc * 64 + c;
+        v = which == 0 ? -tabB[src] : tabA[src];
+      }
+    }
+    T[i] = __float2bfloat16_rn(v);
   }
 }
 

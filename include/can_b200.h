@@ -37,7 +37,8 @@ enum {
   CAN_MODE_UNPOOL = 3, /* g = acc * (mask > 0) scattered to the argmax slot of the 2x map    */
   CAN_MODE_CTX = 4,    /* contextual fusion epilogue                                         */
   CAN_MODE_CTX_BWD = 5,/* backward of the fusion: writes dz_j and the direct ds_j (4096 channels)  */
-  CAN_MODE_DFV = 6     /* dfv = (add - acc + adaptive-pool^T spread) * (mask > 0)              */
+  CAN_MODE_DFV = 6,    /* dfv = (add - acc + adaptive-pool^T spread) * (mask > 0)              */
+  CAN_MODE_CTX2 = 7    /* CTX with the bilinear interpolation folded into the GEMM (bf16 path)   */
 };
 
 typedef struct can_conv_args {
@@ -73,6 +74,8 @@ typedef struct can_conv_args {
   float* head_out;       /* HEAD: [N][H][W] fp32 density                                      */
   const float* tabA;     /* CTX: [N][50][512] a_j = conv{S}_1(pool_S(fv))                     */
   const float* tabB;     /* CTX: [N][50][512] b_j = conv{S}_2(a_j)                            */
+  const void* ctx_wint;  /* CTX2: can_ctx_wint(nsplit 1, N 1) interpolation matrix [H][W][64] bf16 */
+  const void* ctx_ttab;  /* CTX2: can_ctx_ttab tables [2][N][2048][64] bf16                      */
 } can_conv_args;
 
 /* The dense contractions of the step on tcgen05/TMEM fed by TMA.
@@ -91,6 +94,10 @@ int can_conv_tc(const can_conv_args* args, void* stream);
  * Replaces cuDNN's internal filter transforms for nn.Conv2d (model/CANNet.py:114).          */
 int can_pack_conv_weight(const float* w, void* dst, int cout, int cin, int taps, int nsplit, int dgrad,
                          void* stream);
+/* Both packings in one pass over the fp32 weight (either destination may be NULL); the training
+ * step re-packs every weight after each optimizer update.                                        */
+int can_pack_conv_weight_both(const float* w, void* dst_fwd, void* dst_dgrad, int cout, int cin, int taps,
+                              int nsplit, void* stream);
 /* conv{1,2,3,6}_2.weight -> stacked [plane][2048][512] in (channel-chunk, scale, channel) row
  * order for CAN_MODE_CTX (model/CANNet.py:19,21,23,25).                                      */
 int can_pack_ctx_w2(const float* w1_2, const float* w2_2, const float* w3_2, const float* w6_2, void* dst,
@@ -178,6 +185,8 @@ int can_head_bwd(const float* dout, const void* y5, int64_t y_plane, int nsplit,
  * can_ctx_outer: dW[scale][r][c] (+)= alpha * sum_{n,pos in scale} A(n,pos,r) * B[n][pos][c]
  *   (weight gradients of conv{S}_1 and the pooled-position part of conv{S}_2).                  */
 int can_ctx_wint(void* out, int64_t out_plane, int nsplit, int N, int H, int W, void* stream);
+/* CTX2 operands: T[0][n][(cc*4+j)*64+c][pos] = -tabB[n][pos][cc*64+c], T[1] = +tabA (zero outside scale j). */
+int can_ctx_ttab(const float* tabA, const float* tabB, void* T, int N, void* stream);
 int can_ctx_pos_gemv(const float* Wm, const float* in, int64_t in_ns, int64_t in_ps, int64_t in_js,
                      const float* add, float* out, int N, void* stream);
 int can_ctx_outer(const float* A, int64_t a_ns, int64_t a_ps, int64_t a_js, const float* B, int N, float* dW,
