@@ -248,8 +248,8 @@ def main():
         step_resident()
     torch.cuda.synchronize()
     prof, ops.PROFILE = ops.PROFILE, None
-    k_ms = sum(a.elapsed_time(b) for a, b, _ in prof)
-    k_flop = sum(f for _, _, f in prof)
+    k_ms = sum(rec[0].elapsed_time(rec[1]) for rec in prof)
+    k_flop = sum(rec[2] for rec in prof)
     peak_tf, peak_hbm, peak_src = measured_peaks()
     achieved = (k_flop / 1e12) / (k_ms * 1e-3) if k_ms > 0 else 0.0
     roofline = {"bound": "tensor", "kernel": "conv_tc_kernel/wgrad_tc_kernel (tcgen05 implicit GEMM)",

@@ -18,7 +18,8 @@ import os
 import torch
 
 from . import ops
-from .ops import (MODE_CTX, MODE_CTX2, MODE_CTX_BWD, MODE_DFV, MODE_HEAD, MODE_POOL, MODE_STORE, MODE_UNPOOL, Act)
+from .ops import (MODE_CTX, MODE_CTX2, MODE_CTX2_BWD, MODE_CTX_BWD, MODE_DFV, MODE_HEAD, MODE_POOL, MODE_STORE,
+                  MODE_UNPOOL, Act)
 
 FRONTEND_CONVS = (0, 2, 5, 7, 10, 12, 14, 17, 19, 21)  # Sequential indices, CANNet.py:104-121
 POOLED_LAYERS = (1, 3, 6)                               # frontend convs followed by MaxPool2d(2,2)
@@ -117,8 +118,10 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
     if nsplit == 1 and os.environ.get("CAN_B200_CTX2", "1") != "0":
         # bf16 path: the bilinear interpolation of both tables is two extra k-blocks of the same GEMM
         wint1 = cache.get(("wint", 1, h, w), (), lambda: ops.ctx_wint(1, 1, h, w, dev))
-        ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX2, out=fi, ctx_wint=wint1.buf, ctx_ttab=ops.ctx_ttab(tabA, tabB))
+        ttab = ops.ctx_ttab(tabA, tabB)
+        ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX2, out=fi, ctx_wint=wint1.buf, ctx_ttab=ttab)
     else:
+        ttab = None
         ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX, out=fi, tabA=tabA, tabB=tabB)
 
     # ---- backend + head (CANNet.py:89-90) -----------------------------------------
@@ -141,7 +144,8 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
         a = out
         bacts.append(a)
     if save:
-        saved.update(acts=acts, args=args, cat=cat, bacts=bacts, pooled=pooled, tabA=tabA, tabB=tabB, nsplit=nsplit)
+        saved.update(acts=acts, args=args, cat=cat, bacts=bacts, pooled=pooled, tabA=tabA, tabB=tabB, ttab=ttab,
+                     nsplit=nsplit)
     return density, saved
 
 
@@ -197,8 +201,13 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
     w1t = cache.get(("w1t",), w1s, lambda: ops.transpose_stack(w1s))
     w2t = cache.get(("w2t",), w2s, lambda: ops.transpose_stack(w2s))
     D = ops.new_act(nsplit, N, h, w, 4096, dev)   # [dz_1..dz_6 | direct ds_1..ds_6], 512 channels each
-    ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX_BWD, out=D, mask=dcat.view(512, 512), tabA=saved["tabA"],
-                tabB=saved["tabB"])
+    if saved.get("ttab") is not None:
+        wint1 = cache.get(("wint", 1, h, w), (), lambda: ops.ctx_wint(1, 1, h, w, dev))
+        ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX2_BWD, out=D, mask=dcat.view(512, 512), ctx_wint=wint1.buf,
+                    ctx_ttab=saved["ttab"])
+    else:
+        ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX_BWD, out=D, mask=dcat.view(512, 512), tabA=saved["tabA"],
+                    tabB=saved["tabB"])
     wint = cache.get(("wint", nsplit, h, w), (), lambda: ops.ctx_wint(nsplit, 1, h, w, dev))
     T = torch.empty(N, 64, 4096, device=dev, dtype=torch.float32)   # U^T [dz | ds] per image
     for n in range(N):

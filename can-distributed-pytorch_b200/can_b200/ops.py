@@ -12,7 +12,7 @@ import torch
 
 from ._lib import ConvArgs, check, lib
 
-MODE_STORE, MODE_POOL, MODE_HEAD, MODE_UNPOOL, MODE_CTX, MODE_CTX_BWD, MODE_DFV, MODE_CTX2 = range(8)
+MODE_STORE, MODE_POOL, MODE_HEAD, MODE_UNPOOL, MODE_CTX, MODE_CTX_BWD, MODE_DFV, MODE_CTX2, MODE_CTX2_BWD = range(9)
 
 #: number of kernels of this library launched so far (bench.py reports the count per timed region)
 LAUNCHES = 0
@@ -26,8 +26,9 @@ def _count(n=1):
 
 
 class _Prof:
-    def __init__(self, flops):
+    def __init__(self, flops, label=""):
         self.flops = flops
+        self.label = label
 
     def __enter__(self):
         if PROFILE is not None:
@@ -38,7 +39,7 @@ class _Prof:
     def __exit__(self, *a):
         if PROFILE is not None:
             self.e1.record()
-            PROFILE.append((self.e0, self.e1, self.flops))
+            PROFILE.append((self.e0, self.e1, self.flops, self.label))
 
 
 def _stream() -> int:
@@ -192,7 +193,7 @@ def conv_tc(x: Act, wp: torch.Tensor, Cout: int, *, taps=9, dil=1, mode=MODE_STO
     a.tabA, a.tabB = _ptr(tabA), _ptr(tabB)
     a.ctx_wint, a.ctx_ttab = _ptr(ctx_wint), _ptr(ctx_ttab)
     _count()
-    with _Prof(2.0 * taps * x.C * Cout * x.N * x.H * x.W):
+    with _Prof(2.0 * taps * x.C * Cout * x.N * x.H * x.W, f"conv m{mode} {x.C}->{Cout} t{taps} d{dil} {x.H}x{x.W}"):
         check(lib().can_conv_tc(C.byref(a), _stream()), "conv_tc")
 
 
@@ -256,7 +257,7 @@ def conv_wgrad(dz: Act, x: Act, grad: torch.Tensor, *, taps=9, dil=1, accumulate
         _wgrad_ws[dev] = ws
     assert grad.is_contiguous() and grad.dtype == torch.float32 and grad.numel() == dz.C * x.C * taps
     _count(2)
-    with _Prof(2.0 * taps * x.C * dz.C * N * H * W):
+    with _Prof(2.0 * taps * x.C * dz.C * N * H * W, f"wgrad {x.C}->{dz.C} t{taps} d{dil} {H}x{W}"):
         check(lib().can_conv_wgrad(dz.buf.data_ptr(), dz.plane, dz.cs, dz.coff, x.buf.data_ptr(), x.plane, x.cs, x.coff,
                                    dz.nsplit, N, H, W, x.C, dz.C, taps, dil, grad.data_ptr(), int(accumulate),
                                    float(alpha), ws.data_ptr(), ws.numel(), _stream()), "conv_wgrad")

@@ -18,6 +18,7 @@ import torch.distributed as dist
 
 from .. import engine, ops
 from .distributed_utils import get_world_size, is_dist_avail_and_initialized, is_main_process, reduce_value
+from .dp import GradBuckets
 
 
 class FusedTrainer:
@@ -55,17 +56,12 @@ class FusedTrainer:
         # buckets in the order backward produces them: backend+head, ctx, frontend
         n_front = sum(p.numel() for p in params[:engine.IDX_BACKEND])
         n_back = sum(p.numel() for p in params[engine.IDX_BACKEND:engine.IDX_CTX])
-        self.buckets = {"backend": (n_front, n_front + n_back), "ctx": (n_front + n_back, total), "frontend": (0, n_front)}
+        self.buckets = GradBuckets(self.garena, {"backend": (n_front, n_front + n_back), "ctx": (n_front + n_back, total),
+                                                 "frontend": (0, n_front)}, group=process_group)
         self.first = True
-        self._works = []
         model._wcache.invalidate()
         if self.world > 1:  # identical initial weights on every rank (train.py:104-114 / DDP broadcast)
             dist.broadcast(self.arena, src=0, group=self.pg)
-
-    def _on_ready(self, tag):
-        if self.world > 1:
-            a, b = self.buckets[tag]
-            self._works.append(dist.all_reduce(self.garena[a:b], group=self.pg, async_op=True))
 
     def step(self, img: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
         """One training step; returns the rank-mean of the local sum-losses as a device tensor [1]."""
@@ -74,14 +70,12 @@ class FusedTrainer:
             self.garena[a:b].zero_()
         out, saved = engine.forward(m, img, m.nsplit, save=True)
         loss, _, _, grad = ops.mse_count(out, gt, want_grad=True)
-        self._works = []
-        engine.backward(m, saved, grad, grads=self.gviews, on_ready=self._on_ready)
+        engine.backward(m, saved, grad, grads=self.gviews, on_ready=self.buckets.ready)
         if self.world > 1:
-            self._works.append(dist.all_reduce(loss, group=self.pg, async_op=True))
-            for wk in self._works:
-                wk.wait()
+            self.buckets.reduce_scalar(loss)   # logged loss = rank-mean of the local sum-losses (reduce_value)
+            self.buckets.wait()
             loss = loss / self.world
-        ops.sgd_momentum_step(self.arena, self.garena, self.buf, self.lr, self.momentum, 1.0 / self.world,
+        ops.sgd_momentum_step(self.arena, self.garena, self.buf, self.lr, self.momentum, self.buckets.grad_scale,
                               first=self.first)
         self.first = False
         m._wcache.invalidate()  # the arena changed in place: packed weights must be rebuilt

@@ -112,7 +112,7 @@ int dispatch_mode(int mode, const CUtensorMap& a, const CUtensorMap& b, ConvTcPa
 
 
 struct WgradPlan {
-  int TW, TH, tiles_x, tiles_y, total_patches, m_tiles, n_tiles, bn, ksplit, per;
+  int TW, TH, tiles_x, tiles_y, total_patches, m_tiles, n_tiles, bn, ksplit, per, T, tap_groups;
 };
 WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nsplit) {
   WgradPlan pl;
@@ -124,23 +124,36 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   pl.m_tiles = (Cout + 127) / 128;
   pl.bn = Cin < 256 ? Cin : (nsplit > 1 ? 128 : 256);
   pl.n_tiles = Cin / pl.bn;
-  const int tiles = pl.m_tiles * pl.n_tiles * taps;
-  int ks = (2 * 148 + tiles - 1) / tiles;  // about two CTAs per SM in flight
-  if (ks > pl.total_patches) ks = pl.total_patches;
-  if (ks < 1) ks = 1;
+  // taps per CTA: as many TMEM accumulators as fit (bf16 path); the fp32-parity path keeps one
+  pl.T = (nsplit == 1 && taps > 1) ? 512 / pl.bn : 1;
+  if (pl.T > taps) pl.T = taps;
+  pl.tap_groups = (taps + pl.T - 1) / pl.T;
+  const int tiles = pl.m_tiles * pl.n_tiles * pl.tap_groups;
+  // split-K factor: fill the 148 SMs with whole waves (one CTA per SM), preferring fewer splits
+  int ks = 1;
+  double best = -1.0;
+  for (int c = 1; c <= 64 && c <= pl.total_patches; ++c) {
+    const int ctas = tiles * c;
+    const int waves = (ctas + 147) / 148;
+    const double eff = static_cast<double>(ctas) / (148.0 * waves) - 0.002 * c;
+    if (eff > best + 1e-9) {
+      best = eff;
+      ks = c;
+    }
+  }
   pl.per = (pl.total_patches + ks - 1) / ks;
   pl.ksplit = (pl.total_patches + pl.per - 1) / pl.per;  // every split non-empty
   return pl;
 }
 
-template <int BN, int NSPLIT>
+template <int BN, int NSPLIT, int T>
 int launch_wgrad(const CUtensorMap& tmDZ, const CUtensorMap& tmX, WgradTcParams& p, dim3 grid, cudaStream_t st) {
-  using L = WgradTcSmem<BN, NSPLIT>;
+  using L = WgradTcSmem<BN, NSPLIT, T>;
   int stages = (kMaxSmem - L::bytes(0)) / L::kStageBytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return fail(-20, "wgrad_tc: tile BN=%d nsplit=%d does not fit shared memory", BN, NSPLIT);
   p.stages = stages;
-  auto kern = wgrad_tc_kernel<BN, NSPLIT>;
+  auto kern = wgrad_tc_kernel<BN, NSPLIT, T>;
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
@@ -187,7 +200,8 @@ int can_version(void) { return 100; }
 int can_conv_tc(const can_conv_args* a, void* stream) {
   if (!a) return fail(-1, "conv_tc: null args");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const bool ctx = a->mode == CAN_MODE_CTX || a->mode == CAN_MODE_CTX_BWD || a->mode == CAN_MODE_CTX2;
+  const bool ctx2 = a->mode == CAN_MODE_CTX2 || a->mode == CAN_MODE_CTX2_BWD;
+  const bool ctx = a->mode == CAN_MODE_CTX || a->mode == CAN_MODE_CTX_BWD || ctx2;
   if (a->N <= 0 || a->H <= 0 || a->W <= 0) return fail(-2, "conv_tc: bad shape N=%d H=%d W=%d", a->N, a->H, a->W);
   if (a->Cin <= 0 || a->Cin % 64) return fail(-3, "conv_tc: Cin=%d must be a positive multiple of 64", a->Cin);
   if (a->taps != 1 && a->taps != 9) return fail(-4, "conv_tc: taps=%d (want 1 or 9)", a->taps);
@@ -202,13 +216,13 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   int bn = a->bn;
   if (ctx) {
     if (a->Cout != 2048 || a->Cin != 512 || a->taps != 1) return fail(-10, "conv_tc: CTX wants Cin=512 Cout=2048 taps=1");
-    if (a->mode == CAN_MODE_CTX2) {
+    if (ctx2) {
       if (a->nsplit != 1 || !a->ctx_wint || !a->ctx_ttab || !a->out)
         return fail(-10, "conv_tc: CTX2 is the bf16 path (nsplit 1) and needs ctx_wint, ctx_ttab and out");
     } else if (!a->tabA || !a->tabB || !a->out) {
       return fail(-10, "conv_tc: CTX needs tabA/tabB/out");
     }
-    if (a->mode == CAN_MODE_CTX_BWD && (!a->mask || a->out_cs != 4096))
+    if ((a->mode == CAN_MODE_CTX_BWD || a->mode == CAN_MODE_CTX2_BWD) && (!a->mask || a->out_cs != 4096))
       return fail(-10, "conv_tc: CTX_BWD needs the fi-gradient in `mask` and a 4096-channel output");
     bn = 256;
   } else if (a->mode == CAN_MODE_HEAD) {
@@ -227,7 +241,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   if (a->mode == CAN_MODE_UNPOOL && (!a->mask || !a->arg || a->OH < 2 * a->H || a->OW < 2 * a->W))
     return fail(-14, "conv_tc: UNPOOL needs mask, arg and OH>=2H, OW>=2W");
   if (a->mode == CAN_MODE_DFV && (!a->mask || !a->add || !a->tabA)) return fail(-14, "conv_tc: DFV needs mask, add and tabA");
-  if (a->mode < 0 || a->mode > CAN_MODE_CTX2) return fail(-15, "conv_tc: mode=%d", a->mode);
+  if (a->mode < 0 || a->mode > CAN_MODE_CTX2_BWD) return fail(-15, "conv_tc: mode=%d", a->mode);
 
   ConvTcParams p;
   memset(&p, 0, sizeof(p));
@@ -240,6 +254,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   p.tiles_x = (a->W + p.TW - 1) / p.TW;
   p.tiles_y = (a->H + p.TH - 1) / p.TH;
   p.relu = a->relu;
+  p.dbg = env_int("CAN_B200_DBG", 0);
   p.bias = a->bias;
   p.out = static_cast<__nv_bfloat16*>(a->out);
   p.out_plane = a->out_plane;
@@ -293,7 +308,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   const int ns = a->nsplit;
   g_tmW = nullptr;
   g_tmT = nullptr;
-  if (a->mode == CAN_MODE_CTX2) {
+  if (ctx2) {
     CUtensorMap tmW, tmT;
     int rc = make_act_tmap(&tmW, a->ctx_wint, 0, 64, 64, 0, 1, 1, a->H, a->W, p.TW, p.TH);
     if (rc) return rc;
@@ -305,7 +320,8 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     if (rc) return rc;
     g_tmW = &tmW;
     g_tmT = &tmT;
-    rc = launch_conv<256, 1, MODE_CTX2>(tmA, tmB, p, grid, so, st);
+    rc = a->mode == CAN_MODE_CTX2 ? launch_conv<256, 1, MODE_CTX2>(tmA, tmB, p, grid, so, st)
+                                  : launch_conv<256, 1, MODE_CTX2_BWD>(tmA, tmB, p, grid, so, st);
     g_tmW = nullptr;
     g_tmT = nullptr;
     return rc;
@@ -570,17 +586,23 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
   p.patches_per_split = pl.per; p.total_patches = pl.total_patches;
   p.m_groups = Cout >= 128 ? 2 : 1;
   p.ws = static_cast<float*>(ws);
-  dim3 grid(pl.m_tiles * pl.n_tiles * taps, pl.ksplit);
-  if (pl.bn == 64)
-    rc = nsplit == 1   ? launch_wgrad<64, 1>(tmDZ, tmX, p, grid, st)
-         : nsplit == 2 ? launch_wgrad<64, 2>(tmDZ, tmX, p, grid, st)
-                       : launch_wgrad<64, 3>(tmDZ, tmX, p, grid, st);
-  else if (pl.bn == 128)
-    rc = nsplit == 1   ? launch_wgrad<128, 1>(tmDZ, tmX, p, grid, st)
-         : nsplit == 2 ? launch_wgrad<128, 2>(tmDZ, tmX, p, grid, st)
-                       : launch_wgrad<128, 3>(tmDZ, tmX, p, grid, st);
-  else
-    rc = launch_wgrad<256, 1>(tmDZ, tmX, p, grid, st);
+  p.tap_groups = pl.tap_groups;
+  dim3 grid(pl.m_tiles * pl.n_tiles * pl.tap_groups, pl.ksplit);
+  if (pl.T > 1) {  // bf16 path, several taps per CTA
+    if (pl.bn == 64) rc = launch_wgrad<64, 1, 8>(tmDZ, tmX, p, grid, st);
+    else if (pl.bn == 128) rc = launch_wgrad<128, 1, 4>(tmDZ, tmX, p, grid, st);
+    else rc = launch_wgrad<256, 1, 2>(tmDZ, tmX, p, grid, st);
+  } else if (pl.bn == 64) {
+    rc = nsplit == 1   ? launch_wgrad<64, 1, 1>(tmDZ, tmX, p, grid, st)
+         : nsplit == 2 ? launch_wgrad<64, 2, 1>(tmDZ, tmX, p, grid, st)
+                       : launch_wgrad<64, 3, 1>(tmDZ, tmX, p, grid, st);
+  } else if (pl.bn == 128) {
+    rc = nsplit == 1   ? launch_wgrad<128, 1, 1>(tmDZ, tmX, p, grid, st)
+         : nsplit == 2 ? launch_wgrad<128, 2, 1>(tmDZ, tmX, p, grid, st)
+                       : launch_wgrad<128, 3, 1>(tmDZ, tmX, p, grid, st);
+  } else {
+    rc = launch_wgrad<256, 1, 1>(tmDZ, tmX, p, grid, st);
+  }
   if (rc) return rc;
   wgrad_reduce_kernel_v2<<<dim3(Cin / 32, Cout), 32 * taps, 0, st>>>(p.ws, grad, pl.ksplit, taps, Cout, Cin, accumulate,
                                                                      alpha);

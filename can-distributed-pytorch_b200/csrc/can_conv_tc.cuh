@@ -27,6 +27,7 @@ enum ConvMode : int {
   MODE_CTX_BWD = 5, // same GEMM recomputed; writes dz_j and the direct ds_j (backward of the fusion)
   MODE_DFV = 6,     // dfv = (add - acc + pooled-gradient spread) * (mask > 0)
   MODE_CTX2 = 7,    // contextual fusion with the bilinear interpolation folded into the GEMM (bf16 path)
+  MODE_CTX2_BWD = 8, // backward of the fusion on the same extended GEMM (bf16 path)
 };
 
 struct ConvTcParams {
@@ -39,6 +40,7 @@ struct ConvTcParams {
   int n_tiles;         // Cout / BN
   int num_tiles;       // tiles_x * tiles_y * N * n_tiles (persistent CTAs stride over them)
   int stages;
+  int dbg;             // CAN_B200_DBG bit flags (bring-up experiments only; 0 in production)
   int relu;
   const float* bias;   // [Cout] or null
   // primary output, NHWC bf16 planes
@@ -131,7 +133,7 @@ template <int BN, int GS>
 struct AccLayout {
   static constexpr int kNacc = (GS >= 2) ? (512 / BN - 1) : 1;   // hi*hi accumulators
   static constexpr int kCols = (GS >= 2) ? 512 : (BN < 32 ? 32 : BN);
-  static constexpr int cols(int mode) { return mode == MODE_CTX2 ? 512 : kCols; }
+  static constexpr int cols(int mode) { return (mode == MODE_CTX2 || mode == MODE_CTX2_BWD) ? 512 : kCols; }
   // two accumulator stages when they fit: the epilogue of tile i overlaps the MMAs of tile i+1
   static constexpr int acc_stages(int mode) { return cols(mode) * 2 <= 512 ? 2 : 1; }
 };
@@ -162,6 +164,20 @@ __device__ __forceinline__ void load_acc(uint32_t taddr, int col, int nact, floa
   }
 }
 
+// bf16-path transcendental helpers (one MUFU each): sigmoid(-a) = 0.5 - 0.5 tanh(a/2), 1/x.
+// The epilogue runs on four warps (one per scheduler), so every dependent multi-instruction IEEE
+// division costs its full latency; measured: 380 us of a 533 us kernel before this change.
+__device__ __forceinline__ float sigmoid_neg_fast(float a) {
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * a));
+  return fmaf(-0.5f, t, 0.5f);
+}
+__device__ __forceinline__ float rcp_fast(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
 template <int BN, int NSPLIT, int MODE>
 __global__ void __launch_bounds__(192, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -189,7 +205,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int base_kb = p.taps * p.kchunks;
   // MODE_CTX2: two extra k-blocks whose A operand is the interpolation matrix Wint[pixel][64 positions]
   // and whose B operands are the per-image tables (-U-side of z, then s) -- see the epilogue.
-  const int num_kb = base_kb + (MODE == MODE_CTX2 ? 2 : 0);
+  constexpr bool kCtx2 = (MODE == MODE_CTX2 || MODE == MODE_CTX2_BWD);
+  const int num_kb = base_kb + (kCtx2 ? 2 : 0);
   // Persistent CTA: tiles blockIdx.x, blockIdx.x + gridDim.x, ...; the n-tile index varies fastest so
   // that CTAs working at the same time share the activation patch in L2.
 #define CAN_TILE_DECODE(tile)                                   \
@@ -205,7 +222,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    if (MODE == MODE_CTX2) {
+    if (kCtx2) {
       tma_prefetch_desc(&tmW);
       tma_prefetch_desc(&tmT);
     }
@@ -250,7 +267,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           uint8_t* sa = smem + stage * L::kStageBytes;
           uint8_t* sb = sa + GS * L::kABytes;
           mbar_expect_tx(&full_bar[stage], L::kStageBytes);
-          if (MODE == MODE_CTX2 && kb >= base_kb) {
+          if (kCtx2 && kb >= base_kb) {
             tma_load_5d(sa, &tmW, &full_bar[stage], 0, x0, y0, 0, 0);
             tma_load_5d(sb, &tmT, &full_bar[stage], 0, n0, n_img, kb - base_kb, 0);
           } else {
@@ -293,7 +310,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for (int pb = 0; pb < GS; ++pb) {
               if (pa + pb < GS) {
                 // CTX2: the last k-block (Wint x a-table) goes to the second 256-column region (S)
-                const int acc = (MODE == MODE_CTX2) ? (kb == base_kb + 1 ? 1 : 0)
+                const int acc = kCtx2 ? (kb == base_kb + 1 ? 1 : 0)
                                 : (GS == 1)         ? 0
                                                     : ((pa + pb == 0) ? (kb % NACC) : NACC);
 #pragma unroll
@@ -564,13 +581,63 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           float num = 0.f, den = 0.f;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const float wgt = 1.f / (1.f + __expf(__uint_as_float(zr[j][c])));
+            const float wgt = sigmoid_neg_fast(__uint_as_float(zr[j][c]));
             num = fmaf(wgt, __uint_as_float(sr[j][c]), num);
             den += wgt;
           }
-          fi[c] = num / (den + 1e-12f);
+          fi[c] = num * rcp_fast(den + 1e-12f);
         }
         if (valid) store_bf16_planes<NSPLIT, 16>(obase + c0, p.out_plane, fi);
+      }
+    } else if (MODE == MODE_CTX2_BWD) {
+      // Same TMEM contents as MODE_CTX2 (-z_j | s_j).  With D = sum_j w_j + 1e-12 and g = dL/dfi:
+      //   ds_j (direct) = g w_j / D ;  dz_j = g (s_j - fi) / D * w_j (1 - w_j)
+      // out (cs = 4096): channel j*512 + c <- dz_j ; 2048 + j*512 + c <- ds_j.
+      const long long pix = valid ? (static_cast<long long>(n_img) * p.H + y) * p.W + x : 0;
+      __nv_bfloat16* obase = p.out + pix * p.out_cs + n_tile * 64;
+      const __nv_bfloat16* gbase = p.mask + pix * p.mask_cs + p.mask_coff + n_tile * 64;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 64; c0 += 8) {
+        uint32_t zr[4][8], sr[4][8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          tmem_ld_32x8(taddr + j * 64 + c0, zr[j]);
+          tmem_ld_32x8(taddr + 256 + j * 64 + c0, sr[j]);
+        }
+        tmem_ld_wait();
+        float g[8];
+        {
+          const uint4 gq = *reinterpret_cast<const uint4*>(gbase + c0);
+          const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(&gq);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) g[e] = valid ? __bfloat162float(gb[e]) : 0.f;
+        }
+        float dz[4][8], ds[4][8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          float wj[4], num = 0.f, den = 0.f;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            wj[j] = sigmoid_neg_fast(__uint_as_float(zr[j][c]));
+            num = fmaf(wj[j], __uint_as_float(sr[j][c]), num);
+            den += wj[j];
+          }
+          const float dinv = rcp_fast(den + 1e-12f);
+          const float fiv = num * dinv;
+          const float gd = g[c] * dinv;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            ds[j][c] = gd * wj[j];
+            dz[j][c] = gd * (__uint_as_float(sr[j][c]) - fiv) * wj[j] * (1.f - wj[j]);
+          }
+        }
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            store_bf16_planes<NSPLIT, 8>(obase + j * 512 + c0, p.out_plane, dz[j]);
+            store_bf16_planes<NSPLIT, 8>(obase + 2048 + j * 512 + c0, p.out_plane, ds[j]);
+          }
+        }
       }
     } else if (MODE == MODE_CTX_BWD) {
       // Backward of the fusion (CANNet.py:84) and of sigmoid(conv{S}_2(s_j - fv)) w.r.t. z_j.

@@ -6,9 +6,11 @@
 // as NHWC (channels contiguous), i.e. they are MN-major for this GEMM: a TMA box of
 // (64 channels x 64 pixels) lands as 64 rows of 128 B -- exactly the 128B-swizzled MN-major
 // canonical layout (8-pixel groups 1024 B apart = SBO, 64-channel groups one box apart = LBO).
-// One CTA owns (cout tile, cin tile, tap) and a contiguous slice of the pixel patches
-// (split-K); it writes an fp32 partial tile to the workspace, reduced deterministically by
-// wgrad_reduce_kernel.
+// One CTA owns (cout tile, cin tile, group of T taps) and a contiguous slice of the pixel
+// patches (split-K).  The dZ patch is loaded once per stage and multiplied with the T shifted X
+// patches into T TMEM accumulators, so dZ streams from HBM once per tap GROUP instead of once per
+// tap (the large-spatial layers are HBM-bound otherwise).  Partial tiles go to an fp32 workspace,
+// reduced deterministically by wgrad_reduce_kernel_v2.
 #pragma once
 #include "can_ptx.cuh"
 
@@ -25,23 +27,26 @@ struct WgradTcParams {
   int total_patches;
   int stages;
   int m_groups;  // 64-channel groups of dZ actually loaded (1 when Cout == 64)
+  int tap_groups;  // ceil(taps / T)
   float* ws;     // [split][tap][Cout][Cin]
 };
 
-template <int BN, int NSPLIT>
+template <int BN, int NSPLIT, int T>
 struct WgradTcSmem {
   static constexpr int kGroupBytes = 64 * 128;            // 64 pixels x 64 ch x bf16
   static constexpr int kABytes = 2 * kGroupBytes;         // 128 cout
-  static constexpr int kBBytes = (BN / 64) * kGroupBytes;
-  static constexpr int kStageBytes = NSPLIT * (kABytes + kBBytes);
+  static constexpr int kBBytes = (BN / 64) * kGroupBytes; // one tap
+  static constexpr int kStageBytes = NSPLIT * (kABytes + T * kBBytes);
+  static constexpr int kTmemCols = (T * BN <= 32) ? 32 : (T * BN <= 64) ? 64 : (T * BN <= 128) ? 128 : (T * BN <= 256) ? 256 : 512;
   static __host__ __device__ constexpr int bytes(int stages) { return 1024 + stages * kStageBytes + 1024; }
 };
 
-template <int BN, int NSPLIT>
+template <int BN, int NSPLIT, int T>
 __global__ void __launch_bounds__(192, 1)
 wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant__ CUtensorMap tmX,
                 const WgradTcParams p) {
-  using L = WgradTcSmem<BN, NSPLIT>;
+  using L = WgradTcSmem<BN, NSPLIT, T>;
+  static_assert(T * BN <= 512, "accumulators of one tap group must fit TMEM");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int stages = p.stages;
@@ -58,17 +63,13 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
   const int n_tile = t % p.n_tiles;
   t /= p.n_tiles;
   const int m_tile = t % p.m_tiles;
-  const int tap = t / p.m_tiles;
+  const int tap0 = (t / p.m_tiles) * T;               // first tap of this CTA's group
+  const int ntaps = min(T, p.taps - tap0);
   const int split = blockIdx.y;
   const int patch_begin = split * p.patches_per_split;
   const int patch_end = min(patch_begin + p.patches_per_split, p.total_patches);
-  int dy = 0, dx = 0;
-  if (p.taps == 9) {
-    dy = (tap / 3 - 1) * p.dil;
-    dx = (tap % 3 - 1) * p.dil;
-  }
   const int m_groups = p.m_groups;  // 1 or 2
-  const uint32_t stage_tx = NSPLIT * (m_groups * L::kGroupBytes + L::kBBytes);
+  const uint32_t stage_tx = NSPLIT * (m_groups * L::kGroupBytes + ntaps * L::kBBytes);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmDZ);
@@ -84,7 +85,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
       fence_mbar_init();
     }
     __syncwarp();
-    tmem_alloc(tmem_ptr_smem, BN < 32 ? 32 : BN);
+    tmem_alloc(tmem_ptr_smem, L::kTmemCols);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -105,17 +106,25 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
         const int x0 = tx_i * p.TW, y0 = ty_i * p.TH;
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem + stage * L::kStageBytes;
-        uint8_t* sb = sa + NSPLIT * L::kABytes;
+        uint8_t* sb = sa + NSPLIT * L::kABytes;  // [plane][tap][BN/64 groups]
         mbar_expect_tx(&full_bar[stage], stage_tx);
 #pragma unroll
         for (int pl = 0; pl < NSPLIT; ++pl) {
           for (int g = 0; g < m_groups; ++g)
             tma_load_5d(sa + pl * L::kABytes + g * L::kGroupBytes, &tmDZ, &full_bar[stage],
                         m_tile * 128 + g * 64, x0, y0, n_img, pl);
+          for (int tt = 0; tt < ntaps; ++tt) {
+            const int tap = tap0 + tt;
+            int dy = 0, dx = 0;
+            if (p.taps == 9) {
+              dy = (tap / 3 - 1) * p.dil;
+              dx = (tap % 3 - 1) * p.dil;
+            }
 #pragma unroll
-          for (int g = 0; g < BN / 64; ++g)
-            tma_load_5d(sb + pl * L::kBBytes + g * L::kGroupBytes, &tmX, &full_bar[stage], n_tile * BN + g * 64,
-                        x0 + dx, y0 + dy, n_img, pl);
+            for (int g = 0; g < BN / 64; ++g)
+              tma_load_5d(sb + (pl * T + tt) * L::kBBytes + g * L::kGroupBytes, &tmX, &full_bar[stage],
+                          n_tile * BN + g * 64, x0 + dx, y0 + dy, n_img, pl);
+          }
         }
         if (++stage == stages) {
           stage = 0;
@@ -134,21 +143,24 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
         const uint32_t sb = sa + NSPLIT * L::kABytes;
+        for (int tt = 0; tt < ntaps; ++tt) {
 #pragma unroll
-        for (int pa = 0; pa < NSPLIT; ++pa) {
+          for (int pa = 0; pa < NSPLIT; ++pa) {
 #pragma unroll
-          for (int pb = 0; pb < NSPLIT; ++pb) {
-            if (pa + pb < NSPLIT) {
+            for (int pb = 0; pb < NSPLIT; ++pb) {
+              if (pa + pb < NSPLIT) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {  // 16 pixels (= 2 swizzle atoms of 8 rows) per MMA
-                const uint64_t da = umma_smem_desc(sa + pa * L::kABytes + k * 2048, L::kGroupBytes, 1024);
-                const uint64_t db = umma_smem_desc(sb + pb * L::kBBytes + k * 2048, L::kGroupBytes, 1024);
-                umma_bf16(tmem_base, da, db, idesc, accum);
-                accum = 1;
+                for (int k = 0; k < 4; ++k) {  // 16 pixels (= 2 swizzle atoms of 8 rows) per MMA
+                  const uint64_t da = umma_smem_desc(sa + pa * L::kABytes + k * 2048, L::kGroupBytes, 1024);
+                  const uint64_t db =
+                      umma_smem_desc(sb + (pb * T + tt) * L::kBBytes + k * 2048, L::kGroupBytes, 1024);
+                  umma_bf16(tmem_base + tt * BN, da, db, idesc, (accum | (pa + pb) | k) ? 1u : 0u);
+                }
               }
             }
           }
         }
+        accum = 1;
         umma_commit(&empty_bar[stage]);
         if (++stage == stages) {
           stage = 0;
@@ -163,18 +175,21 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
-    float* dst = p.ws + ((static_cast<long long>(split) * p.taps + tap) * p.Cout + co) * p.Cin + n_tile * BN;
     const bool valid = (co < p.Cout) && (patch_end > patch_begin);
+    for (int tt = 0; tt < ntaps; ++tt) {
+      float* dst =
+          p.ws + ((static_cast<long long>(split) * p.taps + tap0 + tt) * p.Cout + co) * p.Cin + n_tile * BN;
 #pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
-      uint32_t r[32];
-      tmem_ld_32x32(taddr + c0, r);
-      tmem_ld_wait();
-      if (valid) {
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + tt * BN + c0, r);
+        tmem_ld_wait();
+        if (valid) {
 #pragma unroll
-        for (int i = 0; i < 32; i += 4)
-          *reinterpret_cast<float4*>(dst + c0 + i) = make_float4(__uint_as_float(r[i]), __uint_as_float(r[i + 1]),
-                                                                 __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+          for (int i = 0; i < 32; i += 4)
+            *reinterpret_cast<float4*>(dst + c0 + i) = make_float4(__uint_as_float(r[i]), __uint_as_float(r[i + 1]),
+                                                                   __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+        }
       }
     }
     tc_fence_before();
@@ -182,7 +197,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, BN < 32 ? 32 : BN);
+    tmem_dealloc(tmem_base, L::kTmemCols);
   }
 }
 

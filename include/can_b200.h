@@ -38,7 +38,8 @@ enum {
   CAN_MODE_CTX = 4,    /* contextual fusion epilogue                                         */
   CAN_MODE_CTX_BWD = 5,/* backward of the fusion: writes dz_j and the direct ds_j (4096 channels)  */
   CAN_MODE_DFV = 6,    /* dfv = (add - acc + adaptive-pool^T spread) * (mask > 0)              */
-  CAN_MODE_CTX2 = 7    /* CTX with the bilinear interpolation folded into the GEMM (bf16 path)   */
+  CAN_MODE_CTX2 = 7,   /* CTX with the bilinear interpolation folded into the GEMM (bf16 path)   */
+  CAN_MODE_CTX2_BWD = 8/* CTX_BWD on the same extended GEMM (bf16 path)                          */
 };
 
 typedef struct can_conv_args {
