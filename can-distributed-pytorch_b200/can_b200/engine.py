@@ -80,7 +80,16 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
 
     # ---- frontend (CANNet.py:40) -------------------------------------------------
     w0, b0 = fr[0]
-    a = ops.conv_first(x, w0.detach().float().contiguous(), b0.detach().float().contiguous(), nsplit)
+    col = None
+    if nsplit == 1 and os.environ.get("CAN_B200_FIRST_TC", "1") != "0":
+        # bf16 path: K = 27 padded to 64 through an im2col of the image turns conv1_1 into a 1x1 GEMM on
+        # the tensor cores; the im2col buffer is reused by the weight gradient in backward
+        col = ops.im2col_first(x, 1)
+        w0p = cache.get(("f0", 1), (w0,), lambda: ops.pack_first_weight(w0))
+        a = ops.new_act(1, N, H, W, 64, dev)
+        ops.conv_tc(col, w0p, 64, taps=1, mode=MODE_STORE, relu=True, bias=b0.detach().float(), out=a)
+    else:
+        a = ops.conv_first(x, w0.detach().float().contiguous(), b0.detach().float().contiguous(), nsplit)
     acts = [a]
     args = {}
     h, w = H, W
@@ -144,7 +153,7 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
         a = out
         bacts.append(a)
     if save:
-        saved.update(acts=acts, args=args, cat=cat, bacts=bacts, pooled=pooled, tabA=tabA, tabB=tabB, ttab=ttab,
+        saved.update(acts=acts, args=args, cat=cat, bacts=bacts, pooled=pooled, tabA=tabA, tabB=tabB, ttab=ttab, col=col,
                      nsplit=nsplit)
     return density, saved
 
@@ -250,7 +259,9 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
             ops.conv_tc(dz, wd, cin, mode=MODE_STORE, relu=False, out=ndz, mask=X)
         dz = ndz
     # first conv (3 -> 64): K = 27 padded to 64 through an im2col of the image
-    col = ops.im2col_first(saved["x"], nsplit)
+    col = saved.get("col")
+    if col is None:
+        col = ops.im2col_first(saved["x"], nsplit)
     g0 = torch.empty(64, 64, device=dev, dtype=torch.float32)
     ops.conv_wgrad(dz, col, g0, taps=1)
     grads[0].copy_(g0[:, :27].reshape(64, 3, 3, 3))

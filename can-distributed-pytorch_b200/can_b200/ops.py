@@ -123,6 +123,13 @@ def pack_conv_weight(w: torch.Tensor, nsplit: int, dgrad: bool = False) -> torch
     return dst
 
 
+def pack_first_weight(w: torch.Tensor) -> torch.Tensor:
+    """frontend.0 weight [64,3,3,3] as a K-major [64][64] bf16 matrix (k = ci*9 + tap, zero-padded from 27)."""
+    wp = torch.zeros(64, 64, 1, 1, device=w.device, dtype=torch.float32)
+    wp[:, :27, 0, 0] = w.detach().float().reshape(64, 27)
+    return pack_conv_weight(wp, 1)
+
+
 def pack_conv_weight_both(w: torch.Tensor, nsplit: int):
     """(fwd pack, dgrad pack) of one OIHW fp32 weight in a single pass over it."""
     co, ci, kh, kw = w.shape

@@ -66,8 +66,7 @@ class FusedTrainer:
     def step(self, img: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
         """One training step; returns the rank-mean of the local sum-losses as a device tensor [1]."""
         m = self.model
-        for a, b in self.zero_ranges:
-            self.garena[a:b].zero_()
+        self.garena.zero_()  # bias / head gradients are accumulated with atomics (one 83 MB memset, ~13 us)
         out, saved = engine.forward(m, img, m.nsplit, save=True)
         loss, _, _, grad = ops.mse_count(out, gt, want_grad=True)
         engine.backward(m, saved, grad, grads=self.gviews, on_ready=self.buckets.ready)

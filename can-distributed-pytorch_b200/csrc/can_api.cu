@@ -132,7 +132,7 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   // split-K factor: fill the 148 SMs with whole waves (one CTA per SM), preferring fewer splits
   int ks = 1;
   double best = -1.0;
-  for (int c = 1; c <= 64 && c <= pl.total_patches; ++c) {
+  for (int c = 1; c <= 160 && c <= pl.total_patches; ++c) {
     const int ctas = tiles * c;
     const int waves = (ctas + 147) / 148;
     const double eff = static_cast<double>(ctas) / (148.0 * waves) - 0.002 * c;
@@ -612,8 +612,13 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
 
 int can_im2col_first(const float* x_nchw, void* out, int64_t out_plane, int nsplit, int N, int H, int W, void* stream) {
   if (!x_nchw || !out || N <= 0 || H <= 0 || W <= 0 || nsplit < 1 || nsplit > 3) return fail(-1, "im2col_first: bad arguments");
-  im2col_first_kernel<<<148 * 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(x_nchw, static_cast<__nv_bfloat16*>(out),
-                                                                             out_plane, nsplit, N, H, W);
+  if (H <= 65535 && N <= 65535) {
+    im2col_first_kernel_v2<<<dim3((W + 127) / 128, H, N), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        x_nchw, static_cast<__nv_bfloat16*>(out), out_plane, nsplit, N, H, W);
+  } else {
+    im2col_first_kernel<<<148 * 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        x_nchw, static_cast<__nv_bfloat16*>(out), out_plane, nsplit, N, H, W);
+  }
   CAN_CHECK_LAUNCH("im2col_first");
   return 0;
 }

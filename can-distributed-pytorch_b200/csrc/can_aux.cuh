@@ -126,4 +126,53 @@ pack_conv_weight_kernel_v2(const float* __restrict__ w, __nv_bfloat16* __restric
   }
 }
 
+// im2col of the 3-channel image (second generation): out[pl][n][y][x][k], k = ci*9 + r*3 + s for
+// k < 27, zero for 27 <= k < 64.  One block = one image row segment of 128 pixels: the 3 x 3 x 130
+// input window is staged in shared memory with coalesced loads; eight threads cooperate on one
+// pixel so that every warp store covers 512 contiguous bytes.
+__global__ void __launch_bounds__(256)
+im2col_first_kernel_v2(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, long long out_plane, int nsplit,
+                       int N, int H, int W) {
+  __shared__ float s_in[3][3][132];
+  const int x0 = blockIdx.x * 128, y = blockIdx.y, n = blockIdx.z;
+  for (int i = threadIdx.x; i < 9 * 130; i += 256) {
+    const int c = i % 130, rr = (i / 130) % 3, ci = i / 390;
+    const int yy = y + rr - 1, xx = x0 + c - 1;
+    s_in[ci][rr][c] = (yy >= 0 && yy < H && xx >= 0 && xx < W)
+                          ? __ldg(x + ((static_cast<long long>(n) * 3 + ci) * H + yy) * W + xx)
+                          : 0.f;
+  }
+  __syncthreads();
+  const int kg = threadIdx.x & 7;
+#pragma unroll 1
+  for (int pp = threadIdx.x >> 3; pp < 128; pp += 32) {
+    const int xq = x0 + pp;
+    if (xq >= W) break;
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int k = kg * 8 + e;
+      float val = 0.f;
+      if (k < 27) {
+        const int ci = k / 9, r = (k % 9) / 3, sx = k % 3;
+        val = s_in[ci][r][pp + sx];
+      }
+      v[e] = val;
+    }
+    __nv_bfloat16* o = out + ((static_cast<long long>(n) * H + y) * W + xq) * 64 + kg * 8;
+    for (int pl = 0; pl < nsplit; ++pl) {
+      uint4 q;
+      q.x = pack_bf16x2(v[0], v[1]);
+      q.y = pack_bf16x2(v[2], v[3]);
+      q.z = pack_bf16x2(v[4], v[5]);
+      q.w = pack_bf16x2(v[6], v[7]);
+      *reinterpret_cast<uint4*>(o + pl * out_plane) = q;
+      if (pl + 1 < nsplit) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] -= bf16_round(v[e]);
+      }
+    }
+  }
+}
+
 }  // namespace canb

@@ -510,30 +510,52 @@ head_bwd_kernel(const float* __restrict__ dout, const __nv_bfloat16* __restrict_
 //   Wm : [4][512 rows][512] row-major (conv weights as stored -> forward; their transposes -> backward)
 //   in(n, pos, k) = in[n*in_ns + pos*in_ps + j*in_js + k]   (same addressing for `add`)
 // grid (8 row slabs of 64 x 4 position groups, 4 scales, N); 256 threads = 64 rows x 4 quarter-rows of 128 k.
+// One warp per output row: lane l owns k = 4l + 128 i (i < 4) -> every weight load is one coalesced
+// 512-byte request and every shared-memory read is conflict-free; the S2 partial sums are combined
+// with shuffles.  Two rows per warp iteration for instruction-level parallelism.
 template <int S2>
-__device__ __forceinline__ void ctx_gemv_body(const float* __restrict__ wrow, const float* s_in, float* __restrict__ o,
-                                              const float* __restrict__ addp, long long in_ps, int q) {
-  float acc[S2];
+__device__ __forceinline__ void ctx_gemv_rows(const float* __restrict__ wbase, const float* s_in,
+                                              float* __restrict__ obase, const float* __restrict__ addbase,
+                                              long long in_ps, int row0, int nrows, int lane) {
+  for (int r = 0; r < nrows; r += 2) {
+    const float* w0 = wbase + static_cast<long long>(row0 + r) * 512 + lane * 4;
+    const float* w1 = w0 + 512;
+    float4 wa[4], wb[4];
 #pragma unroll
-  for (int p = 0; p < S2; ++p) acc[p] = 0.f;
-#pragma unroll 4
-  for (int i = 0; i < 32; ++i) {
-    const float4 w4 = __ldg(reinterpret_cast<const float4*>(wrow + q * 128 + i * 4));
+    for (int i = 0; i < 4; ++i) {
+      wa[i] = __ldg(reinterpret_cast<const float4*>(w0 + i * 128));
+      wb[i] = __ldg(reinterpret_cast<const float4*>(w1 + i * 128));
+    }
+    float acc0[S2], acc1[S2];
 #pragma unroll
     for (int p = 0; p < S2; ++p) {
-      const float4 x4 = *reinterpret_cast<const float4*>(s_in + p * 512 + q * 128 + i * 4);
-      acc[p] = fmaf(w4.x, x4.x, acc[p]);
-      acc[p] = fmaf(w4.y, x4.y, acc[p]);
-      acc[p] = fmaf(w4.z, x4.z, acc[p]);
-      acc[p] = fmaf(w4.w, x4.w, acc[p]);
-    }
-  }
+      float a0 = 0.f, a1 = 0.f;
 #pragma unroll
-  for (int p = 0; p < S2; ++p) {
-    float v = acc[p];
-    v += __shfl_xor_sync(0xffffffffu, v, 1);
-    v += __shfl_xor_sync(0xffffffffu, v, 2);
-    if (q == 0) o[p * 512] = v + (addp ? addp[p * in_ps] : 0.f);
+      for (int i = 0; i < 4; ++i) {
+        const float4 x4 = *reinterpret_cast<const float4*>(s_in + p * 512 + i * 128 + lane * 4);
+        a0 = fmaf(wa[i].x, x4.x, a0); a0 = fmaf(wa[i].y, x4.y, a0);
+        a0 = fmaf(wa[i].z, x4.z, a0); a0 = fmaf(wa[i].w, x4.w, a0);
+        a1 = fmaf(wb[i].x, x4.x, a1); a1 = fmaf(wb[i].y, x4.y, a1);
+        a1 = fmaf(wb[i].z, x4.z, a1); a1 = fmaf(wb[i].w, x4.w, a1);
+      }
+      acc0[p] = a0;
+      acc1[p] = a1;
+    }
+#pragma unroll
+    for (int p = 0; p < S2; ++p) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        acc0[p] += __shfl_xor_sync(0xffffffffu, acc0[p], o);
+        acc1[p] += __shfl_xor_sync(0xffffffffu, acc1[p], o);
+      }
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int p = 0; p < S2; ++p) {
+        obase[p * 512 + row0 + r] = acc0[p] + (addbase ? addbase[p * in_ps + row0 + r] : 0.f);
+        obase[p * 512 + row0 + r + 1] = acc1[p] + (addbase ? addbase[p * in_ps + row0 + r + 1] : 0.f);
+      }
+    }
   }
 }
 
@@ -554,14 +576,14 @@ ctx_pos_gemv_kernel(const float* __restrict__ Wm, const float* __restrict__ in, 
     *reinterpret_cast<float4*>(s_in + p * 512 + k4) = *reinterpret_cast<const float4*>(gin + p * in_ps + k4);
   }
   __syncthreads();
-  const int row = slab * 64 + (threadIdx.x >> 2);
-  const int q = threadIdx.x & 3;
-  const float* wrow = Wm + (static_cast<long long>(j) * 512 + row) * 512;
-  float* o = out + (static_cast<long long>(n) * 50 + pos0) * 512 + row;
-  const float* addp = add ? add + n * in_ns + pos0 * in_ps + j * in_js + row : nullptr;
-  if (j == 0) ctx_gemv_body<1>(wrow, s_in, o, addp, in_ps, q);
-  else if (j == 1) ctx_gemv_body<4>(wrow, s_in, o, addp, in_ps, q);
-  else ctx_gemv_body<9>(wrow, s_in, o, addp, in_ps, q);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int row0 = slab * 64 + wid * 8;  // 8 rows per warp
+  const float* wbase = Wm + static_cast<long long>(j) * 512 * 512;
+  float* obase = out + (static_cast<long long>(n) * 50 + pos0) * 512;
+  const float* addbase = add ? add + n * in_ns + pos0 * in_ps + j * in_js : nullptr;
+  if (j == 0) ctx_gemv_rows<1>(wbase, s_in, obase, addbase, in_ps, row0, 8, lane);
+  else if (j == 1) ctx_gemv_rows<4>(wbase, s_in, obase, addbase, in_ps, row0, 8, lane);
+  else ctx_gemv_rows<9>(wbase, s_in, obase, addbase, in_ps, row0, 8, lane);
 }
 
 // dW[j][r][c] (+)= alpha * sum_{n, p in scale j} A(n, OFF_j + p, r) * B[n][OFF_j + p][c]
@@ -570,6 +592,7 @@ ctx_pos_gemv_kernel(const float* __restrict__ Wm, const float* __restrict__ in, 
 __global__ void __launch_bounds__(256)
 ctx_outer_kernel(const float* __restrict__ A, long long a_ns, long long a_ps, long long a_js,
                  const float* __restrict__ B, int N, float* __restrict__ dW, float alpha, int accumulate) {
+  __shared__ float s_a[36][16];
   const int SS[4] = {1, 2, 3, 6};
   const int OFF[4] = {0, 1, 5, 14};
   const int j = blockIdx.y;
@@ -580,15 +603,28 @@ ctx_outer_kernel(const float* __restrict__ A, long long a_ns, long long a_ps, lo
 #pragma unroll
   for (int r = 0; r < 16; ++r) acc0[r] = acc1[r] = 0.f;
   for (int n = 0; n < N; ++n) {
-    for (int p = 0; p < S2; ++p) {
-      const float* ap = A + n * a_ns + (OFF[j] + p) * a_ps + j * a_js + r0;
-      const float* bp = B + (static_cast<long long>(n) * 50 + OFF[j] + p) * 512;
-      const float b0 = bp[c], b1 = bp[c + 256];
+    __syncthreads();
+    for (int i = threadIdx.x; i < S2 * 16; i += 256)
+      s_a[i >> 4][i & 15] = A[n * a_ns + (OFF[j] + (i >> 4)) * a_ps + j * a_js + r0 + (i & 15)];
+    __syncthreads();
+    const float* bp = B + (static_cast<long long>(n) * 50 + OFF[j]) * 512;
+    for (int p = 0; p < S2; p += 4) {
+      float b0[4], b1[4];
 #pragma unroll
-      for (int r = 0; r < 16; ++r) {
-        const float a = __ldg(ap + r);
-        acc0[r] = fmaf(a, b0, acc0[r]);
-        acc1[r] = fmaf(a, b1, acc1[r]);
+      for (int u = 0; u < 4; ++u) {  // four positions of loads in flight
+        const bool on = (p + u) < S2;
+        b0[u] = on ? bp[(p + u) * 512 + c] : 0.f;
+        b1[u] = on ? bp[(p + u) * 512 + c + 256] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int pp = min(p + u, S2 - 1);
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+          const float a = s_a[pp][r];
+          acc0[r] = fmaf(a, b0[u], acc0[r]);
+          acc1[r] = fmaf(a, b1[u], acc1[r]);
+        }
       }
     }
   }
