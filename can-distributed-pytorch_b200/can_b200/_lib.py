@@ -32,6 +32,7 @@ class ConvArgs(C.Structure):
         ("head_w", C.c_void_p), ("head_b", C.c_void_p), ("head_out", C.c_void_p),
         ("tabA", C.c_void_p), ("tabB", C.c_void_p),
         ("ctx_wint", C.c_void_p), ("ctx_ttab", C.c_void_p),
+        ("db", C.c_void_p),
     ]
 
 

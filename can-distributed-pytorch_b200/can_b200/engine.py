@@ -191,11 +191,14 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
         cin = wt.shape[1]
         X = bacts[li]
         ops.conv_wgrad(dz, X, grads[IDX_BACKEND + 2 * li], dil=2)
-        ops.bias_grad(dz, grads[IDX_BACKEND + 2 * li + 1])
+        if li == 5:
+            ops.bias_grad(dz, grads[IDX_BACKEND + 2 * li + 1])   # dz of the last conv comes from head_bwd
         wd = _packed(cache, "b", li, wt, nsplit, True)[1]
         ndz = ops.new_act(nsplit, N, h, w, cin, dev)
         if li > 0:
-            ops.conv_tc(dz, wd, cin, dil=2, mode=MODE_STORE, relu=False, out=ndz, mask=X)
+            # the dgrad epilogue also accumulates the bias gradient of the layer whose dZ it writes
+            ops.conv_tc(dz, wd, cin, dil=2, mode=MODE_STORE, relu=False, out=ndz, mask=X,
+                        db=grads[IDX_BACKEND + 2 * (li - 1) + 1])
             dz = ndz
         else:
             ops.conv_tc(dz, wd, cin, dil=2, mode=MODE_STORE, relu=False, out=ndz)
@@ -237,7 +240,7 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
         torch.cat([wj.detach().float().reshape(512, 512).t() for wj in w2s], dim=1).reshape(512, 2048, 1, 1), nsplit))
     dz = ops.new_act(nsplit, N, h, w, 512, dev)
     ops.conv_tc(D.view(2048, 0), w2d, 512, taps=1, mode=MODE_DFV, relu=False, out=dz, mask=fv, add=dcat.view(512, 0),
-                tabA=dpool)
+                tabA=dpool, db=grads[2 * 9 + 1])
     if on_ready:
         on_ready("ctx")
 
@@ -247,16 +250,17 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
         cin = wt.shape[1]
         X = acts[li - 1]
         ops.conv_wgrad(dz, X, grads[2 * li], dil=1)
-        ops.bias_grad(dz, grads[2 * li + 1])
         wd = _packed(cache, "f", li, wt, nsplit, True)[1]
+        dbp = grads[2 * (li - 1) + 1]   # bias gradient of layer li-1, fused into the dgrad epilogue below
         if (li - 1) in POOLED_LAYERS:
             pre = acts[li - 2]  # the pooled layer's input has its pre-pool resolution
             OH, OW = pre.H, pre.W
             ndz = ops.new_act(nsplit, N, OH, OW, cin, dev, zero=bool((OH | OW) & 1))
-            ops.conv_tc(dz, wd, cin, mode=MODE_UNPOOL, relu=False, out=ndz, mask=X, arg=args[li - 1], OH=OH, OW=OW)
+            ops.conv_tc(dz, wd, cin, mode=MODE_UNPOOL, relu=False, out=ndz, mask=X, arg=args[li - 1], OH=OH, OW=OW,
+                        db=dbp)
         else:
             ndz = ops.new_act(nsplit, N, X.H, X.W, cin, dev)
-            ops.conv_tc(dz, wd, cin, mode=MODE_STORE, relu=False, out=ndz, mask=X)
+            ops.conv_tc(dz, wd, cin, mode=MODE_STORE, relu=False, out=ndz, mask=X, db=dbp)
         dz = ndz
     # first conv (3 -> 64): K = 27 padded to 64 through an im2col of the image
     col = saved.get("col")
@@ -264,8 +268,7 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
         col = ops.im2col_first(saved["x"], nsplit)
     g0 = torch.empty(64, 64, device=dev, dtype=torch.float32)
     ops.conv_wgrad(dz, col, g0, taps=1)
-    grads[0].copy_(g0[:, :27].reshape(64, 3, 3, 3))
-    ops.bias_grad(dz, grads[1])
+    grads[0].copy_(g0[:, :27].reshape(64, 3, 3, 3))   # bias gradient of conv1_1 was fused into conv1_2's dgrad
     if on_ready:
         on_ready("frontend")
     return grads

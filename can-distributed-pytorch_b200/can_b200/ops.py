@@ -178,7 +178,7 @@ def conv_first(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, nsplit: int) -
 
 def conv_tc(x: Act, wp: torch.Tensor, Cout: int, *, taps=9, dil=1, mode=MODE_STORE, relu=True, bias=None, out: Act = None,
             out_f32=None, mask: Act = None, arg=None, head_w=None, head_b=None, head_out=None, tabA=None, tabB=None,
-            OH=0, OW=0, bn=0, stages=0, add: Act = None, ctx_wint=None, ctx_ttab=None):
+            OH=0, OW=0, bn=0, stages=0, add: Act = None, ctx_wint=None, ctx_ttab=None, db=None):
     a = ConvArgs()
     a.N, a.H, a.W = x.N, x.H, x.W
     a.Cin, a.Cout = x.C, Cout
@@ -199,6 +199,7 @@ def conv_tc(x: Act, wp: torch.Tensor, Cout: int, *, taps=9, dil=1, mode=MODE_STO
     a.head_w, a.head_b, a.head_out = _ptr(head_w), _ptr(head_b), _ptr(head_out)
     a.tabA, a.tabB = _ptr(tabA), _ptr(tabB)
     a.ctx_wint, a.ctx_ttab = _ptr(ctx_wint), _ptr(ctx_ttab)
+    a.db = _ptr(db)
     _count()
     with _Prof(2.0 * taps * x.C * Cout * x.N * x.H * x.W, f"conv m{mode} {x.C}->{Cout} t{taps} d{dil} {x.H}x{x.W}"):
         check(lib().can_conv_tc(C.byref(a), _stream()), "conv_tc")

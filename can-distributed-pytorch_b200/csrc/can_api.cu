@@ -84,7 +84,9 @@ int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p,
   if (stages < 2) return fail(-20, "conv_tc: tile BN=%d nsplit=%d does not fit shared memory", BN, NSPLIT);
   p.stages = stages;
   const int smem = L::bytes(stages, ctx);
-  auto kern = conv_tc_kernel<BN, NSPLIT, MODE>;
+  // eight epilogue warps for the narrow, epilogue-bound tiles of the bf16 path
+  constexpr int EW = (NSPLIT == 1 && BN <= 128 && (MODE == MODE_STORE || MODE == MODE_POOL || MODE == MODE_UNPOOL)) ? 8 : 4;
+  auto kern = conv_tc_kernel<BN, NSPLIT, MODE, 0, EW>;
   static bool attr_done = false;  // per template instantiation
   static int attr_smem = 0;
   if (!attr_done || smem > attr_smem) {
@@ -93,9 +95,43 @@ int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p,
     attr_done = true;
     attr_smem = kMaxSmem;
   }
-  kern<<<grid, 192, smem, st>>>(tmA, tmB, g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA, p);
+  kern<<<grid, 64 + 32 * EW, smem, st>>>(tmA, tmB, g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA, p);
   CAN_CHECK_LAUNCH("conv_tc launch");
   return 0;
+}
+
+// HALO variant (bf16 path, small Cin): resident weights + halo activation stages.
+template <int BN, int MODE>
+int launch_conv_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmHalo, ConvTcParams& p,
+                     dim3 grid, cudaStream_t st) {
+  using L = ConvTcSmem<BN, 1>;
+  const int tail = L::kTailBytes;
+  int stages = (kMaxSmem - 1024 - p.w_bytes - tail) / p.halo_bytes;
+  if (stages > 8) stages = 8;
+  if (stages < 2) return fail(-20, "conv_tc(halo): BN=%d does not fit shared memory", BN);
+  p.stages = stages;
+  const int smem = 1024 + p.w_bytes + stages * p.halo_bytes + tail;
+  auto kern = conv_tc_kernel<BN, 1, MODE, 1, 8>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tc halo)");
+    attr_done = true;
+  }
+  kern<<<grid, 64 + 32 * 8, smem, st>>>(tmA, tmB, tmHalo, tmA, p);
+  CAN_CHECK_LAUNCH("conv_tc(halo) launch");
+  return 0;
+}
+
+template <int BN>
+int dispatch_halo(int mode, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& h, ConvTcParams& p, dim3 grid,
+                  cudaStream_t st) {
+  switch (mode) {
+    case MODE_STORE: return launch_conv_halo<BN, MODE_STORE>(a, b, h, p, grid, st);
+    case MODE_POOL: return launch_conv_halo<BN, MODE_POOL>(a, b, h, p, grid, st);
+    case MODE_UNPOOL: return launch_conv_halo<BN, MODE_UNPOOL>(a, b, h, p, grid, st);
+    default: return fail(-21, "conv_tc(halo): mode %d not available", mode);
+  }
 }
 
 template <int BN, int NSPLIT>
@@ -125,7 +161,8 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   pl.bn = Cin < 256 ? Cin : (nsplit > 1 ? 128 : 256);
   pl.n_tiles = Cin / pl.bn;
   // taps per CTA: as many TMEM accumulators as fit (bf16 path); the fp32-parity path keeps one
-  pl.T = (nsplit == 1 && taps > 1) ? 512 / pl.bn : 1;
+  // (balanced groups: 9 taps = 5+4 for BN=64, 3+3+3 for BN=128, 2+2+2+2+1 for BN=256)
+  pl.T = (nsplit == 1 && taps > 1) ? (pl.bn == 64 ? 5 : pl.bn == 128 ? 3 : 2) : 1;
   if (pl.T > taps) pl.T = taps;
   pl.tap_groups = (taps + pl.T - 1) / pl.T;
   const int tiles = pl.m_tiles * pl.n_tiles * pl.tap_groups;
@@ -260,6 +297,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   p.out_plane = a->out_plane;
   p.out_cs = a->out_cs; p.out_coff = a->out_coff;
   p.out_f32 = a->out_f32;
+  p.db = (a->mode == CAN_MODE_STORE || a->mode == CAN_MODE_UNPOOL || a->mode == CAN_MODE_DFV) ? a->db : nullptr;
   p.mask = static_cast<const __nv_bfloat16*>(a->mask);
   p.mask_cs = a->mask_cs; p.mask_coff = a->mask_coff; p.mask_plane = a->mask_plane;
   p.add = static_cast<const __nv_bfloat16*>(a->add);
@@ -308,6 +346,19 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   const int ns = a->nsplit;
   g_tmW = nullptr;
   g_tmT = nullptr;
+  // small-Cin layers on the bf16 path: resident weights + halo stages (L2->SM traffic / 3.6)
+  if (ns == 1 && a->taps == 9 && p.n_tiles == 1 && (bn == 64 || bn == 128) &&
+      (a->mode == CAN_MODE_STORE || a->mode == CAN_MODE_POOL || a->mode == CAN_MODE_UNPOOL) &&
+      9 * p.kchunks * bn * 128 <= 147456 && env_int("CAN_B200_HALO", 1) != 0) {
+    p.w_bytes = 9 * p.kchunks * bn * 128;
+    p.halo_bytes = (p.TH + 2 * a->dil) * p.TW * 128;
+    CUtensorMap tmH;
+    int rc = make_act_tmap(&tmH, a->x, a->x_coff, a->Cin, a->x_cs, a->x_plane, 1, a->N, a->H, a->W, p.TW,
+                           p.TH + 2 * a->dil);
+    if (rc) return rc;
+    return bn == 64 ? dispatch_halo<64>(a->mode, tmA, tmB, tmH, p, grid, st)
+                    : dispatch_halo<128>(a->mode, tmA, tmB, tmH, p, grid, st);
+  }
   if (ctx2) {
     CUtensorMap tmW, tmT;
     int rc = make_act_tmap(&tmW, a->ctx_wint, 0, 64, 64, 0, 1, 1, a->H, a->W, p.TW, p.TH);
@@ -589,8 +640,8 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
   p.tap_groups = pl.tap_groups;
   dim3 grid(pl.m_tiles * pl.n_tiles * pl.tap_groups, pl.ksplit);
   if (pl.T > 1) {  // bf16 path, several taps per CTA
-    if (pl.bn == 64) rc = launch_wgrad<64, 1, 8>(tmDZ, tmX, p, grid, st);
-    else if (pl.bn == 128) rc = launch_wgrad<128, 1, 4>(tmDZ, tmX, p, grid, st);
+    if (pl.bn == 64) rc = launch_wgrad<64, 1, 5>(tmDZ, tmX, p, grid, st);
+    else if (pl.bn == 128) rc = launch_wgrad<128, 1, 3>(tmDZ, tmX, p, grid, st);
     else rc = launch_wgrad<256, 1, 2>(tmDZ, tmX, p, grid, st);
   } else if (pl.bn == 64) {
     rc = nsplit == 1   ? launch_wgrad<64, 1, 1>(tmDZ, tmX, p, grid, st)

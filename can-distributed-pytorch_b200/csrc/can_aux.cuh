@@ -97,30 +97,44 @@ pack_conv_weight_kernel_v2(const float* __restrict__ w, __nv_bfloat16* __restric
   }
   __syncthreads();
   const long long total = static_cast<long long>(cout) * cin * taps;
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  // eight consecutive K-elements per thread -> one 16-byte store per plane
   if (fwd) {
-    // one warp per (co, tap): lanes = ci
-    for (int i = wid; i < 32 * taps; i += 8) {
-      const int r = i / taps, tap = i - r * taps;
-      float v = s_w[r * row + lane * taps + tap];
-      __nv_bfloat16* d = fwd + (static_cast<long long>(co0 + r) * taps + tap) * cin + ci0 + lane;
+    for (int idx = threadIdx.x; idx < 32 * taps * 4; idx += 256) {
+      const int qd = idx & 3, rt = idx >> 2;
+      const int r = rt / taps, tap = rt - r * taps;
+      float v[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] = s_w[r * row + (qd * 8 + e) * taps + tap];
+      __nv_bfloat16* d = fwd + (static_cast<long long>(co0 + r) * taps + tap) * cin + ci0 + qd * 8;
       for (int pl = 0; pl < nsplit; ++pl) {
-        const __nv_bfloat16 h = __float2bfloat16_rn(v);
-        d[pl * total] = h;
-        v -= __bfloat162float(h);
+        uint4 q;
+        q.x = pack_bf16x2(v[0], v[1]);
+        q.y = pack_bf16x2(v[2], v[3]);
+        q.z = pack_bf16x2(v[4], v[5]);
+        q.w = pack_bf16x2(v[6], v[7]);
+        *reinterpret_cast<uint4*>(d + pl * total) = q;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] -= bf16_round(v[e]);
       }
     }
   }
   if (dgrad) {
-    // one warp per (ci, tap): lanes = co
-    for (int i = wid; i < 32 * taps; i += 8) {
-      const int ci = i / taps, tap = i - ci * taps;
-      float v = s_w[lane * row + ci * taps + tap];
-      __nv_bfloat16* d = dgrad + (static_cast<long long>(ci0 + ci) * taps + (taps - 1 - tap)) * cout + co0 + lane;
+    for (int idx = threadIdx.x; idx < 32 * taps * 4; idx += 256) {
+      const int qd = idx & 3, rt = idx >> 2;
+      const int ci = rt / taps, tap = rt - ci * taps;
+      float v[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] = s_w[(qd * 8 + e) * row + ci * taps + tap];
+      __nv_bfloat16* d = dgrad + (static_cast<long long>(ci0 + ci) * taps + (taps - 1 - tap)) * cout + co0 + qd * 8;
       for (int pl = 0; pl < nsplit; ++pl) {
-        const __nv_bfloat16 h = __float2bfloat16_rn(v);
-        d[pl * total] = h;
-        v -= __bfloat162float(h);
+        uint4 q;
+        q.x = pack_bf16x2(v[0], v[1]);
+        q.y = pack_bf16x2(v[2], v[3]);
+        q.z = pack_bf16x2(v[4], v[5]);
+        q.w = pack_bf16x2(v[6], v[7]);
+        *reinterpret_cast<uint4*>(d + pl * total) = q;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] -= bf16_round(v[e]);
       }
     }
   }

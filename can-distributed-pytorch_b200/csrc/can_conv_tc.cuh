@@ -41,6 +41,8 @@ struct ConvTcParams {
   int num_tiles;       // tiles_x * tiles_y * N * n_tiles (persistent CTAs stride over them)
   int stages;
   int dbg;             // CAN_B200_DBG bit flags (bring-up experiments only; 0 in production)
+  int w_bytes;         // HALO: bytes of the resident weight region (9 * kchunks * BN * 128)
+  int halo_bytes;      // HALO: bytes of one activation stage ((TH + 2 dil) * TW * 128)
   int relu;
   const float* bias;   // [Cout] or null
   // primary output, NHWC bf16 planes
@@ -48,6 +50,7 @@ struct ConvTcParams {
   long long out_plane;  // elements between planes
   int out_cs, out_coff; // pixel stride (channels) and channel offset
   float* out_f32;       // optional fp32 NHWC copy (same cs/coff addressing), may be null
+  float* db;            // optional [Cout]: += column sums of the stored tile (bias gradient of the layer whose dZ this is)
   // mask source (dgrad): activation whose sign gates the gradient, NHWC bf16 (plane 0)
   const __nv_bfloat16* mask;
   int mask_cs, mask_coff;
@@ -81,7 +84,7 @@ struct ConvTcSmem {
   static constexpr int kBBytes = BN * 128;        // BN rows x 64 k x bf16
   static constexpr int kStageBytes = NSPLIT * (kABytes + kBBytes);
   static constexpr int kCtxTabBytes = 2 * 50 * 64 * 4;
-  static constexpr int kTailBytes = 1024 + 2 * BN * 4;  // barriers + tmem ptr, bias (double-buffered)
+  static constexpr int kTailBytes = 1024 + 2 * BN * 4 + 4096;  // barriers + tmem ptr, bias (double-buffered), s_db[1024]
   static __host__ __device__ constexpr int bytes(int stages, bool ctx) {
     return 1024 /*align slack*/ + stages * kStageBytes + kTailBytes + (ctx ? kCtxTabBytes : 0);
   }
@@ -164,6 +167,22 @@ __device__ __forceinline__ void load_acc(uint32_t taddr, int col, int nact, floa
   }
 }
 
+// Sum each of 32 columns over the 32 lanes of the warp (lane = pixel): recursive halving, 31
+// shuffles; on return lane l holds the sum of column l in v[0].  v[] is destroyed.
+__device__ __forceinline__ float warp_column_sums(float* v, int lane) {
+#pragma unroll
+  for (int half = 16; half >= 1; half >>= 1) {
+    const bool upper = (lane & half) != 0;
+#pragma unroll
+    for (int i = 0; i < half; ++i) {
+      const float send = upper ? v[i] : v[i + half];
+      const float keep = upper ? v[i + half] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+    }
+  }
+  return v[0];
+}
+
 // bf16-path transcendental helpers (one MUFU each): sigmoid(-a) = 0.5 - 0.5 tanh(a/2), 1/x.
 // The epilogue runs on four warps (one per scheduler), so every dependent multi-instruction IEEE
 // division costs its full latency; measured: 380 us of a 533 us kernel before this change.
@@ -178,8 +197,15 @@ __device__ __forceinline__ float rcp_fast(float x) {
   return r;
 }
 
-template <int BN, int NSPLIT, int MODE>
-__global__ void __launch_bounds__(192, 1)
+// HALO = 1 (small Cin, bf16 path): all weights of the CTA's output channels stay resident in shared
+// memory and the activation patch is loaded with a (TH + 2 dil)-row halo once per (dx, channel chunk);
+// the three dy taps are row-shifted views of that stage (row shifts are multiples of 1024 B, so the
+// 128B swizzle phase is preserved).  L2->SM traffic per tile drops from 9 x (A + B) to 3 x halo.
+// EW = number of epilogue warps (4 or 8).  The epilogue runs one warp per scheduler, i.e. latency
+// bound; for narrow tiles (small K) it is the critical path, so EW = 8 lets two warps share each TMEM
+// lane quarter, each taking half of the BN columns.
+template <int BN, int NSPLIT, int MODE, int HALO = 0, int EW = 4>
+__global__ void __launch_bounds__(64 + 32 * EW, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmT,
                const ConvTcParams p) {
@@ -188,14 +214,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int stages = p.stages;
-  uint8_t* tail = smem + stages * L::kStageBytes;
+  uint8_t* ring = HALO ? smem + p.w_bytes : smem;                 // stage ring (after the resident weights)
+  const int stage_bytes = HALO ? p.halo_bytes : L::kStageBytes;
+  uint8_t* tail = ring + stages * stage_bytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
   uint64_t* empty_bar = full_bar + 8;
   uint64_t* tmem_full_bar = empty_bar + 8;    // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;  // [2]
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+  uint64_t* w_bar = tmem_empty_bar + 2;          // HALO: resident weights landed
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(w_bar + 1);
   float* s_bias2 = reinterpret_cast<float*>(tail + 1024);  // [2][BN]
-  float* s_tab = s_bias2 + 2 * BN;  // MODE_CTX / MODE_CTX_BWD only: [2][50][64]
+  float* s_db = s_bias2 + 2 * BN;   // [<=1024] per-CTA partial bias gradient (p.db)
+  float* s_tab = s_db + 1024;       // MODE_CTX / MODE_CTX_BWD only: [2][50][64]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -235,8 +265,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(&tmem_full_bar[a], 1);
-        mbar_init(&tmem_empty_bar[a], 128);  // every epilogue thread arrives
+        mbar_init(&tmem_empty_bar[a], 32 * EW);  // every epilogue thread arrives
       }
+      mbar_init(w_bar, 1);
       fence_mbar_init();
     }
     __syncwarp();
@@ -253,6 +284,27 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      if (HALO) {
+        // resident weights: every (tap, chunk) tile of this CTA's BN output channels, once
+        mbar_expect_tx(w_bar, static_cast<uint32_t>(p.w_bytes));
+        for (int kb = 0; kb < base_kb; ++kb) tma_load_3d(smem + kb * L::kBBytes, &tmB, w_bar, kb * 64, 0, 0);
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+          CAN_TILE_DECODE(tile)
+          (void)n0;
+          for (int chunk = 0; chunk < p.kchunks; ++chunk) {
+            for (int dxi = 0; dxi < 3; ++dxi) {
+              mbar_wait(&empty_bar[stage], phase ^ 1);
+              mbar_expect_tx(&full_bar[stage], static_cast<uint32_t>(p.halo_bytes));
+              tma_load_5d(ring + stage * stage_bytes, &tmW, &full_bar[stage], chunk * 64, x0 + (dxi - 1) * p.dil,
+                          y0 - p.dil, n_img, 0);
+              if (++stage == stages) {
+                stage = 0;
+                phase ^= 1;
+              }
+            }
+          }
+        }
+      } else
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
         CAN_TILE_DECODE(tile)
         for (int kb = 0; kb < num_kb; ++kb) {
@@ -299,11 +351,44 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tc_fence_after();
         const uint32_t tacc = tmem_base + as * ACC_COLS;
         uint32_t used = 0;  // bit a: accumulator a already holds a partial sum
+        if (HALO) {
+          if (it == 0) mbar_wait(w_bar, 0);
+          const uint64_t wdesc0 = umma_smem_desc(smem_u32(smem), 16, 1024);
+          const uint32_t dy_bytes = static_cast<uint32_t>(p.dil * p.TW * 128);
+          const uint32_t tap_row_units = static_cast<uint32_t>((3 * p.kchunks * L::kBBytes) >> 4);  // dy -> dy+1
+          uint32_t accum = 0;
+          for (int chunk = 0; chunk < p.kchunks; ++chunk) {
+            for (int dxi = 0; dxi < 3; ++dxi) {
+              mbar_wait(&full_bar[stage], phase);
+              tc_fence_after();
+              // one descriptor per stage; taps and k-steps only add to its 14-bit address field (>> 4).
+              // The issuing thread is alone: every ALU op it spends per MMA is exposed latency.
+              const uint64_t da0 = umma_smem_desc(smem_u32(ring + stage * stage_bytes), 16, 1024);
+              const uint64_t db0 = wdesc0 + static_cast<uint32_t>(((dxi * p.kchunks + chunk) * L::kBBytes) >> 4);
+#pragma unroll
+              for (int dyi = 0; dyi < 3; ++dyi) {
+                const uint64_t da = da0 + static_cast<uint32_t>((dyi * dy_bytes) >> 4);
+                const uint64_t db = db0 + static_cast<uint32_t>(dyi * tap_row_units);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  umma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, accum);
+                  accum = 1;
+                }
+              }
+              umma_commit(&empty_bar[stage]);
+              if (++stage == stages) {
+                stage = 0;
+                phase ^= 1;
+              }
+            }
+          }
+        } else
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
-          const uint32_t sb = sa + GS * L::kABytes;
+          const uint64_t da0 = umma_smem_desc(sa, 16, 1024);                       // one descriptor pair per
+          const uint64_t db0 = umma_smem_desc(sa + GS * L::kABytes, 16, 1024);     // stage (see HALO note)
 #pragma unroll
           for (int pa = 0; pa < GS; ++pa) {
 #pragma unroll
@@ -313,13 +398,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const int acc = kCtx2 ? (kb == base_kb + 1 ? 1 : 0)
                                 : (GS == 1)         ? 0
                                                     : ((pa + pb == 0) ? (kb % NACC) : NACC);
+                const uint32_t accf = (used >> acc) & 1u;
+                used |= 1u << acc;
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                  const uint64_t da = umma_smem_desc(sa + pa * L::kABytes + k * 32, 16, 1024);
-                  const uint64_t db = umma_smem_desc(sb + pb * L::kBBytes + k * 32, 16, 1024);
-                  umma_bf16(tacc + acc * BN, da, db, idesc, (used >> acc) & 1u);
-                  used |= 1u << acc;
-                }
+                for (int k = 0; k < 4; ++k)
+                  umma_bf16(tacc + acc * BN, da0 + ((pa * L::kABytes + k * 32) >> 4), db0 + ((pb * L::kBBytes + k * 32) >> 4),
+                            idesc, k ? 1u : accf);
               }
             }
           }
@@ -339,26 +423,33 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int m = q * 32 + lane;
     const int ty = m / p.TW, tx = m - ty * p.TW;
     const int nact = min(AccLayout<BN, GS>::kNacc, num_kb);  // hi*hi accumulators actually written
+    // columns of the tile handled by this warp (EW == 8: the two warps of a lane quarter split them)
+    constexpr int CW = BN / (EW / 4);
+    const int cbeg = ((warp - 2) >> 2) * CW, cend = cbeg + CW;
+    if (p.db) {
+      for (int i = etid; i < 1024; i += 32 * EW) s_db[i] = 0.f;
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
+    }
     int it = 0;
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
     CAN_TILE_DECODE(tile)
     const int as = it % ACC_STAGES;
     const uint32_t aphase = static_cast<uint32_t>(it / ACC_STAGES) & 1u;
     float* s_bias = s_bias2 + (it & 1) * BN;
-    for (int i = etid; i < BN; i += 128) s_bias[i] = p.bias ? p.bias[n0 + i] : 0.f;
+    for (int i = etid; i < BN; i += 32 * EW) s_bias[i] = p.bias ? p.bias[n0 + i] : 0.f;
     if (MODE == MODE_CTX || MODE == MODE_CTX_BWD) {
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // everyone finished reading the previous tile's tables
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");  // everyone finished reading the previous tile's tables
       // tables of this image for the 64 channels of this n-tile: [2][50][64]
       const float* ga = p.tabA + (static_cast<long long>(n_img) * 50) * 512 + n_tile * 64;
       const float* gb = p.tabB + (static_cast<long long>(n_img) * 50) * 512 + n_tile * 64;
-      for (int i = etid; i < 50 * 16; i += 128) {
+      for (int i = etid; i < 50 * 16; i += 32 * EW) {
         const int pos = i >> 4, c4 = (i & 15) * 4;
         *reinterpret_cast<float4*>(s_tab + pos * 64 + c4) = *reinterpret_cast<const float4*>(ga + pos * 512 + c4);
         *reinterpret_cast<float4*>(s_tab + 3200 + pos * 64 + c4) =
             *reinterpret_cast<const float4*>(gb + pos * 512 + c4);
       }
     }
-    asm volatile("bar.sync 1, 128;" ::: "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
 
     const int y = y0 + ty, x = x0 + tx;
     const bool valid = (y < p.H) && (x < p.W);
@@ -367,13 +458,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     mbar_wait(&tmem_full_bar[as], aphase);
     tc_fence_after();
 
-    if (MODE == MODE_STORE) {
+    if (p.dbg & 16) {
+      // bring-up experiment: no epilogue work at all
+    } else if (MODE == MODE_STORE) {
       const long long pix = (static_cast<long long>(n_img) * p.H + y) * p.W + x;
       __nv_bfloat16* obase = p.out + pix * p.out_cs + p.out_coff + n0;
       const __nv_bfloat16* mbase = p.mask ? p.mask + pix * p.mask_cs + p.mask_coff + n0 : nullptr;
       float* fbase = p.out_f32 ? p.out_f32 + pix * p.out_cs + p.out_coff + n0 : nullptr;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = cbeg; c0 < cend; c0 += 32) {
         float r[32];
         load_acc<BN, GS, 32>(taddr, c0, nact, r);
         float v[32];
@@ -400,6 +493,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               *reinterpret_cast<float4*>(fbase + c0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
           }
         }
+        if (p.db) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = valid ? v[i] : 0.f;
+          atomicAdd(&s_db[n0 + c0 + lane], warp_column_sums(v, lane));
+        }
       }
     } else if (MODE == MODE_POOL) {
       // 2x2 window = lanes {l, l^1, l^TW, l^TW^1}; the lane at the even/even corner writes.
@@ -411,7 +509,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       __nv_bfloat16* obase = p.out + ppix * p.out_cs + p.out_coff + n0;
       uint8_t* abase = p.arg ? p.arg + ppix * p.arg_cs + n0 : nullptr;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = cbeg; c0 < cend; c0 += 32) {
         float r[32];
         load_acc<BN, GS, 32>(taddr, c0, nact, r);
         float v[32];
@@ -445,7 +543,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       __nv_bfloat16* obase = p.out ? p.out + pix * p.out_cs + p.out_coff + n0 : nullptr;
       float dot = 0.f;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = cbeg; c0 < cend; c0 += 32) {
         float r[32];
         load_acc<BN, GS, 32>(taddr, c0, nact, r);
         float v[32];
@@ -463,11 +561,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const __nv_bfloat16* mbase = p.mask + pix * p.mask_cs + p.mask_coff + n0;
       const uint8_t* abase = p.arg + pix * p.arg_cs + n0;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = cbeg; c0 < cend; c0 += 32) {
         float r[32];
         load_acc<BN, GS, 32>(taddr, c0, nact, r);
+        float g[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) g[i] = 0.f;
         if (valid) {
-          float g[32];
           uint32_t code[8];
           {
             uint4 a0 = *reinterpret_cast<const uint4*>(abase + c0);
@@ -496,6 +596,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             store_bf16_planes<NSPLIT, 32>(p.out + opix * p.out_cs + p.out_coff + n0 + c0, p.out_plane, v);
           }
         }
+        if (p.db) atomicAdd(&s_db[n0 + c0 + lane], warp_column_sums(g, lane));
       }
     } else if (MODE == MODE_CTX) {
       // BN == 256 columns = 4 scales x 64 channels of n-tile blockIdx.y; column j*64+c holds
@@ -774,11 +875,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const __nv_bfloat16* abase = p.add + pix * p.add_cs + p.add_coff + n0;
       const float* tab = p.tabA + static_cast<long long>(n_img) * 50 * 512 + n0;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = cbeg; c0 < cend; c0 += 32) {
         float r[32];
         load_acc<BN, GS, 32>(taddr, c0, nact, r);
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = 0.f;
         if (valid) {
-          float v[32];
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = -r[i];
 #pragma unroll
@@ -811,12 +914,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
           store_bf16_planes<NSPLIT, 32>(obase + c0, p.out_plane, v);
         }
+        if (p.db) atomicAdd(&s_db[n0 + c0 + lane], warp_column_sums(v, lane));
       }
     }
     // this accumulator stage may be overwritten by the MMAs of the tile after next
     tc_fence_before();
     mbar_arrive(&tmem_empty_bar[as]);
     }  // tile loop
+    if (p.db) {
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
+      const int cout = p.n_tiles * BN;
+      for (int i = etid; i < cout; i += 32 * EW) atomicAdd(p.db + i, s_db[i]);
+    }
   }
 #undef CAN_TILE_DECODE
 

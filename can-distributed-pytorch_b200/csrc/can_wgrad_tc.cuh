@@ -142,7 +142,9 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
-        const uint32_t sb = sa + NSPLIT * L::kABytes;
+        // one descriptor pair per stage; planes, taps and k-steps only add to the address field (>> 4)
+        const uint64_t da0 = umma_smem_desc(sa, L::kGroupBytes, 1024);
+        const uint64_t db0 = umma_smem_desc(sa + NSPLIT * L::kABytes, L::kGroupBytes, 1024);
         for (int tt = 0; tt < ntaps; ++tt) {
 #pragma unroll
           for (int pa = 0; pa < NSPLIT; ++pa) {
@@ -151,10 +153,9 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
               if (pa + pb < NSPLIT) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {  // 16 pixels (= 2 swizzle atoms of 8 rows) per MMA
-                  const uint64_t da = umma_smem_desc(sa + pa * L::kABytes + k * 2048, L::kGroupBytes, 1024);
-                  const uint64_t db =
-                      umma_smem_desc(sb + (pb * T + tt) * L::kBBytes + k * 2048, L::kGroupBytes, 1024);
-                  umma_bf16(tmem_base + tt * BN, da, db, idesc, (accum | (pa + pb) | k) ? 1u : 0u);
+                  umma_bf16(tmem_base + tt * BN, da0 + ((pa * L::kABytes + k * 2048) >> 4),
+                            db0 + (((pb * T + tt) * L::kBBytes + k * 2048) >> 4), idesc,
+                            (accum | (pa + pb) | k) ? 1u : 0u);
                 }
               }
             }

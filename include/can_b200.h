@@ -77,6 +77,8 @@ typedef struct can_conv_args {
   const float* tabB;     /* CTX: [N][50][512] b_j = conv{S}_2(a_j)                            */
   const void* ctx_wint;  /* CTX2: can_ctx_wint(nsplit 1, N 1) interpolation matrix [H][W][64] bf16 */
   const void* ctx_ttab;  /* CTX2: can_ctx_ttab tables [2][N][2048][64] bf16                      */
+  float* db;             /* STORE/UNPOOL/DFV (dgrad use): [Cout] += per-channel sums of the stored
+                            tile = bias gradient of the layer whose dZ this launch produces; NULL = off */
 } can_conv_args;
 
 /* The dense contractions of the step on tcgen05/TMEM fed by TMA.

@@ -40,6 +40,14 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     print(f"plain step: {e0.elapsed_time(e1) / 5:.3f} ms (batch {B})")
+    import time
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    step()
+    step()
+    t1 = time.perf_counter()
+    torch.cuda.synchronize()
+    print(f"host enqueue time: {(t1 - t0) / 2 * 1e3:.3f} ms per step")
     ops.PROFILE = []
     step()
     torch.cuda.synchronize()
