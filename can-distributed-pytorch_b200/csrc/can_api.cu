@@ -166,15 +166,20 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   if (pl.T > taps) pl.T = taps;
   pl.tap_groups = (taps + pl.T - 1) / pl.T;
   const int tiles = pl.m_tiles * pl.n_tiles * pl.tap_groups;
-  // split-K factor: fill the 148 SMs with whole waves (one CTA per SM), preferring fewer splits
+  // split-K factor from a two-term cost model: MMA time at the wave efficiency of tiles*c CTAs on
+  // 148 SMs (one CTA per SM) + the fp32 partial tiles every split writes and the reduction re-reads
+  // (measured: 11 splits of the 1024->512 layer wrote 155 MB = a third of that kernel's time).
   int ks = 1;
-  double best = -1.0;
+  double best = 1e30;
+  const double flops = 2.0 * taps * static_cast<double>(Cin) * Cout * N * H * W;
+  const double wbytes = 8.0 * taps * static_cast<double>(Cin) * Cout;  // 4 B written + 4 B read per split
   for (int c = 1; c <= 160 && c <= pl.total_patches; ++c) {
     const int ctas = tiles * c;
     const int waves = (ctas + 147) / 148;
-    const double eff = static_cast<double>(ctas) / (148.0 * waves) - 0.002 * c;
-    if (eff > best + 1e-9) {
-      best = eff;
+    const double eff = static_cast<double>(ctas) / (148.0 * waves);
+    const double cost = flops / (1.1e15 * eff) + c * wbytes / 4.5e12 + 1.5e-6 * waves;
+    if (cost < best - 1e-12) {
+      best = cost;
       ks = c;
     }
   }

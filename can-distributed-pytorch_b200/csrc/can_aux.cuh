@@ -73,7 +73,13 @@ __global__ void wgrad_reduce_kernel_v2(const float* __restrict__ ws, float* __re
   const long long slab = static_cast<long long>(taps) * cout * cin;
   const float* src = ws + (static_cast<long long>(tap) * cout + co) * cin + ci0 + c;
   float acc = 0.f;
-  for (int s = 0; s < splits; ++s) acc += src[s * slab];
+  int sp = 0;
+  for (; sp + 4 <= splits; sp += 4) {  // four independent loads in flight
+    const float a0 = src[(sp + 0) * slab], a1 = src[(sp + 1) * slab], a2 = src[(sp + 2) * slab],
+                a3 = src[(sp + 3) * slab];
+    acc += (a0 + a1) + (a2 + a3);
+  }
+  for (; sp < splits; ++sp) acc += src[sp * slab];
   s_t[c * taps + tap] = acc;
   __syncthreads();
   float* g = grad + (static_cast<long long>(co) * cin + ci0) * taps + threadIdx.x;
@@ -91,9 +97,22 @@ pack_conv_weight_kernel_v2(const float* __restrict__ w, __nv_bfloat16* __restric
   extern __shared__ float s_w[];  // [32 co][32*taps + 1]
   const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 32;
   const int row = 32 * taps + 1;
-  for (int i = threadIdx.x; i < 32 * 32 * taps; i += 256) {
-    const int r = i / (32 * taps), o = i - r * 32 * taps;
-    s_w[r * row + o] = w[(static_cast<long long>(co0 + r) * cin + ci0) * taps + o];
+  // four independent loads in flight per thread (a load-then-store loop would serialise on the
+  // memory latency: in-order issue stalls at the first dependent store)
+  const int per_row = 32 * taps, tot = 32 * per_row;
+  for (int i0 = threadIdx.x; i0 < tot; i0 += 1024) {
+    float v[4];
+    int dst[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * 256;
+      const int r = i / per_row, o = i - r * per_row;
+      dst[u] = r * row + o;
+      v[u] = (i < tot) ? __ldg(w + (static_cast<long long>(co0 + r) * cin + ci0) * taps + o) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i0 + u * 256 < tot) s_w[dst[u]] = v[u];
   }
   __syncthreads();
   const long long total = static_cast<long long>(cout) * cin * taps;

@@ -57,7 +57,7 @@ def _worker(rank, world, port, q):
     lr0 = 1e-3
     upd = -(lr0 * world) * buckets.grad_scale * arena
     if rank == 0:
-        q.put((upd, lsum / world))
+        q.put((upd.numpy().copy(), float(lsum / world)))   # by value: the worker may exit before the parent reads
     dist.barrier()
     dist.destroy_process_group()
 
@@ -70,6 +70,7 @@ def test_two_ranks_equal_one_rank_on_the_concatenated_batch():
     for p in procs:
         p.start()
     upd, mean_loss = q.get(timeout=600)
+    upd = torch.from_numpy(upd)
     for p in procs:
         p.join(timeout=600)
         assert p.exitcode == 0

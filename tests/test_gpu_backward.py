@@ -183,3 +183,30 @@ def test_stock_sgd_and_fused_sgd_agree(dev):
     for (k, a), (_, b) in zip(m1.state_dict().items(), m2.state_dict().items()):
         da, db = a.double().cpu() - sd[k].double(), b.double().cpu() - sd[k].double()
         assert harness.rel_l2(db, da) < 2e-2, k
+
+
+# ---------------------------------------------------------------- step drivers (reference signatures)
+class _Loader(list):
+    """Minimal stand-in for the DataLoader the reference passes to train_one_epoch / evaluate."""
+
+
+def test_train_one_epoch_and_evaluate_mirror_the_reference_drivers(dev):
+    from can_b200 import ops
+    from can_b200.utils.train_eval_utils import FusedTrainer, evaluate, train_one_epoch
+    sd = harness.make_state_dict("he")
+    batches = _Loader((harness.make_input(1, 64, 64, seed=10 + i), harness.make_gt(1, 64, 64, seed=20 + i)) for i in range(3))
+    # oracle: three SGD steps, running mean of the losses (train_eval_utils.py:41)
+    ref_sd, bufs, mean = {k: v.double().clone() for k, v in sd.items()}, {}, 0.0
+    for step, (x, gt) in enumerate(batches):
+        mean = (mean * step + float(T.train_step(x.double(), gt.double(), ref_sd, bufs, 1e-7, 0.95))) / (step + 1)
+    m = _model(sd, "fp32", dev)
+    got = train_one_epoch(m, FusedTrainer(m, lr=1e-7, momentum=0.95), batches, dev, epoch=0)
+    assert got == pytest.approx(mean, rel=2e-4)
+    # evaluate: sum over the loader of |sum(et) - sum(gt)| (train_eval_utils.py:83,136)
+    ref_mae = 0.0
+    with torch.no_grad():
+        for x, gt in batches:
+            et = T.forward(x.double(), ref_sd)
+            ref_mae += abs(float(et.sum()) - float(gt.double().sum()))
+    mae = evaluate(m, batches, dev, epoch=0)
+    assert mae == pytest.approx(ref_mae, rel=2e-3)
