@@ -131,3 +131,40 @@ def evaluate(model, test_loader, device, epoch=0, show_images=False, use_wandb=F
         torch.cuda.synchronize(device)
     mae = reduce_value(mae, average=False)
     return mae.item()
+
+
+class DevicePrefetcher:
+    """Pinned-host -> device copies of the NEXT batch on a side stream while the current step computes
+    (the reference copies synchronously from pageable memory, utils/train_eval_utils.py:30-31).
+
+    ``for img, gt in DevicePrefetcher(loader, device): ...`` yields device tensors whose copies have
+    completed with respect to the current stream."""
+
+    def __init__(self, loader, device):
+        self.loader, self.device = loader, device
+        self.stream = torch.cuda.Stream(device=device)
+
+    def _issue(self, batch):
+        with torch.cuda.stream(self.stream):
+            dev = tuple(t.to(self.device, non_blocking=True) for t in batch)
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        return dev, ev
+
+    def __iter__(self):
+        it = iter(self.loader)
+        try:
+            pending = self._issue(next(it))
+        except StopIteration:
+            return
+        while pending is not None:
+            dev, ev = pending
+            try:
+                pending = self._issue(next(it))   # next batch's H2D overlaps this batch's step
+            except StopIteration:
+                pending = None
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_event(ev)
+            for t in dev:
+                t.record_stream(cur)
+            yield dev

@@ -21,7 +21,7 @@ def main():
     m = m.cuda()
     x = harness.make_input(B, 768, 1024).cuda()
     gt = harness.make_gt(B, 768, 1024).cuda()
-    tr = FusedTrainer(m, lr=1e-7) if train else None
+    tr = FusedTrainer(m, lr=1e-10) if train else None
 
     def step():
         if train:

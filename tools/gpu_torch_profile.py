@@ -21,7 +21,7 @@ def main():
     m = m.cuda()
     x = harness.make_input(B, 768, 1024).cuda()
     gt = harness.make_gt(B, 768, 1024).cuda()
-    tr = FusedTrainer(m, lr=1e-7)
+    tr = FusedTrainer(m, lr=1e-10)
     for _ in range(3):
         tr.step(x, gt)
     torch.cuda.synchronize()
