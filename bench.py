@@ -258,14 +258,29 @@ def main():
         step_resident()
     torch.cuda.synchronize()
     prof, ops.PROFILE = ops.PROFILE, None
+    npass = max(1, min(args.steps, 5))
     k_ms = sum(rec[0].elapsed_time(rec[1]) for rec in prof)
     k_flop = sum(rec[2] for rec in prof)
     peak_tf, peak_hbm, peak_src = measured_peaks()
-    achieved = (k_flop / 1e12) / (k_ms * 1e-3) if k_ms > 0 else 0.0
-    roofline = {"bound": "tensor", "kernel": "conv_tc_kernel/wgrad_tc_kernel (tcgen05 implicit GEMM)",
-                "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
-                "traffic": None, "peak_source": peak_src, "launches_per_step": len(prof) // max(1, min(args.steps, 5)),
-                "share_of_step": (k_ms / max(1, min(args.steps, 5))) / (ms / args.steps)}
+    # dominant kernel = conv_tc_kernel<256,1,STORE> on the 512->512 3x3 layers at 96x128 (conv4_2, conv4_3,
+    # backend.2, backend.4 and their data gradients): algorithmic FLOPs per launch / mean launch duration
+    dom = [rec for rec in prof if rec[3].startswith("conv m0 512->512 t9")]
+    dom_ms = sum(rec[0].elapsed_time(rec[1]) for rec in dom)
+    dom_flop = sum(rec[2] for rec in dom)
+    achieved = (dom_flop / 1e12) / (dom_ms * 1e-3) if dom_ms > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "r01_dominant_kernel_traffic.json")
+    if os.path.exists(tpath):  # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
+        traffic = json.load(open(tpath)).get(f"batch{B}")
+    roofline = {"bound": "tensor", "kernel": "conv_tc_kernel<256,1,STORE> 512->512 3x3 @96x128 (tcgen05 implicit GEMM)",
+                "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf if peak_tf else None,
+                "traffic": traffic, "peak_source": peak_src,
+                "flop_per_launch": dom_flop / max(1, len(dom)), "us_per_launch": 1e3 * dom_ms / max(1, len(dom)),
+                "launches_per_step": len(dom) // npass, "share_of_step": (dom_ms / npass) / (ms / args.steps),
+                "all_tensor_kernels": {"achieved": (k_flop / 1e12) / (k_ms * 1e-3) if k_ms > 0 else 0.0,
+                                       "launches_per_step": len(prof) // npass,
+                                       "share_of_step": (k_ms / npass) / (ms / args.steps)},
+                "timing": "CUDA events around every launch in a separate pass of the same steps"}
 
     final = step_resident()
     torch.cuda.synchronize()

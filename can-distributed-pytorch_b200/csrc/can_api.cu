@@ -161,8 +161,8 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   pl.bn = Cin < 256 ? Cin : (nsplit > 1 ? 128 : 256);
   pl.n_tiles = Cin / pl.bn;
   // taps per CTA: as many TMEM accumulators as fit (bf16 path); the fp32-parity path keeps one
-  // (balanced groups: 9 taps = 5+4 for BN=64, 3+3+3 for BN=128, 2+2+2+2+1 for BN=256)
-  pl.T = (nsplit == 1 && taps > 1) ? (pl.bn == 64 ? 5 : pl.bn == 128 ? 3 : 2) : 1;
+  // (balanced groups: 9 taps = 3+3+3 for BN=64 (one N=192 MMA per k-step) and BN=128, 2+2+2+2+1 for BN=256)
+  pl.T = (nsplit == 1 && taps > 1) ? (pl.bn == 64 ? 3 : pl.bn == 128 ? 3 : 2) : 1;
   if (pl.T > taps) pl.T = taps;
   pl.tap_groups = (taps + pl.T - 1) / pl.T;
   const int tiles = pl.m_tiles * pl.n_tiles * pl.tap_groups;
@@ -645,7 +645,7 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
   p.tap_groups = pl.tap_groups;
   dim3 grid(pl.m_tiles * pl.n_tiles * pl.tap_groups, pl.ksplit);
   if (pl.T > 1) {  // bf16 path, several taps per CTA
-    if (pl.bn == 64) rc = launch_wgrad<64, 1, 5>(tmDZ, tmX, p, grid, st);
+    if (pl.bn == 64) rc = launch_wgrad<64, 1, 3>(tmDZ, tmX, p, grid, st);
     else if (pl.bn == 128) rc = launch_wgrad<128, 1, 3>(tmDZ, tmX, p, grid, st);
     else rc = launch_wgrad<256, 1, 2>(tmDZ, tmX, p, grid, st);
   } else if (pl.bn == 64) {

@@ -134,7 +134,6 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 1, 1);  // both operands MN-major
       int stage = 0;
       uint32_t phase = 0;
       uint32_t accum = 0;
@@ -145,7 +144,13 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
         // one descriptor pair per stage; planes, taps and k-steps only add to the address field (>> 4)
         const uint64_t da0 = umma_smem_desc(sa, L::kGroupBytes, 1024);
         const uint64_t db0 = umma_smem_desc(sa + NSPLIT * L::kABytes, L::kGroupBytes, 1024);
-        for (int tt = 0; tt < ntaps; ++tt) {
+        // Several taps per instruction: the X tiles of consecutive taps are consecutive 64-channel
+        // groups in shared memory, exactly what one wider MMA (N = taps * BN <= 256) expects, and a
+        // tcgen05.mma costs ~60 cycles + 0.63 cycles per N column (measured), so fewer, wider MMAs win.
+        constexpr int kTapsPerMma = (256 / BN) < T ? (256 / BN) : T;
+        for (int tt = 0; tt < ntaps; tt += kTapsPerMma) {
+          const int tc = min(kTapsPerMma, ntaps - tt);
+          const uint32_t idesc_n = umma_idesc_bf16(128, tc * BN, 1, 1);
 #pragma unroll
           for (int pa = 0; pa < NSPLIT; ++pa) {
 #pragma unroll
@@ -154,7 +159,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {  // 16 pixels (= 2 swizzle atoms of 8 rows) per MMA
                   umma_bf16(tmem_base + tt * BN, da0 + ((pa * L::kABytes + k * 2048) >> 4),
-                            db0 + (((pb * T + tt) * L::kBBytes + k * 2048) >> 4), idesc,
+                            db0 + (((pb * T + tt) * L::kBBytes + k * 2048) >> 4), idesc_n,
                             (accum | (pa + pb) | k) ? 1u : 0u);
                 }
               }
