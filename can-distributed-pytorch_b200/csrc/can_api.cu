@@ -469,8 +469,42 @@ int can_ctx_pool_fwd(const void* fv, int64_t fv_plane, int nsplit, int cs, int c
   if (cs % 2 || coff % 2) return fail(-3, "ctx_pool_fwd: cs/coff must be even");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   float* R = static_cast<float*>(ws);
-  ctx_pool_rows_kernel<<<dim3(H, N), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(fv), fv_plane, nsplit, cs, coff,
-                                                   R, H, W);
+  if (cs % 4 == 0 && coff % 4 == 0 && W <= 16384 && H <= 65535) {
+    // segment table of a row: window boundaries (sorted, unique) and the windows containing each segment
+    PoolSegments seg;
+    memset(&seg, 0, sizeof(seg));
+    const int SS[4] = {1, 2, 3, 6};
+    int ws12[12], we12[12], nb = 0, k = 0;
+    for (int j = 0; j < 4; ++j)
+      for (int i = 0; i < SS[j]; ++i, ++k) {
+        ws12[k] = adaptive_start(i, W, SS[j]);
+        we12[k] = adaptive_end(i, W, SS[j]);
+        seg.bound[nb++] = ws12[k];
+        seg.bound[nb++] = we12[k];
+      }
+    for (int a = 1; a < nb; ++a)
+      for (int b = a; b > 0 && seg.bound[b - 1] > seg.bound[b]; --b) {
+        const int t = seg.bound[b];
+        seg.bound[b] = seg.bound[b - 1];
+        seg.bound[b - 1] = t;
+      }
+    int u = 1;
+    for (int a = 1; a < nb; ++a)
+      if (seg.bound[a] != seg.bound[u - 1]) seg.bound[u++] = seg.bound[a];
+    seg.nseg = u - 1;
+    for (int sgi = 0; sgi < seg.nseg; ++sgi) {
+      unsigned m = 0;
+      for (int w12 = 0; w12 < 12; ++w12)
+        if (seg.bound[sgi] >= ws12[w12] && seg.bound[sgi + 1] <= we12[w12]) m |= 1u << w12;
+      seg.mask[sgi] = static_cast<unsigned short>(m);
+    }
+    const int smem = (W + 15) & ~15;  // per-x segment ids
+    ctx_pool_rows_kernel_v2<<<dim3(H, N), 256, smem, st>>>(static_cast<const __nv_bfloat16*>(fv), fv_plane, nsplit, cs,
+                                                           coff, R, H, W, seg, env_int("CAN_B200_DBG", 0));
+  } else {
+    ctx_pool_rows_kernel<<<dim3(H, N), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(fv), fv_plane, nsplit, cs, coff,
+                                                     R, H, W);
+  }
   CAN_CHECK_LAUNCH("ctx_pool_rows");
   ctx_pool_finalize_kernel<<<dim3(50, N), 512, 0, st>>>(R, pooled, H, W);
   CAN_CHECK_LAUNCH("ctx_pool_finalize");

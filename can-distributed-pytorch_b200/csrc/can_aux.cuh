@@ -2,6 +2,7 @@
 // reduction into the parameter layout, and weight packing for both GEMM orientations.
 #pragma once
 #include "can_ptx.cuh"
+#include "can_simple.cuh"
 
 namespace canb {
 
@@ -205,6 +206,98 @@ im2col_first_kernel_v2(const float* __restrict__ x, __nv_bfloat16* __restrict__ 
         for (int e = 0; e < 8; ++e) v[e] -= bf16_round(v[e]);
       }
     }
+  }
+}
+
+// Segment table of one image row for K1 (built on the host, passed by value): the 12 x-windows of
+// the scales 1,2,3,6 overlap when W % S != 0, so the row is cut at every window boundary into
+// disjoint segments and `mask[s]` says which windows contain segment s.
+struct PoolSegments {
+  int nseg;
+  int bound[26];
+  unsigned short mask[26];
+};
+
+// K1 stage A (second generation): row sums of fv over the 12 x-windows.  One CTA per (row y, image
+// n); 256 threads = 128 channel groups (4 channels, one 8-byte load) x 2 pixel lanes (adjacent
+// threads, combined with one shuffle); eight loads in flight per thread.  A pixel adds to ONE
+// running segment sum; a finished segment is added to the windows that contain it.  No serial
+// prologue (a per-CTA sort of the boundaries by one thread cost more than streaming the row).
+// fv is read exactly once.   R[n][y][12][512] fp32
+__global__ void __launch_bounds__(256, 3)
+ctx_pool_rows_kernel_v2(const __nv_bfloat16* __restrict__ fv, long long fv_plane, int nsplit, int cs, int coff,
+                        float* __restrict__ R, int H, int W, const __grid_constant__ PoolSegments seg, int dbg) {
+  extern __shared__ unsigned char s_segid[];      // [W] segment index of every x
+  __shared__ unsigned short s_segmask[26];
+  if (threadIdx.x < 26) s_segmask[threadIdx.x] = seg.mask[threadIdx.x];
+  for (int x = threadIdx.x; x < W; x += 256) {
+    int sgi = 0;
+#pragma unroll
+    for (int b = 1; b < 25; ++b) sgi += (b < seg.nseg && x >= seg.bound[b]) ? 1 : 0;
+    s_segid[x] = static_cast<unsigned char>(sgi);
+  }
+  __syncthreads();
+  const int y = blockIdx.x, n = blockIdx.y;
+  const int cg = threadIdx.x >> 1, xl = threadIdx.x & 1;
+  const __nv_bfloat16* row = fv + (static_cast<long long>(n) * H + y) * W * cs + coff + cg * 4;
+  float acc[12][4];
+#pragma unroll
+  for (int k = 0; k < 12; ++k)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) acc[k][e] = 0.f;
+  float cur0 = 0.f, cur1 = 0.f, cur2 = 0.f, cur3 = 0.f;
+  int cur_seg = (xl < W) ? s_segid[xl] : 0;
+  auto flush = [&](int sgi) {
+    const unsigned m = s_segmask[sgi];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+      if (m & (1u << k)) {
+        acc[k][0] += cur0;
+        acc[k][1] += cur1;
+        acc[k][2] += cur2;
+        acc[k][3] += cur3;
+      }
+    }
+    cur0 = cur1 = cur2 = cur3 = 0.f;
+  };
+  for (int pl = 0; pl < nsplit; ++pl) {
+    const __nv_bfloat16* rp = row + pl * fv_plane;
+    for (int x0 = xl; x0 < W; x0 += 16) {
+      uint2 q[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int x = x0 + 2 * u;
+        q[u] = (x < W) ? *reinterpret_cast<const uint2*>(rp + static_cast<long long>(x) * cs) : make_uint2(0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int x = x0 + 2 * u;
+        if (x < W) {
+          const int sgi = (dbg & 1) ? cur_seg : s_segid[x];
+          if (sgi != cur_seg) {
+            flush(cur_seg);
+            cur_seg = sgi;
+          }
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q[u]);
+          cur0 += __low2float(h[0]);
+          cur1 += __high2float(h[0]);
+          cur2 += __low2float(h[1]);
+          cur3 += __high2float(h[1]);
+        }
+      }
+    }
+    flush(cur_seg);
+    cur_seg = (xl < W) ? s_segid[xl] : 0;
+  }
+  float* o = R + ((static_cast<long long>(n) * H + y) * 12) * 512 + cg * 4;
+#pragma unroll
+  for (int k = 0; k < 12; ++k) {
+    float4 t;
+    t.x = acc[k][0] + __shfl_xor_sync(0xffffffffu, acc[k][0], 1);
+    t.y = acc[k][1] + __shfl_xor_sync(0xffffffffu, acc[k][1], 1);
+    t.z = acc[k][2] + __shfl_xor_sync(0xffffffffu, acc[k][2], 1);
+    t.w = acc[k][3] + __shfl_xor_sync(0xffffffffu, acc[k][3], 1);
+    if (xl == 0) *reinterpret_cast<float4*>(o + k * 512) = t;
   }
 }
 
