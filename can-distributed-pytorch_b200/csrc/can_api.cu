@@ -51,12 +51,13 @@ PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
 
 // bf16 tensor map with a 128-byte swizzled box whose innermost extent is 64 elements.
 int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-              const uint32_t* box) {
+              const uint32_t* box, bool swizzle128 = true) {
   auto enc = get_encode();
   if (!enc) return fail(-100, "cuTensorMapEncodeTiled entry point not available");
   uint32_t estr[5] = {1, 1, 1, 1, 1};
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(-101, "cuTensorMapEncodeTiled failed (CUresult %d)", static_cast<int>(r));
   return 0;
@@ -499,8 +500,36 @@ int can_ctx_pool_fwd(const void* fv, int64_t fv_plane, int nsplit, int cs, int c
       seg.mask[sgi] = static_cast<unsigned short>(m);
     }
     const int smem = (W + 15) & ~15;  // per-x segment ids
-    ctx_pool_rows_kernel_v2<<<dim3(H, N), 256, smem, st>>>(static_cast<const __nv_bfloat16*>(fv), fv_plane, nsplit, cs,
-                                                           coff, R, H, W, seg, env_int("CAN_B200_DBG", 0));
+    const bool aligned16 = cs % 8 == 0 && coff % 8 == 0 && fv_plane % 8 == 0 &&
+                           (reinterpret_cast<uintptr_t>(fv) & 15) == 0;
+    if (aligned16 && env_int("CAN_B200_K1", 3) == 3) {
+      // TMA-streamed version: persistent CTAs, producer warp + two sets of 8 consumer warps
+      const int smem3 = pool_rows_smem_bytes(W);
+      static thread_local bool attr_done = false;
+      if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(ctx_pool_rows_kernel_v3, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             pool_rows_smem_bytes(16384));
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(ctx_pool_rows)");
+        attr_done = true;
+      }
+      int dev = 0, sms = 0;
+      cudaGetDevice(&dev);
+      if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+      const int NH = N * H;
+      const int ctas = NH < sms ? NH : sms;
+      CUtensorMap tm;
+      const uint64_t dims[5] = {512, static_cast<uint64_t>(W), static_cast<uint64_t>(NH), static_cast<uint64_t>(nsplit), 1};
+      const uint64_t str[4] = {static_cast<uint64_t>(cs) * 2, static_cast<uint64_t>(W) * cs * 2,
+                               static_cast<uint64_t>(nsplit > 1 ? fv_plane : static_cast<int64_t>(NH) * W * cs) * 2,
+                               static_cast<uint64_t>(nsplit > 1 ? fv_plane * nsplit : static_cast<int64_t>(NH) * W * cs) * 2};
+      const uint32_t box[5] = {256, kPoolChunk, 1, 1, 1};
+      int rc = make_tmap(&tm, static_cast<const __nv_bfloat16*>(fv) + coff, 5, dims, str, box, false);
+      if (rc) return rc;
+      ctx_pool_rows_kernel_v3<<<ctas, 544, smem3, st>>>(tm, nsplit, R, NH, W, seg);
+    } else {
+      ctx_pool_rows_kernel_v2<<<dim3(H, N), 256, smem, st>>>(static_cast<const __nv_bfloat16*>(fv), fv_plane, nsplit,
+                                                             cs, coff, R, H, W, seg, env_int("CAN_B200_DBG", 0));
+    }
   } else {
     ctx_pool_rows_kernel<<<dim3(H, N), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(fv), fv_plane, nsplit, cs, coff,
                                                      R, H, W);

@@ -301,4 +301,171 @@ ctx_pool_rows_kernel_v2(const __nv_bfloat16* __restrict__ fv, long long fv_plane
   }
 }
 
+// K1 stage A (third generation): persistent CTAs stream image rows through shared memory with TMA
+// (two 256-channel x kPoolChunk-pixel boxes per stage, kPoolStages stages), so ~160 KB per SM are in
+// flight at no register cost -- the register-staged versions above were latency-bound at 1.1 TB/s
+// (31 % warps active, long-scoreboard stalls; profiles/).
+//   warp 16      producer: runs ahead, throttled by the per-stage "empty" barriers
+//   warps 0-7    consumer set 0: even stages;   warps 8-15  consumer set 1: odd stages
+// In a consumer set thread t owns channels 2t, 2t+1: straight-line code over the 32 staged pixels
+// (independent 4-byte shared-memory reads, two running sums) that flushes the running sums into the
+// windows containing the current segment wherever a window boundary falls.  At the end of a row set 1
+// hands its 12 window sums to set 0 through shared memory (double-buffered, one named barrier per row).
+//   tm: bf16 map {512 ch, W, N*H, nsplit, 1}, box {256, kPoolChunk, 1, 1, 1}, no swizzle
+//   R[n][y][12][512] fp32
+constexpr int kPoolChunk = 32;    // pixels per stage (32 KB)
+constexpr int kPoolStages = 5;
+constexpr int kPoolXchgBytes = 2 * 12 * 512 * 4;   // set 1 -> set 0 hand-over, two rows
+__host__ __device__ inline int pool_rows_smem_bytes(int W) {
+  return kPoolStages * kPoolChunk * 1024 + kPoolXchgBytes + 8 * ((W + kPoolChunk - 1) / kPoolChunk) + 128;
+}
+__global__ void __launch_bounds__(544, 1)
+ctx_pool_rows_kernel_v3(const __grid_constant__ CUtensorMap tm, int nsplit, float* __restrict__ R, int NH, int W,
+                        const __grid_constant__ PoolSegments seg) {
+  extern __shared__ __align__(128) unsigned char s_raw[];
+  constexpr int kChunk = kPoolChunk, kStages = kPoolStages;
+  unsigned char* s_al = s_raw + ((128u - (smem_u32(s_raw) & 127u)) & 127u);   // TMA destinations: 128-byte aligned
+  __nv_bfloat16* buf = reinterpret_cast<__nv_bfloat16*>(s_al);  // [kStages][2 halves][kChunk][256]
+  float* s_xchg = reinterpret_cast<float*>(s_al + kStages * kChunk * 1024);                     // [2][12][512]
+  uint32_t* s_endmask = reinterpret_cast<uint32_t*>(s_al + kStages * kChunk * 1024 + kPoolXchgBytes);  // [chunks]
+  const int chunks_per_row = (W + kChunk - 1) / kChunk;
+  uint32_t* s_segstart = s_endmask + chunks_per_row;                                            // [chunks]
+  __shared__ uint64_t full_bar[kStages], empty_bar[kStages];
+  __shared__ unsigned short s_segmask[26];
+  if (threadIdx.x < 26) s_segmask[threadIdx.x] = threadIdx.x < seg.nseg ? seg.mask[threadIdx.x] : 0;
+  // bit p of s_endmask[c]: a segment ends after pixel c * kChunk + p;  s_segstart[c]: segment of its first pixel
+  for (int c = threadIdx.x; c < chunks_per_row; c += blockDim.x) {
+    uint32_t m = 0;
+    int first = 0;
+    for (int b = 1; b <= seg.nseg; ++b) {
+      const int e = seg.bound[b] - 1 - c * kChunk;
+      if (e >= 0 && e < kChunk) m |= 1u << e;
+      if (b < seg.nseg && seg.bound[b] <= c * kChunk) first = b;
+    }
+    s_endmask[c] = m;
+    s_segstart[c] = first;
+  }
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tm);
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 8);
+    }
+    fence_mbar_init();
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5;
+  if (warp == 16) {
+    // ---- producer
+    if (threadIdx.x == 512) {
+      int sg = 0;
+      uint32_t ph = 0;
+      for (int rowi = blockIdx.x; rowi < NH; rowi += gridDim.x)
+        for (int pl = 0; pl < nsplit; ++pl)
+          for (int ch = 0; ch < chunks_per_row; ++ch) {
+            mbar_wait(&empty_bar[sg], ph ^ 1u);
+            __nv_bfloat16* dst = buf + sg * kChunk * 512;
+            mbar_expect_tx(&full_bar[sg], kChunk * 1024u);
+            tma_load_5d(dst, &tm, &full_bar[sg], 0, ch * kChunk, rowi, pl, 0);
+            tma_load_5d(dst + kChunk * 256, &tm, &full_bar[sg], 256, ch * kChunk, rowi, pl, 0);
+            if (++sg == kStages) {
+              sg = 0;
+              ph ^= 1u;
+            }
+          }
+    }
+    return;
+  }
+  // ---- consumers
+  const int set = warp >> 3;                  // 0 or 1
+  const int tid = threadIdx.x & 255;
+  const int t2 = tid * 2;
+  const int soff = (tid >> 7) * kChunk * 256 + (tid & 127) * 2;
+  const int lane = threadIdx.x & 31;
+  float acc[12][2];
+  float cur0 = 0.f, cur1 = 0.f;   // running sums of segment sgi (may span stages)
+  int sgi = 0;
+  auto flush = [&]() {
+    const unsigned m = s_segmask[sgi];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+      if (m & (1u << k)) {
+        acc[k][0] += cur0;
+        acc[k][1] += cur1;
+      }
+    }
+    cur0 = cur1 = 0.f;
+  };
+  int sg = 0, it = 0, rowpar = 0;
+  uint32_t ph = 0;
+  for (int rowi = blockIdx.x; rowi < NH; rowi += gridDim.x, rowpar ^= 1) {
+#pragma unroll
+    for (int k = 0; k < 12; ++k) acc[k][0] = acc[k][1] = 0.f;
+    for (int pl = 0; pl < nsplit; ++pl)
+      for (int ch = 0; ch < chunks_per_row; ++ch, ++it) {
+        if ((it & 1) == set) {
+          const int first = static_cast<int>(s_segstart[ch]);
+          if (first != sgi) {   // the other set took the stages in between (or a new row / plane began)
+            flush();
+            sgi = first;
+          }
+          const uint32_t em = s_endmask[ch];
+          mbar_wait(&full_bar[sg], ph);
+          const __nv_bfloat16* b = buf + sg * kChunk * 512 + soff;
+          // pixels past W are zero-filled by TMA
+#pragma unroll
+          for (int g = 0; g < kChunk / 8; ++g) {
+            __nv_bfloat162 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = *reinterpret_cast<const __nv_bfloat162*>(b + (g * 8 + u) * 256);
+            if ((em >> (g * 8)) & 0xffu) {
+#pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                cur0 += __low2float(v[u]);
+                cur1 += __high2float(v[u]);
+                if (em & (1u << (g * 8 + u))) {
+                  flush();
+                  ++sgi;
+                }
+              }
+            } else {   // no boundary inside these 8 pixels
+              float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+              for (int u = 0; u < 8; u += 2) {
+                cur0 += __low2float(v[u]);
+                cur1 += __high2float(v[u]);
+                a0 += __low2float(v[u + 1]);
+                a1 += __high2float(v[u + 1]);
+              }
+              cur0 += a0;
+              cur1 += a1;
+            }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&empty_bar[sg]);   // this warp is done with the stage
+        }
+        if (++sg == kStages) {
+          sg = 0;
+          ph ^= 1u;
+        }
+      }
+    flush();   // (adds zeros when the row's last stage was this set's: its boundary bit already flushed)
+    // row finished: set 1 hands over, set 0 adds and writes the 12 window sums
+    float* xc = s_xchg + rowpar * 12 * 512 + t2;
+    if (set == 1) {
+#pragma unroll
+      for (int k = 0; k < 12; ++k) *reinterpret_cast<float2*>(xc + k * 512) = make_float2(acc[k][0], acc[k][1]);
+    }
+    asm volatile("bar.sync 1, 512;" ::: "memory");
+    if (set == 0) {
+      float* o = R + static_cast<long long>(rowi) * 12 * 512 + t2;
+#pragma unroll
+      for (int k = 0; k < 12; ++k) {
+        const float2 other = *reinterpret_cast<const float2*>(xc + k * 512);
+        *reinterpret_cast<float2*>(o + k * 512) = make_float2(acc[k][0] + other.x, acc[k][1] + other.y);
+      }
+    }
+  }
+}
+
 }  // namespace canb
