@@ -94,7 +94,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
   const uint32_t tmem_base = *tmem_ptr_smem;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int pid = patch_begin; pid < patch_end; ++pid) {
@@ -133,7 +133,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       uint32_t accum = 0;
