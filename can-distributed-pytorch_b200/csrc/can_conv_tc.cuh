@@ -455,6 +455,31 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const bool valid = (y < p.H) && (x < p.W);
     const uint32_t taddr = tmem_base + as * ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
 
+    // Operands of the epilogue that do not depend on the accumulator (ReLU mask / arg-max codes /
+    // upstream gradient of the first column group) are requested before waiting for the MMAs, and
+    // inside the column loops one group ahead, so their latency is off the critical path.
+    uint4 pre_m[4] = {};
+    uint4 pre_a[2] = {};
+    const __nv_bfloat16* pre_mbase = nullptr;
+    const uint8_t* pre_abase = nullptr;
+    if (MODE == MODE_STORE || MODE == MODE_UNPOOL || MODE == MODE_CTX2_BWD) {
+      const long long pix_ = valid ? (static_cast<long long>(n_img) * p.H + y) * p.W + x : 0;
+      if (p.mask && valid)
+        pre_mbase = p.mask + pix_ * p.mask_cs + p.mask_coff + (MODE == MODE_CTX2_BWD ? n_tile * 64 : n0 + cbeg);
+      if (MODE == MODE_UNPOOL && valid) pre_abase = p.arg + pix_ * p.arg_cs + n0 + cbeg;
+      if (pre_mbase) {
+        pre_m[0] = *reinterpret_cast<const uint4*>(pre_mbase);
+        if (MODE != MODE_CTX2_BWD) {
+#pragma unroll
+          for (int i = 1; i < 4; ++i) pre_m[i] = *reinterpret_cast<const uint4*>(pre_mbase + 8 * i);
+        }
+      }
+      if (pre_abase) {
+        pre_a[0] = *reinterpret_cast<const uint4*>(pre_abase);
+        pre_a[1] = *reinterpret_cast<const uint4*>(pre_abase + 16);
+      }
+    }
+
     mbar_wait(&tmem_full_bar[as], aphase);
     tc_fence_after();
 
@@ -477,10 +502,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         if (valid) {
           if (mbase) {
+            uint4 mcur[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) mcur[i] = pre_m[i];
+            if (c0 + 32 < cend) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) pre_m[i] = *reinterpret_cast<const uint4*>(mbase + c0 + 32 + 8 * i);
+            }
 #pragma unroll
             for (int i = 0; i < 32; i += 8) {
-              uint4 mq = *reinterpret_cast<const uint4*>(mbase + c0 + i);
-              const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mq);
+              const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mcur[i >> 3]);
 #pragma unroll
               for (int e = 0; e < 8; ++e)
                 if (!(__bfloat162float(mb[e]) > 0.f)) v[i + e] = 0.f;
@@ -569,16 +600,23 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int i = 0; i < 32; ++i) g[i] = 0.f;
         if (valid) {
           uint32_t code[8];
+          uint4 mcur[4];
           {
-            uint4 a0 = *reinterpret_cast<const uint4*>(abase + c0);
-            uint4 a1 = *reinterpret_cast<const uint4*>(abase + c0 + 16);
+            const uint4 a0 = pre_a[0], a1 = pre_a[1];
             code[0] = a0.x; code[1] = a0.y; code[2] = a0.z; code[3] = a0.w;
             code[4] = a1.x; code[5] = a1.y; code[6] = a1.z; code[7] = a1.w;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) mcur[i] = pre_m[i];
+            if (c0 + 32 < cend) {
+              pre_a[0] = *reinterpret_cast<const uint4*>(abase + c0 + 32);
+              pre_a[1] = *reinterpret_cast<const uint4*>(abase + c0 + 48);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) pre_m[i] = *reinterpret_cast<const uint4*>(mbase + c0 + 32 + 8 * i);
+            }
           }
 #pragma unroll
           for (int i = 0; i < 32; i += 8) {
-            uint4 mq = *reinterpret_cast<const uint4*>(mbase + c0 + i);
-            const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mq);
+            const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mcur[i >> 3]);
 #pragma unroll
             for (int e = 0; e < 8; ++e)
               g[i + e] = (__bfloat162float(mb[e]) > 0.f) ? r[i + e] : 0.f;
@@ -708,7 +746,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tmem_ld_wait();
         float g[8];
         {
-          const uint4 gq = *reinterpret_cast<const uint4*>(gbase + c0);
+          const uint4 gq = pre_m[0];
+          if (valid && c0 + 8 < 64) pre_m[0] = *reinterpret_cast<const uint4*>(gbase + c0 + 8);
           const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(&gq);
 #pragma unroll
           for (int e = 0; e < 8; ++e) g[e] = valid ? __bfloat162float(gb[e]) : 0.f;
