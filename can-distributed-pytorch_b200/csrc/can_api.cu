@@ -73,20 +73,25 @@ constexpr int kMaxSmem = 232448;  // 227 KB opt-in limit per CTA on sm_100
 // extra tensor maps of MODE_CTX2 (interpolation matrix, per-image tables); other modes pass copies of tmA
 thread_local const CUtensorMap* g_tmW = nullptr;
 thread_local const CUtensorMap* g_tmT = nullptr;
+// output map of the staged (TMA store) epilogue; null -> direct stores
+thread_local const CUtensorMap* g_tmO = nullptr;
+thread_local const CUtensorMap* g_tmM = nullptr;   // mask map of the staged epilogue
 
 template <int BN, int NSPLIT, int MODE>
 int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p, dim3 grid, int stages_override,
                 cudaStream_t st) {
   using L = ConvTcSmem<BN, gemm_planes(NSPLIT, MODE)>;
   const bool ctx = (MODE == MODE_CTX || MODE == MODE_CTX_BWD);
-  int stages = (kMaxSmem - L::bytes(0, ctx)) / L::kStageBytes;
+  const int staged_bytes = p.out_stage_bytes + p.mask_bufs * BN * 256;
+  int stages = (kMaxSmem - L::bytes(0, ctx) - staged_bytes) / L::kStageBytes;
   if (stages > 8) stages = 8;
   if (stages_override > 0 && stages_override < stages) stages = stages_override;
   if (stages < 2) return fail(-20, "conv_tc: tile BN=%d nsplit=%d does not fit shared memory", BN, NSPLIT);
   p.stages = stages;
-  const int smem = L::bytes(stages, ctx);
+  const int smem = L::bytes(stages, ctx) + staged_bytes;
   // eight epilogue warps for the narrow, epilogue-bound tiles of the bf16 path
-  constexpr int EW = (NSPLIT == 1 && BN <= 128 && (MODE == MODE_STORE || MODE == MODE_POOL || MODE == MODE_UNPOOL)) ? 8 : 4;
+  constexpr int EW = ((NSPLIT == 1 && BN <= 128 && (MODE == MODE_STORE || MODE == MODE_POOL || MODE == MODE_UNPOOL)) ||
+                      MODE == MODE_CTX2 || MODE == MODE_CTX2_BWD) ? 8 : 4;
   auto kern = conv_tc_kernel<BN, NSPLIT, MODE, 0, EW>;
   static bool attr_done = false;  // per template instantiation
   static int attr_smem = 0;
@@ -96,7 +101,8 @@ int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p,
     attr_done = true;
     attr_smem = kMaxSmem;
   }
-  kern<<<grid, 64 + 32 * EW, smem, st>>>(tmA, tmB, g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA, p);
+  kern<<<grid, 128 + 32 * EW, smem, st>>>(tmA, tmB, g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA, g_tmO ? *g_tmO : tmA,
+                                         g_tmM ? *g_tmM : tmA, p);
   CAN_CHECK_LAUNCH("conv_tc launch");
   return 0;
 }
@@ -107,11 +113,12 @@ int launch_conv_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUten
                      dim3 grid, cudaStream_t st) {
   using L = ConvTcSmem<BN, 1>;
   const int tail = L::kTailBytes;
-  int stages = (kMaxSmem - 1024 - p.w_bytes - tail) / p.halo_bytes;
+  const int staged_bytes = p.out_stage_bytes + p.mask_bufs * BN * 256;
+  int stages = (kMaxSmem - 1024 - staged_bytes - p.w_bytes - tail) / p.halo_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return fail(-20, "conv_tc(halo): BN=%d does not fit shared memory", BN);
   p.stages = stages;
-  const int smem = 1024 + p.w_bytes + stages * p.halo_bytes + tail;
+  const int smem = 1024 + staged_bytes + p.w_bytes + stages * p.halo_bytes + tail;
   auto kern = conv_tc_kernel<BN, 1, MODE, 1, 8>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -119,7 +126,7 @@ int launch_conv_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUten
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tc halo)");
     attr_done = true;
   }
-  kern<<<grid, 64 + 32 * 8, smem, st>>>(tmA, tmB, tmHalo, tmA, p);
+  kern<<<grid, 128 + 32 * 8, smem, st>>>(tmA, tmB, tmHalo, tmA, g_tmO ? *g_tmO : tmA, g_tmM ? *g_tmM : tmA, p);
   CAN_CHECK_LAUNCH("conv_tc(halo) launch");
   return 0;
 }
@@ -352,12 +359,48 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   const int ns = a->nsplit;
   g_tmW = nullptr;
   g_tmT = nullptr;
+  // bf16 path, narrow tiles: the epilogue is store-bound when every lane writes 16 bytes to its own
+  // line (measured 4-5 B/cycle/SM), so the tile is staged in shared memory and written by TMA
+  CUtensorMap tmO, tmM;
+  g_tmO = nullptr;
+  g_tmM = nullptr;
+  p.out_stage_bytes = 0;
+  p.mask_bufs = 0;
+  if (ns == 1 && a->mode == CAN_MODE_STORE && (bn == 64 || bn == 128) && a->out && env_int("CAN_B200_TMASTORE", 1) != 0) {
+    const uint64_t cs = static_cast<uint64_t>(a->out_cs) * 2;
+    const uint64_t dimsO[4] = {static_cast<uint64_t>(a->Cout), static_cast<uint64_t>(a->W), static_cast<uint64_t>(a->H),
+                               static_cast<uint64_t>(a->N)};
+    const uint64_t strO[3] = {cs, cs * a->W, cs * a->W * a->H};
+    const uint32_t boxO[4] = {64, static_cast<uint32_t>(p.TW), static_cast<uint32_t>(p.TH), 1};
+    int rc = make_tmap(&tmO, static_cast<__nv_bfloat16*>(a->out) + a->out_coff, 4, dimsO, strO, boxO);
+    if (rc) return rc;
+    g_tmO = &tmO;
+    p.out_stage_bytes = bn * 256;
+    if (a->mask && a->mask_cs % 8 == 0 && a->mask_coff % 8 == 0 && (reinterpret_cast<uintptr_t>(a->mask) & 15) == 0 &&
+        env_int("CAN_B200_TMAMASK", 1) != 0) {
+      const uint64_t mcs = static_cast<uint64_t>(a->mask_cs) * 2;
+      const uint64_t strM[3] = {mcs, mcs * a->W, mcs * a->W * a->H};
+      rc = make_tmap(&tmM, static_cast<const __nv_bfloat16*>(a->mask) + a->mask_coff, 4, dimsO, strM, boxO);
+      if (rc) return rc;
+      g_tmM = &tmM;
+      p.mask_bufs = env_int("CAN_B200_MASKBUFS", bn == 64 ? 2 : 1);
+    }
+  }
   // small-Cin layers on the bf16 path: resident weights + halo stages (L2->SM traffic / 3.6)
   if (ns == 1 && a->taps == 9 && p.n_tiles == 1 && (bn == 64 || bn == 128) &&
       (a->mode == CAN_MODE_STORE || a->mode == CAN_MODE_POOL || a->mode == CAN_MODE_UNPOOL) &&
       9 * p.kchunks * bn * 128 <= 147456 && env_int("CAN_B200_HALO", 1) != 0) {
     p.w_bytes = 9 * p.kchunks * bn * 128;
     p.halo_bytes = (p.TH + 2 * a->dil) * p.TW * 128;
+    // staged output only while at least two halo stages still fit beside the resident weights
+    while (p.mask_bufs > 0 &&
+           1024 + p.out_stage_bytes + p.mask_bufs * bn * 256 + p.w_bytes + 2 * p.halo_bytes + 8192 > kMaxSmem)
+      --p.mask_bufs;
+    if (!p.mask_bufs) g_tmM = nullptr;
+    if (p.out_stage_bytes && 1024 + p.out_stage_bytes + p.w_bytes + 2 * p.halo_bytes + 8192 > kMaxSmem) {
+      p.out_stage_bytes = 0;
+      g_tmO = nullptr;
+    }
     CUtensorMap tmH;
     int rc = make_act_tmap(&tmH, a->x, a->x_coff, a->Cin, a->x_cs, a->x_plane, 1, a->N, a->H, a->W, p.TW,
                            p.TH + 2 * a->dil);

@@ -43,6 +43,8 @@ struct ConvTcParams {
   int dbg;             // CAN_B200_DBG bit flags (bring-up experiments only; 0 in production)
   int w_bytes;         // HALO: bytes of the resident weight region (9 * kchunks * BN * 128)
   int halo_bytes;      // HALO: bytes of one activation stage ((TH + 2 dil) * TW * 128)
+  int out_stage_bytes; // > 0: the epilogue stages the bf16 tile in shared memory (BN * 256 B) and writes it with TMA (tmO)
+  int mask_bufs;       // staged epilogue: 0 = mask read from global memory, 1|2 = mask tiles (BN * 256 B each) brought in by TMA (tmM)
   int relu;
   const float* bias;   // [Cout] or null
   // primary output, NHWC bf16 planes
@@ -205,16 +207,20 @@ __device__ __forceinline__ float rcp_fast(float x) {
 // bound; for narrow tiles (small K) it is the critical path, so EW = 8 lets two warps share each TMEM
 // lane quarter, each taking half of the BN columns.
 template <int BN, int NSPLIT, int MODE, int HALO = 0, int EW = 4>
-__global__ void __launch_bounds__(64 + 32 * EW, 1)
+__global__ void __launch_bounds__(128 + 32 * EW, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmT,
+               const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmM,
                const ConvTcParams p) {
   constexpr int GS = gemm_planes(NSPLIT, MODE);  // planes that enter the GEMM
   using L = ConvTcSmem<BN, GS>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int stages = p.stages;
-  uint8_t* ring = HALO ? smem + p.w_bytes : smem;                 // stage ring (after the resident weights)
+  uint8_t* s_out = smem;                                           // staged output tile (p.out_stage_bytes, 1024-aligned)
+  uint8_t* s_mask = smem + p.out_stage_bytes;                       // staged mask tiles (p.mask_bufs x BN * 256 B)
+  uint8_t* wbase = s_mask + p.mask_bufs * (BN * 256);               // HALO: resident weights
+  uint8_t* ring = HALO ? wbase + p.w_bytes : wbase;                // stage ring
   const int stage_bytes = HALO ? p.halo_bytes : L::kStageBytes;
   uint8_t* tail = ring + stages * stage_bytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
@@ -222,7 +228,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tmem_full_bar = empty_bar + 8;    // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;  // [2]
   uint64_t* w_bar = tmem_empty_bar + 2;          // HALO: resident weights landed
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(w_bar + 1);
+  uint64_t* out_free_bar = w_bar + 1;            // staged output: the previous tile's TMA store has read s_out
+  uint64_t* out_full_bar = out_free_bar + 1;     // staged output: every epilogue thread has written its part of s_out
+  uint64_t* mask_full_bar = out_full_bar + 1;    // [2] staged mask tile landed
+  uint64_t* mask_free_bar = mask_full_bar + 2;   // [2] every epilogue thread is done with it
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(mask_free_bar + 2);
   float* s_bias2 = reinterpret_cast<float*>(tail + 1024);  // [2][BN]
   float* s_db = s_bias2 + 2 * BN;   // [<=1024] per-CTA partial bias gradient (p.db)
   float* s_tab = s_db + 1024;       // MODE_CTX / MODE_CTX_BWD only: [2][50][64]
@@ -256,6 +266,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tma_prefetch_desc(&tmW);
       tma_prefetch_desc(&tmT);
     }
+    if (p.out_stage_bytes) tma_prefetch_desc(&tmO);
+    if (p.mask_bufs) tma_prefetch_desc(&tmM);
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -268,6 +280,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_init(&tmem_empty_bar[a], 32 * EW);  // every epilogue thread arrives
       }
       mbar_init(w_bar, 1);
+      mbar_init(out_free_bar, 1);
+      mbar_init(out_full_bar, 32 * EW);
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&mask_full_bar[a], 1);
+        mbar_init(&mask_free_bar[a], 32 * EW);
+      }
       fence_mbar_init();
     }
     __syncwarp();
@@ -287,7 +305,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (HALO) {
         // resident weights: every (tap, chunk) tile of this CTA's BN output channels, once
         mbar_expect_tx(w_bar, static_cast<uint32_t>(p.w_bytes));
-        for (int kb = 0; kb < base_kb; ++kb) tma_load_3d(smem + kb * L::kBBytes, &tmB, w_bar, kb * 64, 0, 0);
+        for (int kb = 0; kb < base_kb; ++kb) tma_load_3d(wbase + kb * L::kBBytes, &tmB, w_bar, kb * 64, 0, 0);
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
           CAN_TILE_DECODE(tile)
           (void)n0;
@@ -316,7 +334,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             dy = (tap / 3 - 1) * p.dil;
             dx = (tap % 3 - 1) * p.dil;
           }
-          uint8_t* sa = smem + stage * L::kStageBytes;
+          uint8_t* sa = ring + stage * L::kStageBytes;
           uint8_t* sb = sa + GS * L::kABytes;
           mbar_expect_tx(&full_bar[stage], L::kStageBytes);
           if (kCtx2 && kb >= base_kb) {
@@ -353,7 +371,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint32_t used = 0;  // bit a: accumulator a already holds a partial sum
         if (HALO) {
           if (it == 0) mbar_wait(w_bar, 0);
-          const uint64_t wdesc0 = umma_smem_desc(smem_u32(smem), 16, 1024);
+          const uint64_t wdesc0 = umma_smem_desc(smem_u32(wbase), 16, 1024);
           const uint32_t dy_bytes = static_cast<uint32_t>(p.dil * p.TW * 128);
           const uint32_t tap_row_units = static_cast<uint32_t>((3 * p.kchunks * L::kBBytes) >> 4);  // dy -> dy+1
           uint32_t accum = 0;
@@ -386,7 +404,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
+          const uint32_t sa = smem_u32(ring + stage * L::kStageBytes);
           const uint64_t da0 = umma_smem_desc(sa, 16, 1024);                       // one descriptor pair per
           const uint64_t db0 = umma_smem_desc(sa + GS * L::kABytes, 16, 1024);     // stage (see HALO note)
 #pragma unroll
@@ -416,8 +434,39 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         umma_commit(&tmem_full_bar[as]);  // accumulator of this tile complete
       }
     }
+  } else if (warp == 2 + EW) {
+    // ===================== output warp (staged epilogue only) =====================
+    // hands each staged tile to TMA and waits until it has been read, so no epilogue warp ever stalls on that
+    if (p.out_stage_bytes && elect_one()) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        CAN_TILE_DECODE(tile)
+        mbar_wait(out_full_bar, static_cast<uint32_t>(it) & 1u);
+#pragma unroll
+        for (int blk = 0; blk < BN / 64; ++blk) tma_store_4d(&tmO, s_out + blk * 16384, n0 + blk * 64, x0, y0, n_img);
+        bulk_commit_group();
+        bulk_wait_group_read0();
+        mbar_arrive(out_free_bar);
+      }
+    }
+  } else if (warp == 3 + EW) {
+    // ===================== mask warp (staged epilogue only) =====================
+    // brings the ReLU-mask tile of each output tile into shared memory, as far ahead as the buffers allow
+    if (p.mask_bufs && elect_one()) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        CAN_TILE_DECODE(tile)
+        const int b = it % p.mask_bufs;
+        const uint32_t ph = static_cast<uint32_t>(it / p.mask_bufs) & 1u;
+        mbar_wait(&mask_free_bar[b], ph ^ 1u);
+        mbar_expect_tx(&mask_full_bar[b], BN * 256);
+#pragma unroll
+        for (int blk = 0; blk < BN / 64; ++blk)
+          tma_load_4d(s_mask + b * (BN * 256) + blk * 16384, &tmM, &mask_full_bar[b], n0 + blk * 64, x0, y0, n_img);
+      }
+    }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
+    // ===================== epilogue (warps 2 .. 2+EW-1) =====================
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     const int etid = threadIdx.x - 64;
     const int m = q * 32 + lane;
@@ -430,6 +479,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int i = etid; i < 1024; i += 32 * EW) s_db[i] = 0.f;
       asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
     }
+    // bias gradient of narrow single-n-tile layers: every thread keeps the column sums of its own pixels in
+    // registers over all tiles; the cross-lane reduction happens once per kernel instead of once per tile
+    constexpr bool kDbRegMode = (CW == 32) && (MODE == MODE_STORE || MODE == MODE_UNPOOL);
+    const bool db_reg = kDbRegMode && p.db && p.n_tiles == 1;
+    float dbacc[kDbRegMode ? 32 : 1];
+#pragma unroll
+    for (int i = 0; i < (kDbRegMode ? 32 : 1); ++i) dbacc[i] = 0.f;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
     CAN_TILE_DECODE(tile)
@@ -464,8 +520,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const uint8_t* pre_abase = nullptr;
     if (MODE == MODE_STORE || MODE == MODE_UNPOOL || MODE == MODE_CTX2_BWD) {
       const long long pix_ = valid ? (static_cast<long long>(n_img) * p.H + y) * p.W + x : 0;
-      if (p.mask && valid)
-        pre_mbase = p.mask + pix_ * p.mask_cs + p.mask_coff + (MODE == MODE_CTX2_BWD ? n_tile * 64 : n0 + cbeg);
+      if (p.mask && valid && !p.mask_bufs)
+        pre_mbase = p.mask + pix_ * p.mask_cs + p.mask_coff +
+                    (MODE == MODE_CTX2_BWD ? n_tile * 64 + ((warp - 2) >> 2) * (64 / (EW / 4)) : n0 + cbeg);
       if (MODE == MODE_UNPOOL && valid) pre_abase = p.arg + pix_ * p.arg_cs + n0 + cbeg;
       if (pre_mbase) {
         pre_m[0] = *reinterpret_cast<const uint4*>(pre_mbase);
@@ -483,11 +540,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     mbar_wait(&tmem_full_bar[as], aphase);
     tc_fence_after();
 
+    const bool kStaged = (MODE == MODE_STORE) && NSPLIT == 1 && BN <= 128 && p.out_stage_bytes > 0;
+    if (kStaged) mbar_wait(out_free_bar, static_cast<uint32_t>(it & 1) ^ 1u);  // previous tile's store has read s_out
+    const bool kMaskStaged = kStaged && p.mask_bufs > 0;
+    const int mb_i = kMaskStaged ? it % p.mask_bufs : 0;
+    if (kMaskStaged) mbar_wait(&mask_full_bar[mb_i], static_cast<uint32_t>(it / p.mask_bufs) & 1u);
+
     if (p.dbg & 16) {
       // bring-up experiment: no epilogue work at all
     } else if (MODE == MODE_STORE) {
       const long long pix = (static_cast<long long>(n_img) * p.H + y) * p.W + x;
-      __nv_bfloat16* obase = p.out + pix * p.out_cs + p.out_coff + n0;
+      __nv_bfloat16* obase = p.out + ((p.dbg & 32) ? (pix & 0xfff) : pix) * p.out_cs + p.out_coff + n0;
       const __nv_bfloat16* mbase = p.mask ? p.mask + pix * p.mask_cs + p.mask_coff + n0 : nullptr;
       float* fbase = p.out_f32 ? p.out_f32 + pix * p.out_cs + p.out_coff + n0 : nullptr;
 #pragma unroll 1
@@ -503,11 +566,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (valid) {
           if (mbase) {
             uint4 mcur[4];
+            if (kMaskStaged) {
+              const uint8_t* mrow = s_mask + mb_i * (BN * 256) + (c0 >> 6) * 16384 + m * 128;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) mcur[i] = pre_m[i];
-            if (c0 + 32 < cend) {
+              for (int i = 0; i < 4; ++i)
+                mcur[i] = *reinterpret_cast<const uint4*>(mrow + (((((c0 & 63) >> 3) + i) ^ (m & 7)) << 4));
+            } else {
 #pragma unroll
-              for (int i = 0; i < 4; ++i) pre_m[i] = *reinterpret_cast<const uint4*>(mbase + c0 + 32 + 8 * i);
+              for (int i = 0; i < 4; ++i) mcur[i] = pre_m[i];
+              if (c0 + 32 < cend) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) pre_m[i] = *reinterpret_cast<const uint4*>(mbase + c0 + 32 + 8 * i);
+              }
             }
 #pragma unroll
             for (int i = 0; i < 32; i += 8) {
@@ -517,14 +587,32 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (!(__bfloat162float(mb[e]) > 0.f)) v[i + e] = 0.f;
             }
           }
-          if (p.out) store_bf16_planes<NSPLIT, 32>(obase + c0, p.out_plane, v);
+          if (kStaged) {
+            // 16-byte chunks into the 128B-swizzled [64-ch block][pixel][64 ch] staging tile
+            uint8_t* row = s_out + (c0 >> 6) * 16384 + m * 128;
+#pragma unroll
+            for (int i = 0; i < 32; i += 8) {
+              uint4 q;
+              q.x = pack_bf16x2(v[i], v[i + 1]);
+              q.y = pack_bf16x2(v[i + 2], v[i + 3]);
+              q.z = pack_bf16x2(v[i + 4], v[i + 5]);
+              q.w = pack_bf16x2(v[i + 6], v[i + 7]);
+              const int chunk = ((c0 & 63) + i) >> 3;
+              *reinterpret_cast<uint4*>(row + ((chunk ^ (m & 7)) << 4)) = q;
+            }
+          } else if (p.out) {
+            store_bf16_planes<NSPLIT, 32>(obase + c0, p.out_plane, v);
+          }
           if (fbase) {
 #pragma unroll
             for (int i = 0; i < 32; i += 4)
               *reinterpret_cast<float4*>(fbase + c0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
           }
         }
-        if (p.db) {
+        if (kDbRegMode && db_reg) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) dbacc[kDbRegMode ? i : 0] += valid ? v[i] : 0.f;
+        } else if (p.db) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = valid ? v[i] : 0.f;
           atomicAdd(&s_db[n0 + c0 + lane], warp_column_sums(v, lane));
@@ -634,7 +722,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             store_bf16_planes<NSPLIT, 32>(p.out + opix * p.out_cs + p.out_coff + n0 + c0, p.out_plane, v);
           }
         }
-        if (p.db) atomicAdd(&s_db[n0 + c0 + lane], warp_column_sums(g, lane));
+        if (kDbRegMode && db_reg) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) dbacc[kDbRegMode ? i : 0] += g[i];
+        } else if (p.db) {
+          atomicAdd(&s_db[n0 + c0 + lane], warp_column_sums(g, lane));
+        }
       }
     } else if (MODE == MODE_CTX) {
       // BN == 256 columns = 4 scales x 64 channels of n-tile blockIdx.y; column j*64+c holds
@@ -705,8 +798,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // column j*64 + c for the 64 channels of n-tile blockIdx.y.  w_j = sigmoid(z_j) = 1/(1+exp(-z_j)).
       const long long pix = valid ? (static_cast<long long>(n_img) * p.H + y) * p.W + x : 0;
       __nv_bfloat16* obase = p.out + pix * p.out_cs + p.out_coff + n_tile * 64;
+      constexpr int CH = 64 / (EW / 4);              // channels of the n-tile handled by this warp
+      const int hb = ((warp - 2) >> 2) * CH;
 #pragma unroll 1
-      for (int c0 = 0; c0 < 64; c0 += 16) {
+      for (int c0 = hb; c0 < hb + CH; c0 += 16) {
         uint32_t zr[4][16], sr[4][16];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -735,8 +830,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const long long pix = valid ? (static_cast<long long>(n_img) * p.H + y) * p.W + x : 0;
       __nv_bfloat16* obase = p.out + pix * p.out_cs + n_tile * 64;
       const __nv_bfloat16* gbase = p.mask + pix * p.mask_cs + p.mask_coff + n_tile * 64;
+      constexpr int CH = 64 / (EW / 4);              // channels of the n-tile handled by this warp
+      const int hb = ((warp - 2) >> 2) * CH;
 #pragma unroll 1
-      for (int c0 = 0; c0 < 64; c0 += 8) {
+      for (int c0 = hb; c0 < hb + CH; c0 += 8) {
         uint32_t zr[4][8], sr[4][8];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -747,7 +844,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         float g[8];
         {
           const uint4 gq = pre_m[0];
-          if (valid && c0 + 8 < 64) pre_m[0] = *reinterpret_cast<const uint4*>(gbase + c0 + 8);
+          if (valid && c0 + 8 < hb + CH) pre_m[0] = *reinterpret_cast<const uint4*>(gbase + c0 + 8);
           const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(&gq);
 #pragma unroll
           for (int e = 0; e < 8; ++e) g[e] = valid ? __bfloat162float(gb[e]) : 0.f;
@@ -959,7 +1056,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // this accumulator stage may be overwritten by the MMAs of the tile after next
     tc_fence_before();
     mbar_arrive(&tmem_empty_bar[as]);
+    if (kStaged) {
+      // generic-proxy writes of s_out -> visible to the async proxy, then tell the output warp
+      // (out-of-image pixels of edge tiles are clipped by the tensor map)
+      fence_proxy_async();
+      mbar_arrive(out_full_bar);
+      if (kMaskStaged) mbar_arrive(&mask_free_bar[mb_i]);
+    }
     }  // tile loop
+    if (kDbRegMode && db_reg) atomicAdd(&s_db[cbeg + lane], warp_column_sums(dbacc, lane));
     if (p.db) {
       asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
       const int cout = p.n_tiles * BN;

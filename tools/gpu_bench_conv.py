@@ -24,6 +24,14 @@ def main():
 
         def run():
             ops.conv_tc(x, wp, Cout, dil=dil, mode=ops.MODE_POOL, bias=b, out=out, arg=arg)
+    elif mode.startswith("dgrad"):
+        out = ops.new_act(1, N, H, W, Cout, dev)
+        mask = ops.new_act(1, N, H, W, Cout, dev, zero=True)
+        mask.buf.normal_()
+        db = torch.zeros(Cin, device=dev) if mode == "dgraddb" else None
+
+        def run():
+            ops.conv_tc(x, wp, Cout, dil=dil, mode=ops.MODE_STORE, relu=False, out=out, mask=mask, db=db)
     else:
         out = ops.new_act(1, N, H, W, Cout, dev)
 
@@ -40,7 +48,7 @@ def main():
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 10
     tag = " ".join(f"{k[9:]}={os.environ[k]}" for k in ("CAN_B200_DBG", "CAN_B200_HALO", "CAN_B200_CTAS", "CAN_B200_STAGES",
-                                                       "CAN_B200_BN") if k in os.environ)
+                                                       "CAN_B200_BN", "CAN_B200_TMASTORE") if k in os.environ)
     print(f"{Cin}->{Cout} {H}x{W} N={N} {mode} [{tag}]: {ms * 1e3:.1f} us  ({2 * 9 * Cin * Cout * N * H * W / ms / 1e9:.0f} TF)")
 
 
