@@ -156,7 +156,7 @@ int dispatch_mode(int mode, const CUtensorMap& a, const CUtensorMap& b, ConvTcPa
 
 
 struct WgradPlan {
-  int TW, TH, tiles_x, tiles_y, total_patches, m_tiles, n_tiles, bn, ksplit, per, T, tap_groups;
+  int TW, TH, tiles_x, tiles_y, total_patches, m_tiles, n_tiles, bn, ksplit, per, T, tap_groups, swap64;
 };
 WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nsplit) {
   WgradPlan pl;
@@ -173,6 +173,15 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   pl.T = (nsplit == 1 && taps > 1) ? (pl.bn == 64 ? 3 : pl.bn == 128 ? 3 : 2) : 1;
   if (pl.T > taps) pl.T = taps;
   pl.tap_groups = (taps + pl.T - 1) / pl.T;
+  // 64 -> 64 3x3 (bf16 path): operand roles swapped, all nine taps in one CTA (wgrad_tc_swap64_kernel)
+  pl.swap64 = (nsplit == 1 && taps == 9 && Cin == 64 && Cout == 64 && env_int("CAN_B200_WGSWAP", 1) != 0) ? 1 : 0;
+  if (pl.swap64) {
+    pl.tap_groups = 1;
+    int ks = pl.total_patches < 148 ? pl.total_patches : 148;
+    pl.per = (pl.total_patches + ks - 1) / ks;
+    pl.ksplit = (pl.total_patches + pl.per - 1) / pl.per;
+    return pl;
+  }
   const int tiles = pl.m_tiles * pl.n_tiles * pl.tap_groups;
   // split-K factor from a two-term cost model: MMA time at the wave efficiency of tiles*c CTAs on
   // 148 SMs (one CTA per SM) + the fp32 partial tiles every split writes and the reduction re-reads
@@ -750,6 +759,22 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
   p.ws = static_cast<float*>(ws);
   p.tap_groups = pl.tap_groups;
   dim3 grid(pl.m_tiles * pl.n_tiles * pl.tap_groups, pl.ksplit);
+  if (pl.swap64) {
+    using L = WgradSwapSmem;
+    p.stages = (kMaxSmem - L::bytes(0)) / L::kStageBytes;   // 2
+    static bool attr_done = false;
+    if (!attr_done) {
+      cudaError_t e = cudaFuncSetAttribute(wgrad_tc_swap64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
+      if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(wgrad_tc_swap64)");
+      attr_done = true;
+    }
+    wgrad_tc_swap64_kernel<<<pl.ksplit, 192, L::bytes(p.stages), st>>>(tmDZ, tmX, p);
+    CAN_CHECK_LAUNCH("wgrad_tc_swap64 launch");
+    wgrad_reduce_kernel_t<<<dim3(Cout / 32, Cin), 32 * taps, 0, st>>>(p.ws, grad, pl.ksplit, taps, Cout, Cin, accumulate,
+                                                                      alpha);
+    CAN_CHECK_LAUNCH("wgrad_reduce_t");
+    return 0;
+  }
   if (pl.T > 1) {  // bf16 path, several taps per CTA
     if (pl.bn == 64) rc = launch_wgrad<64, 1, 3>(tmDZ, tmX, p, grid, st);
     else if (pl.bn == 128) rc = launch_wgrad<128, 1, 3>(tmDZ, tmX, p, grid, st);

@@ -225,4 +225,171 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
   }
 }
 
+// Weight gradient of a 64 -> 64 3x3 layer (bf16 path), operand roles swapped.
+//
+// With M = Cout = 64 the kernel above spends half of every M = 128 MMA on padding and needs three
+// CTAs (tap groups) that each re-read the dZ patch.  Here the nine shifted X patches are the A
+// operand: two taps (2 x 64 input channels, consecutive 8 KB tiles in shared memory = the two
+// 64-channel groups of an MN-major M = 128 operand) per MMA, dZ (N = 64 output channels) is B,
+//   D_pair[(tap, ci)][co] += X_tap[pixel][ci]^T dZ[pixel][co]
+// so all nine taps (five pair accumulators, 320 TMEM columns) live in one CTA, every MMA row is
+// useful (the ninth tap's partner rows are ignored), and a patch costs one dZ + nine X tiles.
+// Partial results go to ws[split][tap][ci][co] (note: ci before co), reduced by wgrad_reduce_kernel_t.
+struct WgradSwapSmem {
+  static constexpr int kTile = 64 * 128;                  // 64 pixels x 64 ch x bf16
+  static constexpr int kStageBytes = 10 * kTile;          // dZ + 9 X tiles
+  static __host__ __device__ constexpr int bytes(int stages) { return 1024 + stages * kStageBytes + 1024; }
+};
+
+__global__ void __launch_bounds__(192, 1)
+wgrad_tc_swap64_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant__ CUtensorMap tmX,
+                       const WgradTcParams p) {
+  using L = WgradSwapSmem;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int stages = p.stages;
+  uint8_t* tail = smem + stages * L::kStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
+  uint64_t* empty_bar = full_bar + 8;
+  uint64_t* tmem_full_bar = empty_bar + 8;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int split = blockIdx.x;
+  const int patch_begin = split * p.patches_per_split;
+  const int patch_end = min(patch_begin + p.patches_per_split, p.total_patches);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmDZ);
+    tma_prefetch_desc(&tmX);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < stages; ++s) {
+        mbar_init(&full_bar[s], 1);
+        mbar_init(&empty_bar[s], 1);
+      }
+      mbar_init(tmem_full_bar, 1);
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_ptr_smem, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int pid = patch_begin; pid < patch_end; ++pid) {
+        int q = pid;
+        const int tx_i = q % p.tiles_x;
+        q /= p.tiles_x;
+        const int ty_i = q % p.tiles_y;
+        const int n_img = q / p.tiles_y;
+        const int x0 = tx_i * p.TW, y0 = ty_i * p.TH;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sx = smem + stage * L::kStageBytes;   // 9 X tiles, then dZ
+        mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap)
+          tma_load_5d(sx + tap * L::kTile, &tmX, &full_bar[stage], 0, x0 + (tap % 3 - 1) * p.dil,
+                      y0 + (tap / 3 - 1) * p.dil, n_img, 0);
+        tma_load_5d(sx + 9 * L::kTile, &tmDZ, &full_bar[stage], 0, x0, y0, n_img, 0);
+        if (++stage == stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t accum = 0;
+      for (int pid = patch_begin; pid < patch_end; ++pid) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sx = smem_u32(smem + stage * L::kStageBytes);
+        const uint64_t da0 = umma_smem_desc(sx, L::kTile, 1024);                 // 64-channel groups = taps, 8 KB apart
+        const uint64_t db0 = umma_smem_desc(sx + 9 * L::kTile, L::kTile, 1024);
+#pragma unroll
+        for (int pair = 0; pair < 5; ++pair) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)   // 16 pixels per MMA
+            umma_bf16(tmem_base + pair * 64, da0 + ((pair * 2 * L::kTile + k * 2048) >> 4), db0 + ((k * 2048) >> 4),
+                      idesc, (accum | k) ? 1u : 0u);
+        }
+        accum = 1;
+        umma_commit(&empty_bar[stage]);
+        if (++stage == stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit(tmem_full_bar);
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;            // (tap within pair, ci)
+    const int unit = row >> 6, ci = row & 63;
+    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const bool any = patch_end > patch_begin;
+#pragma unroll 1
+    for (int pair = 0; pair < 5; ++pair) {
+      const int tap = pair * 2 + unit;
+      float* dst = p.ws + ((static_cast<long long>(split) * 9 + tap) * 64 + ci) * 64;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 64; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + pair * 64 + c0, r);
+        tmem_ld_wait();
+        if (tap < 9 && any) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 4)
+            *reinterpret_cast<float4*>(dst + c0 + i) = make_float4(__uint_as_float(r[i]), __uint_as_float(r[i + 1]),
+                                                                   __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// grad[co][ci][tap] = (accumulate ? grad : 0) + alpha * sum_s ws[s][tap][ci][co]   (ws of wgrad_tc_swap64_kernel)
+// grid (cout/32, cin), block 32*taps
+__global__ void wgrad_reduce_kernel_t(const float* __restrict__ ws, float* __restrict__ grad, int splits, int taps,
+                                      int cout, int cin, int accumulate, float alpha) {
+  __shared__ float s_t[32 * 9];
+  const int ci = blockIdx.y, co0 = blockIdx.x * 32;
+  const int c = threadIdx.x & 31, tap = threadIdx.x >> 5;
+  const long long slab = static_cast<long long>(taps) * cout * cin;
+  const float* src = ws + (static_cast<long long>(tap) * cin + ci) * cout + co0 + c;
+  float acc = 0.f;
+  int sp = 0;
+  for (; sp + 4 <= splits; sp += 4) {
+    const float a0 = src[(sp + 0) * slab], a1 = src[(sp + 1) * slab], a2 = src[(sp + 2) * slab],
+                a3 = src[(sp + 3) * slab];
+    acc += (a0 + a1) + (a2 + a3);
+  }
+  for (; sp < splits; ++sp) acc += src[sp * slab];
+  s_t[c * taps + tap] = acc;
+  __syncthreads();
+  const int co = co0 + threadIdx.x / taps, tp = threadIdx.x % taps;
+  float* g = grad + (static_cast<long long>(co) * cin + ci) * taps + tp;
+  *g = (accumulate ? *g : 0.f) + alpha * s_t[threadIdx.x];
+}
+
 }  // namespace canb
