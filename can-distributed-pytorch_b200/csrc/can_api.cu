@@ -761,14 +761,19 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
   dim3 grid(pl.m_tiles * pl.n_tiles * pl.tap_groups, pl.ksplit);
   if (pl.swap64) {
     using L = WgradSwapSmem;
-    p.stages = (kMaxSmem - L::bytes(0)) / L::kStageBytes;   // 2
+    rc = make_act_tmap(&tmX, x, x_coff, Cin, x_cs, x_plane, nsplit, N, H, W, pl.TW, pl.TH + 2 * dil);   // halo tile
+    if (rc) return rc;
+    const int stage_b = 3 * (pl.TH + 2 * dil) * pl.TW * 128 + L::kTile;
+    p.stages = (kMaxSmem - 2048) / stage_b;
+    if (p.stages > 8) p.stages = 8;
+    if (p.stages < 2) return fail(-20, "wgrad_tc_swap64: dil=%d does not fit shared memory", dil);
     static bool attr_done = false;
     if (!attr_done) {
       cudaError_t e = cudaFuncSetAttribute(wgrad_tc_swap64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
       if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(wgrad_tc_swap64)");
       attr_done = true;
     }
-    wgrad_tc_swap64_kernel<<<pl.ksplit, 192, L::bytes(p.stages), st>>>(tmDZ, tmX, p);
+    wgrad_tc_swap64_kernel<<<pl.ksplit, 192, 2048 + p.stages * stage_b, st>>>(tmDZ, tmX, p);
     CAN_CHECK_LAUNCH("wgrad_tc_swap64 launch");
     wgrad_reduce_kernel_t<<<dim3(Cout / 32, Cin), 32 * taps, 0, st>>>(p.ws, grad, pl.ksplit, taps, Cout, Cin, accumulate,
                                                                       alpha);

@@ -235,10 +235,14 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
 // so all nine taps (five pair accumulators, 320 TMEM columns) live in one CTA, every MMA row is
 // useful (the ninth tap's partner rows are ignored), and a patch costs one dZ + nine X tiles.
 // Partial results go to ws[split][tap][ci][co] (note: ci before co), reduced by wgrad_reduce_kernel_t.
+// The X patches of the three taps that share a column shift dx are row-shifted views of ONE halo
+// tile ((TH + 2 dil) rows, row = TW pixels = a multiple of 1024 B, so the swizzle phase is kept):
+// a stage holds three halo tiles + the dZ patch (44 KB for dil = 1) instead of ten 8 KB tiles.
 struct WgradSwapSmem {
   static constexpr int kTile = 64 * 128;                  // 64 pixels x 64 ch x bf16
-  static constexpr int kStageBytes = 10 * kTile;          // dZ + 9 X tiles
-  static __host__ __device__ constexpr int bytes(int stages) { return 1024 + stages * kStageBytes + 1024; }
+  static __host__ __device__ constexpr int halo_bytes(int dil) { return (64 + 2 * dil * 16) * 128; }  // TW*TH == 64, TW <= 16
+  static __host__ __device__ constexpr int stage_bytes(int dil) { return 3 * halo_bytes(dil) + kTile; }
+  static __host__ __device__ constexpr int bytes(int stages, int dil) { return 1024 + stages * stage_bytes(dil) + 1024; }
 };
 
 __global__ void __launch_bounds__(192, 1)
@@ -248,7 +252,10 @@ wgrad_tc_swap64_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_co
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int stages = p.stages;
-  uint8_t* tail = smem + stages * L::kStageBytes;
+  const int row_bytes = p.TW * 128;                       // one patch row (1024 or 2048 B)
+  const int halo_bytes = (p.TH + 2 * p.dil) * row_bytes;
+  const int stage_bytes = 3 * halo_bytes + L::kTile;
+  uint8_t* tail = smem + stages * stage_bytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
   uint64_t* empty_bar = full_bar + 8;
   uint64_t* tmem_full_bar = empty_bar + 8;
@@ -293,13 +300,12 @@ wgrad_tc_swap64_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_co
         const int n_img = q / p.tiles_y;
         const int x0 = tx_i * p.TW, y0 = ty_i * p.TH;
         mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sx = smem + stage * L::kStageBytes;   // 9 X tiles, then dZ
-        mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+        uint8_t* sx = smem + stage * stage_bytes;   // 3 halo tiles (dx = -dil, 0, +dil), then dZ
+        mbar_expect_tx(&full_bar[stage], static_cast<uint32_t>(stage_bytes));
 #pragma unroll
-        for (int tap = 0; tap < 9; ++tap)
-          tma_load_5d(sx + tap * L::kTile, &tmX, &full_bar[stage], 0, x0 + (tap % 3 - 1) * p.dil,
-                      y0 + (tap / 3 - 1) * p.dil, n_img, 0);
-        tma_load_5d(sx + 9 * L::kTile, &tmDZ, &full_bar[stage], 0, x0, y0, n_img, 0);
+        for (int dxi = 0; dxi < 3; ++dxi)
+          tma_load_5d(sx + dxi * halo_bytes, &tmX, &full_bar[stage], 0, x0 + (dxi - 1) * p.dil, y0 - p.dil, n_img, 0);
+        tma_load_5d(sx + 3 * halo_bytes, &tmDZ, &full_bar[stage], 0, x0, y0, n_img, 0);
         if (++stage == stages) {
           stage = 0;
           phase ^= 1;
@@ -315,15 +321,21 @@ wgrad_tc_swap64_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_co
       for (int pid = patch_begin; pid < patch_end; ++pid) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        const uint32_t sx = smem_u32(smem + stage * L::kStageBytes);
-        const uint64_t da0 = umma_smem_desc(sx, L::kTile, 1024);                 // 64-channel groups = taps, 8 KB apart
-        const uint64_t db0 = umma_smem_desc(sx + 9 * L::kTile, L::kTile, 1024);
+        const uint32_t sx = smem_u32(smem + stage * stage_bytes);
+        const uint32_t dyb = static_cast<uint32_t>(p.dil * row_bytes);           // one tap row (dy) down
+        const uint64_t db0 = umma_smem_desc(sx + 3 * halo_bytes, L::kTile, 1024);
+        // pairs 0..2: taps (dy=-1, dx) and (dy=0, dx) of halo tile dx: the two "64-channel groups" are dyb apart
+        // pair 3: taps (dy=+1, dx=-1) and (dy=+1, dx=0): one halo tile apart;  pair 4: tap (dy=+1, dx=+1) alone
 #pragma unroll
         for (int pair = 0; pair < 5; ++pair) {
+          const uint32_t a_start = pair < 3 ? sx + pair * halo_bytes : sx + (pair - 3) * 2 * halo_bytes + 2 * dyb;
+          // (pair 4: the partner rows are ignored; distance 0 keeps their reads inside this stage)
+          const uint64_t da0 =
+              umma_smem_desc(a_start, pair < 3 ? dyb : (pair == 3 ? static_cast<uint32_t>(halo_bytes) : 0u), 1024);
 #pragma unroll
           for (int k = 0; k < 4; ++k)   // 16 pixels per MMA
-            umma_bf16(tmem_base + pair * 64, da0 + ((pair * 2 * L::kTile + k * 2048) >> 4), db0 + ((k * 2048) >> 4),
-                      idesc, (accum | k) ? 1u : 0u);
+            umma_bf16(tmem_base + pair * 64, da0 + ((k * 2048) >> 4), db0 + ((k * 2048) >> 4), idesc,
+                      (accum | k) ? 1u : 0u);
         }
         accum = 1;
         umma_commit(&empty_bar[stage]);
@@ -344,7 +356,8 @@ wgrad_tc_swap64_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_co
     const bool any = patch_end > patch_begin;
 #pragma unroll 1
     for (int pair = 0; pair < 5; ++pair) {
-      const int tap = pair * 2 + unit;
+      // pair -> taps (see the MMA issuer): tap = dyi * 3 + dxi
+      const int tap = pair < 3 ? unit * 3 + pair : (pair == 3 ? 6 + unit : (unit == 0 ? 8 : 9));
       float* dst = p.ws + ((static_cast<long long>(split) * 9 + tap) * 64 + ci) * 64;
 #pragma unroll 1
       for (int c0 = 0; c0 < 64; c0 += 32) {

@@ -37,7 +37,8 @@ def _cos(a, b):
 
 # ---------------------------------------------------------------- single kernels
 @pytest.mark.parametrize("case", [(1, 16, 16, 64, 64, 1), (2, 24, 40, 64, 128, 1), (1, 13, 17, 1024, 512, 2),
-                                  (1, 24, 32, 128, 64, 2), (1, 16, 8, 256, 256, 1)])
+                                  (1, 24, 32, 128, 64, 2), (1, 16, 8, 256, 256, 1),
+                                  (1, 128, 400, 64, 64, 1)])   # > 5 patches per CTA: the swapped 64->64 wgrad wraps its stage ring
 @pytest.mark.parametrize("nsplit", [1, 2])
 def test_wgrad_dgrad_bias_match_autograd_oracle(dev, case, nsplit):
     import torch.nn.functional as F
