@@ -156,17 +156,19 @@ int dispatch_mode(int mode, const CUtensorMap& a, const CUtensorMap& b, ConvTcPa
 
 
 struct WgradPlan {
-  int TW, TH, tiles_x, tiles_y, total_patches, m_tiles, n_tiles, bn, ksplit, per, T, tap_groups, swap64;
+  int TW, TH, tiles_x, tiles_y, total_patches, m_tiles, n_tiles, bn, ksplit, per, T, tap_groups, swap64, pix;
 };
 WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nsplit) {
   WgradPlan pl;
+  pl.bn = Cin < 256 ? Cin : (nsplit > 1 ? 128 : 256);
+  // widest tiles (bf16 path, BN = 256, two taps): an 80 KB stage would leave a 2-deep pipeline -> 32-pixel patches
+  pl.pix = (nsplit == 1 && taps > 1 && pl.bn == 256 && env_int("CAN_B200_WGPIX", 64) == 32) ? 32 : 64;
   pl.TW = (W >= 16) ? 16 : 8;
-  pl.TH = 64 / pl.TW;
+  pl.TH = pl.pix / pl.TW;
   pl.tiles_x = (W + pl.TW - 1) / pl.TW;
   pl.tiles_y = (H + pl.TH - 1) / pl.TH;
   pl.total_patches = pl.tiles_x * pl.tiles_y * N;
   pl.m_tiles = (Cout + 127) / 128;
-  pl.bn = Cin < 256 ? Cin : (nsplit > 1 ? 128 : 256);
   pl.n_tiles = Cin / pl.bn;
   // taps per CTA: as many TMEM accumulators as fit (bf16 path); the fp32-parity path keeps one
   // (balanced groups: 9 taps = 3+3+3 for BN=64 (one N=192 MMA per k-step) and BN=128, 2+2+2+2+1 for BN=256)
@@ -205,14 +207,14 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   return pl;
 }
 
-template <int BN, int NSPLIT, int T>
+template <int BN, int NSPLIT, int T, int PIX = 64>
 int launch_wgrad(const CUtensorMap& tmDZ, const CUtensorMap& tmX, WgradTcParams& p, dim3 grid, cudaStream_t st) {
-  using L = WgradTcSmem<BN, NSPLIT, T>;
+  using L = WgradTcSmem<BN, NSPLIT, T, PIX>;
   int stages = (kMaxSmem - L::bytes(0)) / L::kStageBytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return fail(-20, "wgrad_tc: tile BN=%d nsplit=%d does not fit shared memory", BN, NSPLIT);
   p.stages = stages;
-  auto kern = wgrad_tc_kernel<BN, NSPLIT, T>;
+  auto kern = wgrad_tc_kernel<BN, NSPLIT, T, PIX>;
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
@@ -783,6 +785,7 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
   if (pl.T > 1) {  // bf16 path, several taps per CTA
     if (pl.bn == 64) rc = launch_wgrad<64, 1, 3>(tmDZ, tmX, p, grid, st);
     else if (pl.bn == 128) rc = launch_wgrad<128, 1, 3>(tmDZ, tmX, p, grid, st);
+    else if (pl.pix == 32) rc = launch_wgrad<256, 1, 2, 32>(tmDZ, tmX, p, grid, st);
     else rc = launch_wgrad<256, 1, 2>(tmDZ, tmX, p, grid, st);
   } else if (pl.bn == 64) {
     rc = nsplit == 1   ? launch_wgrad<64, 1, 1>(tmDZ, tmX, p, grid, st)

@@ -20,7 +20,7 @@ struct WgradTcParams {
   int N, H, W;
   int Cout, Cin;
   int taps, dil;
-  int TW, TH;  // patch, TW*TH == 64
+  int TW, TH;  // patch, TW*TH == 64 (32 for the PIX = 32 instantiations)
   int tiles_x, tiles_y;
   int m_tiles, n_tiles;
   int patches_per_split;
@@ -31,9 +31,9 @@ struct WgradTcParams {
   float* ws;     // [split][tap][Cout][Cin]
 };
 
-template <int BN, int NSPLIT, int T>
+template <int BN, int NSPLIT, int T, int PIX = 64>
 struct WgradTcSmem {
-  static constexpr int kGroupBytes = 64 * 128;            // 64 pixels x 64 ch x bf16
+  static constexpr int kGroupBytes = PIX * 128;           // PIX pixels x 64 ch x bf16 (PIX = 64, or 32 for deeper pipelines)
   static constexpr int kABytes = 2 * kGroupBytes;         // 128 cout
   static constexpr int kBBytes = (BN / 64) * kGroupBytes; // one tap
   static constexpr int kStageBytes = NSPLIT * (kABytes + T * kBBytes);
@@ -41,11 +41,11 @@ struct WgradTcSmem {
   static __host__ __device__ constexpr int bytes(int stages) { return 1024 + stages * kStageBytes + 1024; }
 };
 
-template <int BN, int NSPLIT, int T>
+template <int BN, int NSPLIT, int T, int PIX = 64>
 __global__ void __launch_bounds__(192, 1)
 wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant__ CUtensorMap tmX,
                 const WgradTcParams p) {
-  using L = WgradTcSmem<BN, NSPLIT, T>;
+  using L = WgradTcSmem<BN, NSPLIT, T, PIX>;
   static_assert(T * BN <= 512, "accumulators of one tap group must fit TMEM");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -157,7 +157,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
             for (int pb = 0; pb < NSPLIT; ++pb) {
               if (pa + pb < NSPLIT) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {  // 16 pixels (= 2 swizzle atoms of 8 rows) per MMA
+                for (int k = 0; k < PIX / 16; ++k) {  // 16 pixels (= 2 swizzle atoms of 8 rows) per MMA
                   umma_bf16(tmem_base + tt * BN, da0 + ((pa * L::kABytes + k * 2048) >> 4),
                             db0 + (((pb * T + tt) * L::kBBytes + k * 2048) >> 4), idesc_n,
                             (accum | (pa + pb) | k) ? 1u : 0u);
