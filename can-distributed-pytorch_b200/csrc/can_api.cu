@@ -238,6 +238,18 @@ int make_act_tmap(CUtensorMap* m, const void* base, int coff, int C, int cs, int
 }
 
 
+// single-plane activation map whose 4th dimension is the 64-channel group: one TMA op brings `gbox`
+// groups of a (TW x TH) patch, landing group-major ([group][pixel][64 ch]) as the MN-major operands want
+int make_act_tmap_groups(CUtensorMap* m, const void* base, int coff, int C, int cs, int N, int H, int W, int TW, int TH,
+                         int gbox) {
+  const uint64_t dims[5] = {64, static_cast<uint64_t>(W), static_cast<uint64_t>(H), static_cast<uint64_t>(C / 64),
+                            static_cast<uint64_t>(N)};
+  const uint64_t csb = static_cast<uint64_t>(cs) * 2;
+  const uint64_t str[4] = {csb, csb * W, 128, csb * W * H};
+  const uint32_t box[5] = {64, static_cast<uint32_t>(TW), static_cast<uint32_t>(TH), static_cast<uint32_t>(gbox), 1};
+  return make_tmap(m, static_cast<const __nv_bfloat16*>(base) + coff, 5, dims, str, box);
+}
+
 int launch_ctx_gemv(const float* Wm, const float* in, long long in_ns, long long in_ps, long long in_js,
                     const float* add, float* out, int N, cudaStream_t st) {
   static bool attr = false;
@@ -761,6 +773,12 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
   p.ws = static_cast<float*>(ws);
   p.tap_groups = pl.tap_groups;
   dim3 grid(pl.m_tiles * pl.n_tiles * pl.tap_groups, pl.ksplit);
+  if (nsplit == 1 && !pl.swap64) {
+    rc = make_act_tmap_groups(&tmDZ, dz, dz_coff, Cout, dz_cs, N, H, W, pl.TW, pl.TH, p.m_groups);
+    if (rc) return rc;
+    rc = make_act_tmap_groups(&tmX, x, x_coff, Cin, x_cs, N, H, W, pl.TW, pl.TH, pl.bn / 64);
+    if (rc) return rc;
+  }
   if (pl.swap64) {
     using L = WgradSwapSmem;
     rc = make_act_tmap(&tmX, x, x_coff, Cin, x_cs, x_plane, nsplit, N, H, W, pl.TW, pl.TH + 2 * dil);   // halo tile

@@ -97,17 +97,31 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      // this thread is alone on the critical path of the pipeline: tap offsets once, patch coordinates incrementally
+      int tdx[T], tdy[T];
+#pragma unroll
+      for (int tt = 0; tt < T; ++tt) {
+        const int tap = tap0 + tt;
+        tdx[tt] = p.taps == 9 ? (tap % 3 - 1) * p.dil : 0;
+        tdy[tt] = p.taps == 9 ? (tap / 3 - 1) * p.dil : 0;
+      }
+      int tx_i = patch_begin % p.tiles_x, ty_i = (patch_begin / p.tiles_x) % p.tiles_y,
+          n_img = patch_begin / (p.tiles_x * p.tiles_y);
       for (int pid = patch_begin; pid < patch_end; ++pid) {
-        int q = pid;
-        const int tx_i = q % p.tiles_x;
-        q /= p.tiles_x;
-        const int ty_i = q % p.tiles_y;
-        const int n_img = q / p.tiles_y;
         const int x0 = tx_i * p.TW, y0 = ty_i * p.TH;
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem + stage * L::kStageBytes;
         uint8_t* sb = sa + NSPLIT * L::kABytes;  // [plane][tap][BN/64 groups]
         mbar_expect_tx(&full_bar[stage], stage_tx);
+        if (NSPLIT == 1) {
+          // single-plane maps carry the 64-channel group as their 4th dimension: one TMA op per operand tile
+          tma_load_5d(sa, &tmDZ, &full_bar[stage], 0, x0, y0, m_tile * 2, n_img);
+#pragma unroll
+          for (int tt = 0; tt < T; ++tt)
+            if (tt < ntaps)
+              tma_load_5d(sb + tt * L::kBBytes, &tmX, &full_bar[stage], 0, x0 + tdx[tt], y0 + tdy[tt], n_tile * (BN / 64),
+                          n_img);
+        } else
 #pragma unroll
         for (int pl = 0; pl < NSPLIT; ++pl) {
           for (int g = 0; g < m_groups; ++g)
@@ -129,6 +143,13 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
         if (++stage == stages) {
           stage = 0;
           phase ^= 1;
+        }
+        if (++tx_i == p.tiles_x) {
+          tx_i = 0;
+          if (++ty_i == p.tiles_y) {
+            ty_i = 0;
+            ++n_img;
+          }
         }
       }
     }
