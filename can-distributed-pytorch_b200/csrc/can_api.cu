@@ -162,7 +162,7 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   WgradPlan pl;
   pl.bn = Cin < 256 ? Cin : (nsplit > 1 ? 128 : 256);
   // widest tiles (bf16 path, BN = 256, two taps): an 80 KB stage would leave a 2-deep pipeline -> 32-pixel patches
-  pl.pix = (nsplit == 1 && taps > 1 && pl.bn == 256 && env_int("CAN_B200_WGPIX", 64) == 32) ? 32 : 64;
+  pl.pix = (nsplit == 1 && taps > 1 && pl.bn == 256 && env_int("CAN_B200_WGPIX", 32) == 32) ? 32 : 64;
   pl.TW = (W >= 16) ? 16 : 8;
   pl.TH = pl.pix / pl.TW;
   pl.tiles_x = (W + pl.TW - 1) / pl.TW;
