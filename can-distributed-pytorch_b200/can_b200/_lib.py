@@ -67,6 +67,11 @@ _SIGNATURES = {
     "can_ctx_outer": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int, C.c_void_p,
                                 C.c_float, C.c_int, C.c_void_p]),
     "can_im2col_first": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "can_conv_first_tc_fwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                        C.c_int, C.c_int, C.c_void_p]),
+    "can_conv_first_wgrad_workspace_bytes": (C.c_int64, []),
+    "can_conv_first_wgrad": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                       C.c_int, C.c_float, C.c_void_p, C.c_int64, C.c_void_p]),
     "can_bias_grad": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_void_p,
                                 C.c_void_p]),
     "can_head_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_int64,

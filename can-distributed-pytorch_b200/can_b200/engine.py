@@ -81,9 +81,15 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
     # ---- frontend (CANNet.py:40) -------------------------------------------------
     w0, b0 = fr[0]
     col = None
-    if nsplit == 1 and os.environ.get("CAN_B200_FIRST_TC", "1") != "0":
-        # bf16 path: K = 27 padded to 64 through an im2col of the image turns conv1_1 into a 1x1 GEMM on
-        # the tensor cores; the im2col buffer is reused by the weight gradient in backward
+    first_mode = os.environ.get("CAN_B200_FIRST_TC", "2") if nsplit == 1 else "0"
+    if first_mode == "2":
+        # bf16 path: conv1_1 as a K = 32 GEMM whose 27-wide patch rows are rebuilt in shared memory from the
+        # fp32 image (no im2col buffer in HBM); backward does the same for the weight gradient
+        w0p = cache.get(("f0", 1), (w0,), lambda: ops.pack_first_weight(w0))
+        a = ops.new_act(1, N, H, W, 64, dev)
+        ops.conv_first_tc(x, w0p, b0.detach().float().contiguous(), a)
+    elif first_mode == "1":
+        # K = 27 padded to 64 through an im2col of the image (1x1 GEMM); the buffer is reused by backward
         col = ops.im2col_first(x, 1)
         w0p = cache.get(("f0", 1), (w0,), lambda: ops.pack_first_weight(w0))
         a = ops.new_act(1, N, H, W, 64, dev)
@@ -264,11 +270,15 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
         dz = ndz
     # first conv (3 -> 64): K = 27 padded to 64 through an im2col of the image
     col = saved.get("col")
-    if col is None:
-        col = ops.im2col_first(saved["x"], nsplit)
-    g0 = torch.empty(64, 64, device=dev, dtype=torch.float32)
-    ops.conv_wgrad(dz, col, g0, taps=1)
-    grads[0].copy_(g0[:, :27].reshape(64, 3, 3, 3))   # bias gradient of conv1_1 was fused into conv1_2's dgrad
+    if nsplit == 1 and col is None and grads[0].is_contiguous() and os.environ.get("CAN_B200_FIRST_TC", "2") == "2":
+        ops.conv_first_wgrad(dz, saved["x"], grads[0])   # straight from the image, into the parameter's layout
+    else:
+        if col is None:
+            col = ops.im2col_first(saved["x"], nsplit)
+        g0 = torch.empty(64, 64, device=dev, dtype=torch.float32)
+        ops.conv_wgrad(dz, col, g0, taps=1)
+        grads[0].copy_(g0[:, :27].reshape(64, 3, 3, 3))
+    # (the bias gradient of conv1_1 was fused into conv1_2's dgrad)
     if on_ready:
         on_ready("frontend")
     return grads

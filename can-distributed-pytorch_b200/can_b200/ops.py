@@ -279,6 +279,35 @@ def im2col_first(x: torch.Tensor, nsplit: int) -> Act:
     return out
 
 
+def conv_first_tc(x: torch.Tensor, w_packed: torch.Tensor, bias: torch.Tensor, out: Act):
+    """frontend.0 + ReLU straight from the fp32 NCHW image (bf16 path; no im2col buffer)."""
+    N, _, H, W = x.shape
+    assert out.nsplit == 1 and out.C == 64
+    _count()
+    with _Prof(2.0 * 27 * 64 * N * H * W, f"conv first 3->64 {H}x{W}"):
+        check(lib().can_conv_first_tc_fwd(x.data_ptr(), w_packed.data_ptr(), bias.data_ptr(), out.buf.data_ptr(), out.cs,
+                                          out.coff, N, H, W, _stream()), "conv_first_tc_fwd")
+
+
+_FIRST_WS = {}
+
+
+def conv_first_wgrad(dz: Act, x: torch.Tensor, grad: torch.Tensor, accumulate=False, alpha=1.0):
+    """grad [64,3,3,3] fp32 (+)= alpha * dW of frontend.0 from dz (NHWC bf16, one plane) and the image itself."""
+    N, _, H, W = x.shape
+    assert dz.nsplit == 1 and dz.C == 64 and grad.is_contiguous() and grad.numel() == 64 * 27
+    dev = x.device
+    ws = _FIRST_WS.get(dev)
+    if ws is None:
+        ws = torch.empty(lib().can_conv_first_wgrad_workspace_bytes(), device=dev, dtype=torch.uint8)
+        _FIRST_WS[dev] = ws
+    _count(2)
+    with _Prof(2.0 * 27 * 64 * N * H * W, f"wgrad first 3->64 {H}x{W}"):
+        check(lib().can_conv_first_wgrad(dz.buf.data_ptr(), dz.cs, dz.coff, x.data_ptr(), N, H, W, grad.data_ptr(),
+                                         int(accumulate), float(alpha), ws.data_ptr(), ws.numel(), _stream()),
+              "conv_first_wgrad")
+
+
 def bias_grad(dz: Act, db: torch.Tensor):
     """db[c] += sum_pixels dz[pix][c]; db fp32 [C], already initialised."""
     check(lib().can_bias_grad(dz.buf.data_ptr(), dz.plane, dz.nsplit, dz.cs, dz.coff, dz.C, dz.N * dz.H * dz.W,

@@ -13,6 +13,7 @@
 #include "can_simple.cuh"
 #include "can_wgrad_tc.cuh"
 #include "can_aux.cuh"
+#include "can_first_tc.cuh"
 
 using namespace canb;
 
@@ -833,6 +834,85 @@ int can_im2col_first(const float* x_nchw, void* out, int64_t out_plane, int nspl
         x_nchw, static_cast<__nv_bfloat16*>(out), out_plane, nsplit, N, H, W);
   }
   CAN_CHECK_LAUNCH("im2col_first");
+  return 0;
+}
+
+namespace {
+constexpr int kFirstWgradCtas = 148 * 6;
+int first_act_map(CUtensorMap* m, const void* base, int cs, int coff, int N, int H, int W, int rank, int box_px) {
+  const uint64_t csb = static_cast<uint64_t>(cs) * 2;
+  const uint64_t dims[4] = {64, static_cast<uint64_t>(W), static_cast<uint64_t>(N) * H, 1};
+  const uint64_t str[3] = {csb, csb * W, csb * W * N * H};
+  const uint32_t box[4] = {64, static_cast<uint32_t>(box_px), 1, 1};
+  return make_tmap(m, static_cast<const __nv_bfloat16*>(base) + coff, rank, dims, str, box);
+}
+}  // namespace
+
+int can_conv_first_tc_fwd(const float* x_nchw, const void* w_packed, const float* bias, void* out, int out_cs,
+                          int out_coff, int N, int H, int W, void* stream) {
+  if (!x_nchw || !w_packed || !bias || !out || N <= 0 || H <= 0 || W <= 0) return fail(-1, "conv_first_tc_fwd: bad arguments");
+  if (out_cs % 8 || out_coff % 8 || (reinterpret_cast<uintptr_t>(out) & 15) || (reinterpret_cast<uintptr_t>(w_packed) & 15))
+    return fail(-2, "conv_first_tc_fwd: output stride/offset must be multiples of 8 channels, pointers 16-byte aligned");
+  if (static_cast<long long>(N) * H > 0x7fffffffLL) return fail(-3, "conv_first_tc_fwd: N*H too large");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CUtensorMap tmW, tmO;
+  {
+    const uint64_t dims[2] = {64, 64};
+    const uint64_t str[1] = {128};
+    const uint32_t box[2] = {64, 64};
+    int rc = make_tmap(&tmW, w_packed, 2, dims, str, box);
+    if (rc) return rc;
+  }
+  int rc = first_act_map(&tmO, out, out_cs, out_coff, N, H, W, 4, 128);
+  if (rc) return rc;
+  FirstFwdParams p;
+  p.x = x_nchw; p.bias = bias; p.N = N; p.H = H; p.W = W;
+  p.tiles_x = (W + 127) / 128;
+  const long long tiles = static_cast<long long>(N) * H * p.tiles_x;
+  if (tiles > 0x7fffffffLL) return fail(-3, "conv_first_tc_fwd: too many tiles");
+  p.num_tiles = static_cast<int>(tiles);
+  static thread_local bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(conv_first_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFirstFwdSmem);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_first_tc)");
+    attr_done = true;
+  }
+  const int ctas = p.num_tiles < 148 * 4 ? p.num_tiles : 148 * 4;
+  conv_first_tc_kernel<<<ctas, 128, kFirstFwdSmem, st>>>(tmW, tmO, p);
+  CAN_CHECK_LAUNCH("conv_first_tc");
+  return 0;
+}
+
+int64_t can_conv_first_wgrad_workspace_bytes(void) { return static_cast<int64_t>(kFirstWgradCtas) * 64 * 32 * sizeof(float); }
+
+int can_conv_first_wgrad(const void* dz, int dz_cs, int dz_coff, const float* x_nchw, int N, int H, int W, float* grad,
+                         int accumulate, float alpha, void* ws, int64_t ws_bytes, void* stream) {
+  if (!dz || !x_nchw || !grad || !ws || N <= 0 || H <= 0 || W <= 0) return fail(-1, "conv_first_wgrad: bad arguments");
+  if (dz_cs % 8 || dz_coff % 8 || (reinterpret_cast<uintptr_t>(dz) & 15))
+    return fail(-2, "conv_first_wgrad: dz stride/offset must be multiples of 8 channels, pointer 16-byte aligned");
+  if (ws_bytes < can_conv_first_wgrad_workspace_bytes()) return fail(-3, "conv_first_wgrad: workspace too small");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CUtensorMap tmDZ;
+  int rc = first_act_map(&tmDZ, dz, dz_cs, dz_coff, N, H, W, 3, 64);
+  if (rc) return rc;
+  FirstWgradParams p;
+  p.x = x_nchw; p.N = N; p.H = H; p.W = W;
+  p.tiles_x = (W + 63) / 64;
+  const long long patches = static_cast<long long>(N) * H * p.tiles_x;
+  if (patches > 0x7fffffffLL) return fail(-3, "conv_first_wgrad: too many patches");
+  p.num_patches = static_cast<int>(patches);
+  p.ws = static_cast<float*>(ws);
+  static thread_local bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(wgrad_first_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFirstWgSmem);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(wgrad_first_tc)");
+    attr_done = true;
+  }
+  const int ctas = p.num_patches < kFirstWgradCtas ? p.num_patches : kFirstWgradCtas;
+  wgrad_first_tc_kernel<<<ctas, 128, kFirstWgSmem, st>>>(tmDZ, p);
+  CAN_CHECK_LAUNCH("wgrad_first_tc");
+  wgrad_first_reduce_kernel<<<64, 256, 0, st>>>(p.ws, grad, ctas, accumulate, alpha);
+  CAN_CHECK_LAUNCH("wgrad_first_reduce");
   return 0;
 }
 

@@ -169,6 +169,22 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
 int can_im2col_first(const float* x_nchw, void* out, int64_t out_plane, int nsplit, int N, int H, int W,
                      void* stream);
 
+/* frontend.0 (model/CANNet.py:14: Conv2d(3, 64, 3, padding=1) + ReLU) on the tensor cores without an
+ * im2col buffer: the 27-wide patch rows are rebuilt in shared memory from the fp32 NCHW image.
+ * bf16 path only (single-plane output).  w_packed: the [64][64] bf16 matrix of
+ * can_pack_conv_weight(w padded to [64][64][1][1], nsplit 1); out: NHWC bf16 with pixel stride out_cs
+ * and channel offset out_coff.  Replaces the cuDNN forward of that layer (model/CANNet.py:40).      */
+int can_conv_first_tc_fwd(const float* x_nchw, const void* w_packed, const float* bias, void* out, int out_cs,
+                          int out_coff, int N, int H, int W, void* stream);
+
+/* Weight gradient of frontend.0 from the image itself (no im2col buffer):
+ *   grad[co][ci][ky][kx] (+)= alpha * sum_{n,y,x} dz[n,y,x,co] * x[n,ci,y+ky-1,x+kx-1]  (bf16 products, fp32 sums)
+ * dz: NHWC bf16 (single plane), ws: can_conv_first_wgrad_workspace_bytes() bytes of scratch.
+ * Replaces cuDNN backward-filter for that layer under loss.backward() (utils/train_eval_utils.py:38). */
+int64_t can_conv_first_wgrad_workspace_bytes(void);
+int can_conv_first_wgrad(const void* dz, int dz_cs, int dz_coff, const float* x_nchw, int N, int H, int W, float* grad,
+                         int accumulate, float alpha, void* ws, int64_t ws_bytes, void* stream);
+
 /* db[c] += sum_pixels dz[pixel][c]  (bias gradient of every conv; db must be initialised).    */
 int can_bias_grad(const void* dz, int64_t plane, int nsplit, int cs, int coff, int C, int64_t npix, float* db,
                   void* stream);

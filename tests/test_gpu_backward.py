@@ -213,3 +213,39 @@ def test_train_one_epoch_and_evaluate_mirror_the_reference_drivers(dev):
             ref_mae += abs(float(et.sum()) - float(gt.double().sum()))
     mae = evaluate(m, batches, dev, epoch=0)
     assert mae == pytest.approx(ref_mae, rel=2e-3)
+
+
+# ---------------------------------------------------------------- fused first layer (no im2col buffer)
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(1, 16, 16), (2, 37, 200), (1, 9, 333)])
+def test_first_layer_fused_kernels_match_im2col_path(dev, shape):
+    """conv1_1 forward and weight gradient rebuilt from the image in shared memory == the im2col + GEMM route
+    (same bf16 operands, fp32 accumulation), and both == an fp64 conv of the bf16-rounded operands."""
+    import torch.nn.functional as F
+    from can_b200 import ops
+    N, H, W = shape
+    g = torch.Generator().manual_seed(5)
+    x = torch.rand(N, 3, H, W, generator=g).to(dev)
+    w = (torch.randn(64, 3, 3, 3, generator=g) * 0.2).to(dev)
+    b = (torch.randn(64, generator=g) * 0.1).to(dev)
+    wp = ops.pack_first_weight(w)
+    fused = ops.new_act(1, N, H, W, 64, dev, zero=True)
+    ops.conv_first_tc(x, wp, b, fused)
+    col = ops.im2col_first(x, 1)
+    ref = ops.new_act(1, N, H, W, 64, dev)
+    ops.conv_tc(col, wp, 64, taps=1, mode=ops.MODE_STORE, relu=True, bias=b, out=ref)
+    assert torch.equal(fused.to_nchw(), ref.to_nchw())
+    truth = torch.relu(F.conv2d(x.bfloat16().double().cpu(), w.bfloat16().double().cpu(), b.double().cpu(), padding=1))
+    assert harness.rel_l2(fused.to_nchw().cpu(), truth) < 3e-3          # bf16 output rounding
+    # weight gradient
+    dz = torch.randn(N, 64, H, W, generator=g)
+    dza = ops.act_from_nchw(dz.to(dev), 1)
+    g_fused = torch.empty(64, 3, 3, 3, device=dev)
+    ops.conv_first_wgrad(dza, x, g_fused)
+    xg = x.bfloat16().double().cpu()
+    wg = torch.zeros(64, 3, 3, 3, dtype=torch.float64, requires_grad=True)
+    F.conv2d(xg, wg, None, padding=1).backward(dza.to_nchw().cpu().double())
+    assert harness.rel_l2(g_fused.cpu(), wg.grad) < 1e-5
+    g_acc = g_fused.clone()
+    ops.conv_first_wgrad(dza, x, g_acc, accumulate=True, alpha=0.5)
+    assert harness.rel_l2(g_acc.cpu(), 1.5 * wg.grad) < 1e-5
