@@ -838,7 +838,7 @@ int can_im2col_first(const float* x_nchw, void* out, int64_t out_plane, int nspl
 }
 
 namespace {
-constexpr int kFirstWgradCtas = 148 * 6;
+constexpr int kFirstWgradCtas = 148 * 5;
 int first_act_map(CUtensorMap* m, const void* base, int cs, int coff, int N, int H, int W, int rank, int box_px) {
   const uint64_t csb = static_cast<uint64_t>(cs) * 2;
   const uint64_t dims[4] = {64, static_cast<uint64_t>(W), static_cast<uint64_t>(N) * H, 1};
@@ -877,7 +877,7 @@ int can_conv_first_tc_fwd(const float* x_nchw, const void* w_packed, const float
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_first_tc)");
     attr_done = true;
   }
-  const int ctas = p.num_tiles < 148 * 4 ? p.num_tiles : 148 * 4;
+  const int ctas = p.num_tiles < 148 * 7 ? p.num_tiles : 148 * 7;
   conv_first_tc_kernel<<<ctas, 128, kFirstFwdSmem, st>>>(tmW, tmO, p);
   CAN_CHECK_LAUNCH("conv_first_tc");
   return 0;
@@ -893,11 +893,11 @@ int can_conv_first_wgrad(const void* dz, int dz_cs, int dz_coff, const float* x_
   if (ws_bytes < can_conv_first_wgrad_workspace_bytes()) return fail(-3, "conv_first_wgrad: workspace too small");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   CUtensorMap tmDZ;
-  int rc = first_act_map(&tmDZ, dz, dz_cs, dz_coff, N, H, W, 3, 64);
+  int rc = first_act_map(&tmDZ, dz, dz_cs, dz_coff, N, H, W, 3, 128);
   if (rc) return rc;
   FirstWgradParams p;
   p.x = x_nchw; p.N = N; p.H = H; p.W = W;
-  p.tiles_x = (W + 63) / 64;
+  p.tiles_x = (W + 127) / 128;
   const long long patches = static_cast<long long>(N) * H * p.tiles_x;
   if (patches > 0x7fffffffLL) return fail(-3, "conv_first_wgrad: too many patches");
   p.num_patches = static_cast<int>(patches);

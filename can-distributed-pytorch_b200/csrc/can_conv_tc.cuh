@@ -215,7 +215,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   constexpr int GS = gemm_planes(NSPLIT, MODE);  // planes that enter the GEMM
   using L = ConvTcSmem<BN, GS>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-aligned, still a shared-space pointer
   const int stages = p.stages;
   uint8_t* s_out = smem;                                           // staged output tile (p.out_stage_bytes, 1024-aligned)
   uint8_t* s_mask = smem + p.out_stage_bytes;                       // staged mask tiles (p.mask_bufs x BN * 256 B)

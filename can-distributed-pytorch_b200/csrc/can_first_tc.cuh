@@ -27,11 +27,26 @@ template <int P>
 __device__ __forceinline__ void first_build_rows(const float* __restrict__ x, int n, int y, int x0, int H, int W,
                                                  float* s_in, uint8_t* s_a) {
   constexpr int PW = P + 4;
-  for (int i = threadIdx.x; i < 9 * (P + 2); i += blockDim.x) {
-    const int c = i % (P + 2), rr = (i / (P + 2)) % 3, ci = i / (3 * (P + 2));
-    const int yy = y + rr - 1, xx = x0 + c - 1;
-    s_in[(ci * 3 + rr) * PW + c] =
-        (yy >= 0 && yy < H && xx >= 0 && xx < W) ? __ldg(x + ((static_cast<long long>(n) * 3 + ci) * H + yy) * W + xx) : 0.f;
+  static_assert(P == 128, "one thread per pixel, blockDim.x == P");
+  {
+    // all loads first, then the stores: a load-store-load-store sequence would expose the memory latency
+    // nine times per tile (in-order issue stalls at every dependent store)
+    const int t = threadIdx.x;
+    float v[9], e[9];
+#pragma unroll
+    for (int r = 0; r < 9; ++r) {   // r = ci * 3 + window row; coalesced along x
+      const int yy = y + (r % 3) - 1;
+      const float* src = x + ((static_cast<long long>(n) * 3 + r / 3) * H + yy) * W + x0 - 1;
+      const bool row_ok = yy >= 0 && yy < H;
+      const int xx = x0 + t - 1, xe = x0 + P + t - 1;
+      v[r] = (row_ok && xx >= 0 && xx < W) ? __ldg(src + t) : 0.f;
+      e[r] = (t < 2 && row_ok && xe < W) ? __ldg(src + P + t) : 0.f;   // the two extra halo columns
+    }
+#pragma unroll
+    for (int r = 0; r < 9; ++r) {
+      s_in[r * PW + t] = v[r];
+      if (t < 2) s_in[r * PW + P + t] = e[r];
+    }
   }
   __syncthreads();
   for (int t = threadIdx.x; t < P; t += blockDim.x) {
@@ -65,16 +80,16 @@ struct FirstFwdParams {
 
 // tmW: packed weight [64 co][64 k] bf16 (k >= 27 zero), box (64, 64), 128B swizzle
 // tmO: output activation (64 ch, W, N*H), box (64, 128, 1), 128B swizzle
-constexpr int kFirstFwdSmem = 1024 + 16384 /*A*/ + 8192 /*W*/ + 16384 /*out*/ + 9 * 132 * 4 + 64 * 4 + 64;
+constexpr int kFirstFwdSmem = 1024 + 16384 /*A, then the staged output tile*/ + 8192 /*W*/ + 9 * 132 * 4 + 64 * 4 + 64;
 __global__ void __launch_bounds__(128)
 conv_first_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmO,
                      const FirstFwdParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-aligned, still a shared-space pointer
   uint8_t* s_a = smem;
   uint8_t* s_w = smem + 16384;
-  uint8_t* s_o = smem + 24576;
-  float* s_in = reinterpret_cast<float*>(smem + 40960);
+  uint8_t* s_o = s_a;   // the output tile is staged over the A tile once the MMAs have consumed it
+  float* s_in = reinterpret_cast<float*>(smem + 24576);
   float* s_bias = s_in + 9 * 132;
   uint64_t* w_bar = reinterpret_cast<uint64_t*>(s_bias + 64);
   uint64_t* mma_bar = w_bar + 1;
@@ -109,8 +124,8 @@ conv_first_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
     const int row_id = tile / p.tiles_x;   // n * H + y
     const int y = row_id % p.H, n = row_id / p.H;
     const int x0 = tx * 128;
-    first_build_rows<128>(p.x, n, y, x0, p.H, p.W, s_in, s_a);
-    if (threadIdx.x == 0) bulk_wait_group_read0();   // the previous tile's store has read s_o
+    if (threadIdx.x == 0) bulk_wait_group_read0();   // the previous tile's store has read s_o (= s_a); ordered
+    first_build_rows<128>(p.x, n, y, x0, p.H, p.W, s_in, s_a);   // before the row writes by the barrier inside
     tc_fence_before();
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -161,21 +176,21 @@ conv_first_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
 struct FirstWgradParams {
   const float* x;      // [N][3][H][W] fp32
   int N, H, W;
-  int tiles_x;         // ceil(W / 64)
+  int tiles_x;         // ceil(W / 128)
   int num_patches;     // N * H * tiles_x
   float* ws;           // [gridDim.x][64 co][32 k] fp32 partial sums
 };
 
-// tmDZ: dZ of conv1_1's output (64 ch, W, N*H), box (64, 64, 1), 128B swizzle (an MN-major A tile: [64 px][64 co])
-constexpr int kFirstWgSmem = 1024 + 2 * 8192 /*dZ (+ the ignored second M group)*/ + 8192 /*B*/ + 9 * 68 * 4 + 64;
+// tmDZ: dZ of conv1_1's output (64 ch, W, N*H), box (64, 128, 1), 128B swizzle (an MN-major A tile: [128 px][64 co])
+constexpr int kFirstWgSmem = 1024 + 16384 /*dZ*/ + 16384 /*B*/ + 9 * 132 * 4 + 64;
 __global__ void __launch_bounds__(128)
 wgrad_first_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const FirstWgradParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* s_dz = smem;            // 8 KB used; M rows 64..127 of the MMA read the next 8 KB (finite, ignored)
-  uint8_t* s_b = smem + 16384;
-  float* s_in = reinterpret_cast<float*>(smem + 24576);
-  uint64_t* dz_bar = reinterpret_cast<uint64_t*>(s_in + 9 * 68);
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-aligned, still a shared-space pointer
+  uint8_t* s_dz = smem;            // [128 px][64 co]; M rows 64..127 of the MMA re-read rows 0..63 (group distance 0), ignored
+  uint8_t* s_b = smem + 16384;     // [128 px][32 k (+ unused half)]
+  float* s_in = reinterpret_cast<float*>(smem + 32768);
+  uint64_t* dz_bar = reinterpret_cast<uint64_t*>(s_in + 9 * 132);
   uint64_t* mma_bar = dz_bar + 1;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(mma_bar + 1);
   const int warp = threadIdx.x >> 5;
@@ -185,9 +200,6 @@ wgrad_first_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const FirstWgrad
     mbar_init(mma_bar, 1);
     fence_mbar_init();
   }
-  // the ignored half of the A operand must hold finite numbers
-  for (int i = threadIdx.x; i < 8192 / 16; i += blockDim.x) reinterpret_cast<uint4*>(s_dz + 8192)[i] = make_uint4(0, 0, 0, 0);
-  fence_proxy_async();
   if (warp == 0) {
     tmem_alloc(tmem_ptr_smem, 32);
     tmem_relinquish();
@@ -202,23 +214,23 @@ wgrad_first_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const FirstWgrad
     const int tx = patch % p.tiles_x;
     const int row_id = patch / p.tiles_x;
     const int y = row_id % p.H, n = row_id / p.H;
-    const int x0 = tx * 64;
+    const int x0 = tx * 128;
     // previous patch's MMAs have finished reading s_dz / s_b
     if (it > 0) mbar_wait(mma_bar, static_cast<uint32_t>(it - 1) & 1u);
     if (threadIdx.x == 0) {
-      mbar_expect_tx(dz_bar, 8192);
+      mbar_expect_tx(dz_bar, 16384);
       tma_load_3d(s_dz, &tmDZ, dz_bar, 0, x0, row_id);   // pixels past W arrive as zeros
     }
-    first_build_rows<64>(p.x, n, y, x0, p.H, p.W, s_in, s_b);
+    first_build_rows<128>(p.x, n, y, x0, p.H, p.W, s_in, s_b);
     tc_fence_before();
     __syncthreads();
     if (threadIdx.x == 0) {
       mbar_wait(dz_bar, static_cast<uint32_t>(it) & 1u);
       tc_fence_after();
-      const uint64_t da = umma_smem_desc(smem_u32(s_dz), 8192, 1024);
-      const uint64_t db = umma_smem_desc(smem_u32(s_b), 8192, 1024);
+      const uint64_t da = umma_smem_desc(smem_u32(s_dz), 0, 1024);
+      const uint64_t db = umma_smem_desc(smem_u32(s_b), 0, 1024);
 #pragma unroll
-      for (int k = 0; k < 4; ++k)   // 16 pixels per MMA
+      for (int k = 0; k < 8; ++k)   // 16 pixels per MMA
         umma_bf16(tmem_base, da + ((k * 2048) >> 4), db + ((k * 2048) >> 4), idesc, (it | k) ? 1u : 0u);
       umma_commit(mma_bar);
     }

@@ -48,7 +48,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
   using L = WgradTcSmem<BN, NSPLIT, T, PIX>;
   static_assert(T * BN <= 512, "accumulators of one tap group must fit TMEM");
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-aligned, still a shared-space pointer
   const int stages = p.stages;
   uint8_t* tail = smem + stages * L::kStageBytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
@@ -271,7 +271,7 @@ wgrad_tc_swap64_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_co
                        const WgradTcParams p) {
   using L = WgradSwapSmem;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-aligned, still a shared-space pointer
   const int stages = p.stages;
   const int row_bytes = p.TW * 128;                       // one patch row (1024 or 2048 B)
   const int halo_bytes = (p.TH + 2 * p.dil) * row_bytes;
