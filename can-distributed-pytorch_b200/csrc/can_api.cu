@@ -52,10 +52,12 @@ PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
 
 // bf16 tensor map with a 128-byte swizzled box whose innermost extent is 64 elements.
 int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-              const uint32_t* box, bool swizzle128 = true) {
+              const uint32_t* box, bool swizzle128 = true, const uint32_t* elem_strides = nullptr) {
   auto enc = get_encode();
   if (!enc) return fail(-100, "cuTensorMapEncodeTiled entry point not available");
   uint32_t estr[5] = {1, 1, 1, 1, 1};
+  if (elem_strides)
+    for (int i = 0; i < rank; ++i) estr[i] = elem_strides[i];
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -390,6 +392,20 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   g_tmM = nullptr;
   p.out_stage_bytes = 0;
   p.mask_bufs = 0;
+  if (ns == 1 && a->mode == CAN_MODE_UNPOOL && (bn == 64 || bn == 128) && a->out && env_int("CAN_B200_TMASTORE", 1) != 0) {
+    // max-unpool: the four positions of the 2x2 window are four (TH x TW) sub-tiles of the 2x upsampled map,
+    // each written by one TMA store that walks the output with element stride 2 in x and y
+    const uint64_t cs = static_cast<uint64_t>(a->out_cs) * 2;
+    const uint64_t dimsU[4] = {static_cast<uint64_t>(a->Cout), static_cast<uint64_t>(a->OW), static_cast<uint64_t>(a->OH),
+                               static_cast<uint64_t>(a->N)};
+    const uint64_t strU[3] = {cs, cs * a->OW, cs * a->OW * a->OH};
+    const uint32_t boxU[4] = {64, static_cast<uint32_t>(2 * p.TW), static_cast<uint32_t>(2 * p.TH), 1};
+    const uint32_t estrU[4] = {1, 2, 2, 1};
+    int rc = make_tmap(&tmO, static_cast<__nv_bfloat16*>(a->out) + a->out_coff, 4, dimsU, strU, boxU, true, estrU);
+    if (rc) return rc;
+    g_tmO = &tmO;
+    p.out_stage_bytes = 2 * bn * 256;
+  }
   if (ns == 1 && a->mode == CAN_MODE_STORE && (bn == 64 || bn == 128) && a->out && env_int("CAN_B200_TMASTORE", 1) != 0) {
     const uint64_t cs = static_cast<uint64_t>(a->out_cs) * 2;
     const uint64_t dimsO[4] = {static_cast<uint64_t>(a->Cout), static_cast<uint64_t>(a->W), static_cast<uint64_t>(a->H),
@@ -401,7 +417,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     g_tmO = &tmO;
     p.out_stage_bytes = bn * 256;
     if (a->mask && a->mask_cs % 8 == 0 && a->mask_coff % 8 == 0 && (reinterpret_cast<uintptr_t>(a->mask) & 15) == 0 &&
-        env_int("CAN_B200_TMAMASK", 1) != 0) {
+        a->mode == CAN_MODE_STORE && env_int("CAN_B200_TMAMASK", 1) != 0) {
       const uint64_t mcs = static_cast<uint64_t>(a->mask_cs) * 2;
       const uint64_t strM[3] = {mcs, mcs * a->W, mcs * a->W * a->H};
       rc = make_tmap(&tmM, static_cast<const __nv_bfloat16*>(a->mask) + a->mask_coff, 4, dimsO, strM, boxO);

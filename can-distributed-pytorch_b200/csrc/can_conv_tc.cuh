@@ -228,9 +228,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tmem_full_bar = empty_bar + 8;    // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;  // [2]
   uint64_t* w_bar = tmem_empty_bar + 2;          // HALO: resident weights landed
-  uint64_t* out_free_bar = w_bar + 1;            // staged output: the previous tile's TMA store has read s_out
-  uint64_t* out_full_bar = out_free_bar + 1;     // staged output: every epilogue thread has written its part of s_out
-  uint64_t* mask_full_bar = out_full_bar + 1;    // [2] staged mask tile landed
+  uint64_t* out_free_bar = w_bar + 1;            // [2] staged output: the TMA store has read this s_out buffer
+  uint64_t* out_full_bar = out_free_bar + 2;     // [2] staged output: every epilogue thread has written its part of it
+  uint64_t* mask_full_bar = out_full_bar + 2;    // [2] staged mask tile landed
   uint64_t* mask_free_bar = mask_full_bar + 2;   // [2] every epilogue thread is done with it
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(mask_free_bar + 2);
   float* s_bias2 = reinterpret_cast<float*>(tail + 1024);  // [2][BN]
@@ -280,8 +280,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_init(&tmem_empty_bar[a], 32 * EW);  // every epilogue thread arrives
       }
       mbar_init(w_bar, 1);
-      mbar_init(out_free_bar, 1);
-      mbar_init(out_full_bar, 32 * EW);
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&out_free_bar[a], 1);
+        mbar_init(&out_full_bar[a], 32 * EW);
+      }
       for (int a = 0; a < 2; ++a) {
         mbar_init(&mask_full_bar[a], 1);
         mbar_init(&mask_free_bar[a], 32 * EW);
@@ -437,7 +439,28 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 2 + EW) {
     // ===================== output warp (staged epilogue only) =====================
     // hands each staged tile to TMA and waits until it has been read, so no epilogue warp ever stalls on that
-    if (p.out_stage_bytes && elect_one()) {
+    // (one elect.sync for the whole warp: a second one in an else-branch would wait for the elected lane forever)
+    const bool out_lane = p.out_stage_bytes && elect_one();
+    if (MODE == MODE_UNPOOL && out_lane) {
+      // four rounds per tile (one per position of the 2x2 window), two staging buffers; tmO strides by 2 in x and y
+      int R = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        CAN_TILE_DECODE(tile)
+        for (int r = 0; r < 4; ++r, ++R) {
+          const int b = R & 1;
+          mbar_wait(&out_full_bar[b], static_cast<uint32_t>(R >> 1) & 1u);
+#pragma unroll
+          for (int blk = 0; blk < BN / 64; ++blk)
+            tma_store_4d(&tmO, s_out + b * (BN * 256) + blk * 16384, n0 + blk * 64, 2 * x0 + (r & 1), 2 * y0 + (r >> 1),
+                         n_img);
+          bulk_commit_group();
+          bulk_wait_group_read1();                      // the previous round's store has read its buffer
+          if (R > 0) mbar_arrive(&out_free_bar[b ^ 1]);
+        }
+      }
+      bulk_wait_group_read0();
+      if (R > 0) mbar_arrive(&out_free_bar[(R - 1) & 1]);
+    } else if (out_lane) {
       int it = 0;
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
         CAN_TILE_DECODE(tile)
@@ -674,6 +697,81 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (valid && obase) store_bf16_planes<NSPLIT, 32>(obase + c0, p.out_plane, v);
       }
       if (valid) p.head_out[pix] = dot + __ldg(p.head_b);
+    } else if (MODE == MODE_UNPOOL && NSPLIT == 1 && CW <= 64 && p.out_stage_bytes > 0) {
+      // staged variant: gradients of this thread's CW channels stay in registers; one round per window position
+      // writes a (TH x TW) sub-tile of the 2x upsampled map to shared memory, the output warp stores it with TMA
+      const long long pix = valid ? (static_cast<long long>(n_img) * p.H + y) * p.W + x : 0;
+      const __nv_bfloat16* mbase = p.mask + pix * p.mask_cs + p.mask_coff + n0;
+      const uint8_t* abase = p.arg + pix * p.arg_cs + n0;
+      constexpr int NI = CW / 32;
+      float g[NI][32];
+      uint32_t code[NI][8];
+#pragma unroll
+      for (int ci = 0; ci < NI; ++ci) {
+        const int c0 = cbeg + ci * 32;
+        float r[32];
+        load_acc<BN, GS, 32>(taddr, c0, nact, r);
+        uint4 mcur[4], a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) mcur[i] = make_uint4(0, 0, 0, 0);
+        if (valid) {
+          if (ci == 0) {
+            a0 = pre_a[0];
+            a1 = pre_a[1];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) mcur[i] = pre_m[i];
+          } else {
+            a0 = *reinterpret_cast<const uint4*>(abase + c0);
+            a1 = *reinterpret_cast<const uint4*>(abase + c0 + 16);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) mcur[i] = *reinterpret_cast<const uint4*>(mbase + c0 + 8 * i);
+          }
+        }
+        code[ci][0] = a0.x; code[ci][1] = a0.y; code[ci][2] = a0.z; code[ci][3] = a0.w;
+        code[ci][4] = a1.x; code[ci][5] = a1.y; code[ci][6] = a1.z; code[ci][7] = a1.w;
+#pragma unroll
+        for (int i = 0; i < 32; i += 8) {
+          const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mcur[i >> 3]);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) g[ci][i + e] = (__bfloat162float(mb[e]) > 0.f) ? r[i + e] : 0.f;   // mask 0 when !valid
+        }
+        if (kDbRegMode && db_reg) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) dbacc[kDbRegMode ? i : 0] += g[ci][i];
+        } else if (p.db) {
+          float t[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) t[i] = g[ci][i];
+          atomicAdd(&s_db[n0 + c0 + lane], warp_column_sums(t, lane));
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tmem_empty_bar[as]);   // the accumulator is in registers now
+#pragma unroll 1
+      for (int wpos = 0; wpos < 4; ++wpos) {
+        const int R = it * 4 + wpos, b = R & 1;
+        mbar_wait(&out_free_bar[b], (static_cast<uint32_t>(R >> 1) & 1u) ^ 1u);
+#pragma unroll
+        for (int ci = 0; ci < NI; ++ci) {
+          const int c0 = cbeg + ci * 32;
+          uint8_t* row = s_out + b * (BN * 256) + (c0 >> 6) * 16384 + m * 128;
+#pragma unroll
+          for (int i = 0; i < 32; i += 8) {
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const int cd = (code[ci][(i + e) >> 2] >> (((i + e) & 3) * 8)) & 0xff;
+              v[e] = (cd == wpos) ? g[ci][i + e] : 0.f;
+            }
+            const int chunk = ((c0 & 63) + i) >> 3;
+            *reinterpret_cast<uint4*>(row + ((chunk ^ (m & 7)) << 4)) =
+                make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+          }
+        }
+        fence_proxy_async();
+        mbar_arrive(&out_full_bar[b]);
+      }
+      continue;   // (accumulator already released above)
     } else if (MODE == MODE_UNPOOL) {
       // this GEMM runs on the pooled grid (H x W); gradients land on the OH x OW map
       const long long pix = (static_cast<long long>(n_img) * p.H + y) * p.W + x;

@@ -9,11 +9,6 @@
 
 namespace canb {
 
-#ifndef CAN_SPIN_LIMIT
-// Bounded spins: a protocol bug traps (-> cudaErrorLaunchFailure) instead of
-// hanging the GPU box.  ~2^28 polls is seconds, far above any legitimate wait.
-#define CAN_SPIN_LIMIT (1u << 28)
-#endif
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -62,10 +57,28 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+__device__ __forceinline__ uint64_t global_timer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// Time-bounded wait: a protocol bug traps (-> cudaErrorLaunchFailure) after CAN_WAIT_LIMIT_NS instead of
+// hanging the GPU box (a failed try_wait may itself suspend for an implementation-defined time, so the
+// bound is on wall-clock time, not on the number of polls).
+#ifndef CAN_WAIT_LIMIT_NS
+#define CAN_WAIT_LIMIT_NS 4000000000ull
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const uint64_t t0 = global_timer_ns();
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > CAN_SPIN_LIMIT) __trap();
+    if ((++spins & 0xff) == 0 && global_timer_ns() - t0 > CAN_WAIT_LIMIT_NS) {
+#ifdef CAN_MBAR_DEBUG
+      printf("mbar timeout: block %d thread %d bar@%u parity %u\n", blockIdx.x, threadIdx.x, smem_u32(bar), parity);
+#endif
+      __trap();
+    }
   }
 }
 
@@ -112,6 +125,8 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* s
                : "memory");
 }
 __device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all but the most recent bulk group of this thread have finished reading shared memory
+__device__ __forceinline__ void bulk_wait_group_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 // all of this thread's bulk groups have finished READING shared memory (the global writes may still be in flight)
 __device__ __forceinline__ void bulk_wait_group_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 
