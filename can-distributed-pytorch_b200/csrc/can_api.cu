@@ -458,6 +458,17 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     const uint32_t boxT[5] = {64, 256, 1, 1, 1};
     rc = make_tmap(&tmT, a->ctx_ttab, 5, dimsT, strT, boxT);
     if (rc) return rc;
+    if (a->mode == CAN_MODE_CTX2_BWD && a->out && env_int("CAN_B200_TMASTORE", 1) != 0) {
+      // the eight output segments of a tile leave through TMA stores of [pixel][16 ch] sub-tiles (2 x 32 KB staging)
+      const uint64_t cs = static_cast<uint64_t>(a->out_cs) * 2;
+      const uint64_t dimsD[4] = {4096, static_cast<uint64_t>(a->W), static_cast<uint64_t>(a->H), static_cast<uint64_t>(a->N)};
+      const uint64_t strD[3] = {cs, cs * a->W, cs * a->W * a->H};
+      const uint32_t boxD[4] = {16, static_cast<uint32_t>(p.TW), static_cast<uint32_t>(p.TH), 1};
+      rc = make_tmap(&tmO, a->out, 4, dimsD, strD, boxD, false);
+      if (rc) return rc;
+      g_tmO = &tmO;
+      p.out_stage_bytes = 65536;
+    }
     g_tmW = &tmW;
     g_tmT = &tmT;
     rc = a->mode == CAN_MODE_CTX2 ? launch_conv<256, 1, MODE_CTX2>(tmA, tmB, p, grid, so, st)

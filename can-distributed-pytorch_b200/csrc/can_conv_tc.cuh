@@ -460,6 +460,26 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       bulk_wait_group_read0();
       if (R > 0) mbar_arrive(&out_free_bar[(R - 1) & 1]);
+    } else if (MODE == MODE_CTX2_BWD && out_lane) {
+      // four rounds per tile, eight segment stores per round (tmO: box (16 ch, TW, TH), no swizzle)
+      int R = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        CAN_TILE_DECODE(tile)
+        (void)n0;
+        for (int r = 0; r < 4; ++r, ++R) {
+          const int b = R & 1;
+          mbar_wait(&out_full_bar[b], static_cast<uint32_t>(R >> 1) & 1u);
+#pragma unroll
+          for (int sg = 0; sg < 8; ++sg)   // sg < 4: dz_j -> channel j*512 + ..; sg >= 4: ds_j -> 2048 + j*512 + ..
+            tma_store_4d(&tmO, s_out + b * 32768 + sg * 4096, (sg >> 2) * 2048 + (sg & 3) * 512 + n_tile * 64 + 16 * r, x0, y0,
+                         n_img);
+          bulk_commit_group();
+          bulk_wait_group_read1();
+          if (R > 0) mbar_arrive(&out_free_bar[b ^ 1]);
+        }
+      }
+      bulk_wait_group_read0();
+      if (R > 0) mbar_arrive(&out_free_bar[(R - 1) & 1]);
     } else if (out_lane) {
       int it = 0;
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
@@ -545,7 +565,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const long long pix_ = valid ? (static_cast<long long>(n_img) * p.H + y) * p.W + x : 0;
       if (p.mask && valid && !p.mask_bufs)
         pre_mbase = p.mask + pix_ * p.mask_cs + p.mask_coff +
-                    (MODE == MODE_CTX2_BWD ? n_tile * 64 + ((warp - 2) >> 2) * (64 / (EW / 4)) : n0 + cbeg);
+                    (MODE == MODE_CTX2_BWD ? n_tile * 64 + ((warp - 2) >> 2) * (p.out_stage_bytes ? 8 : 64 / (EW / 4))
+                                           : n0 + cbeg);
       if (MODE == MODE_UNPOOL && valid) pre_abase = p.arg + pix_ * p.arg_cs + n0 + cbeg;
       if (pre_mbase) {
         pre_m[0] = *reinterpret_cast<const uint4*>(pre_mbase);
@@ -920,6 +941,64 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           fi[c] = num * rcp_fast(den + 1e-12f);
         }
         if (valid) store_bf16_planes<NSPLIT, 16>(obase + c0, p.out_plane, fi);
+      }
+    } else if (MODE == MODE_CTX2_BWD && NSPLIT == 1 && EW == 8 && p.out_stage_bytes > 0) {
+      // Staged variant of the branch below: four rounds per tile, round s covers channels 16 s .. 16 s + 15 of
+      // the n-tile (this warp: 8 of them), all eight output segments (dz_j, ds_j) of those channels go to a
+      // [segment][pixel][16 ch] staging buffer and leave through eight TMA stores issued by the output warp.
+      const long long pix = valid ? (static_cast<long long>(n_img) * p.H + y) * p.W + x : 0;
+      const __nv_bfloat16* gbase = p.mask + pix * p.mask_cs + p.mask_coff + n_tile * 64;
+      const int half = (warp - 2) >> 2;
+#pragma unroll 1
+      for (int s4 = 0; s4 < 4; ++s4) {
+        const int c0 = 16 * s4 + 8 * half;
+        uint32_t zr[4][8], sr[4][8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          tmem_ld_32x8(taddr + j * 64 + c0, zr[j]);
+          tmem_ld_32x8(taddr + 256 + j * 64 + c0, sr[j]);
+        }
+        tmem_ld_wait();
+        float g[8];
+        {
+          const uint4 gq = pre_m[0];
+          if (valid && s4 < 3) pre_m[0] = *reinterpret_cast<const uint4*>(gbase + c0 + 16);
+          const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(&gq);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) g[e] = valid ? __bfloat162float(gb[e]) : 0.f;
+        }
+        float dz[4][8], ds[4][8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          float wj[4], num = 0.f, den = 0.f;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            wj[j] = sigmoid_neg_fast(__uint_as_float(zr[j][c]));
+            num = fmaf(wj[j], __uint_as_float(sr[j][c]), num);
+            den += wj[j];
+          }
+          const float dinv = rcp_fast(den + 1e-12f);
+          const float fiv = num * dinv;
+          const float gd = g[c] * dinv;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            ds[j][c] = gd * wj[j];
+            dz[j][c] = gd * (__uint_as_float(sr[j][c]) - fiv) * wj[j] * (1.f - wj[j]);
+          }
+        }
+        const int R = it * 4 + s4, b = R & 1;
+        mbar_wait(&out_free_bar[b], (static_cast<uint32_t>(R >> 1) & 1u) ^ 1u);
+        uint8_t* row = s_out + b * 32768 + m * 32 + half * 16;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          *reinterpret_cast<uint4*>(row + j * 4096) = make_uint4(pack_bf16x2(dz[j][0], dz[j][1]), pack_bf16x2(dz[j][2], dz[j][3]),
+                                                                 pack_bf16x2(dz[j][4], dz[j][5]), pack_bf16x2(dz[j][6], dz[j][7]));
+          *reinterpret_cast<uint4*>(row + (4 + j) * 4096) =
+              make_uint4(pack_bf16x2(ds[j][0], ds[j][1]), pack_bf16x2(ds[j][2], ds[j][3]), pack_bf16x2(ds[j][4], ds[j][5]),
+                         pack_bf16x2(ds[j][6], ds[j][7]));
+        }
+        fence_proxy_async();
+        mbar_arrive(&out_full_bar[b]);
       }
     } else if (MODE == MODE_CTX2_BWD) {
       // Same TMEM contents as MODE_CTX2 (-z_j | s_j).  With D = sum_j w_j + 1e-12 and g = dL/dfi:
