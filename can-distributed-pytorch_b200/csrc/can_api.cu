@@ -266,6 +266,16 @@ int launch_ctx_gemv(const float* Wm, const float* in, long long in_ns, long long
   return 0;
 }
 
+// cout, cin multiples of 32; taps <= 9
+void launch_pack(const float* w, __nv_bfloat16* fwd, __nv_bfloat16* dgrad, int cout, int cin, int taps, int nsplit,
+                 cudaStream_t st) {
+  const dim3 grid(cin / 32, cout / 32);
+  const size_t smem = 32 * (32 * taps + 1) * sizeof(float);
+  if (taps == 9) pack_conv_weight_kernel_v3<9><<<grid, 256, smem, st>>>(w, fwd, dgrad, cout, cin, nsplit);
+  else if (taps == 1) pack_conv_weight_kernel_v3<1><<<grid, 256, smem, st>>>(w, fwd, dgrad, cout, cin, nsplit);
+  else pack_conv_weight_kernel_v2<<<grid, 256, smem, st>>>(w, fwd, dgrad, cout, cin, taps, nsplit);
+}
+
 }  // namespace
 
 extern "C" {
@@ -510,9 +520,7 @@ int can_pack_conv_weight(const float* w, void* dst, int cout, int cin, int taps,
     return fail(-1, "pack_conv_weight: bad arguments");
   if (cout % 32 == 0 && cin % 32 == 0 && taps <= 9) {
     __nv_bfloat16* d = static_cast<__nv_bfloat16*>(dst);
-    pack_conv_weight_kernel_v2<<<dim3(cin / 32, cout / 32), 256, 32 * (32 * taps + 1) * sizeof(float),
-                                 static_cast<cudaStream_t>(stream)>>>(w, dgrad ? nullptr : d, dgrad ? d : nullptr, cout,
-                                                                      cin, taps, nsplit);
+    launch_pack(w, dgrad ? nullptr : d, dgrad ? d : nullptr, cout, cin, taps, nsplit, static_cast<cudaStream_t>(stream));
   } else {
     const long long total = static_cast<long long>(cout) * cin * taps;
     const int blocks = static_cast<int>((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256);
@@ -845,8 +853,8 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
     rc = launch_wgrad<256, 1, 1>(tmDZ, tmX, p, grid, st);
   }
   if (rc) return rc;
-  wgrad_reduce_kernel_v2<<<dim3(Cin / 32, Cout), 32 * taps, 0, st>>>(p.ws, grad, pl.ksplit, taps, Cout, Cin, accumulate,
-                                                                     alpha);
+  wgrad_reduce_kernel_v3<<<dim3((Cin + 127) / 128, Cout), 32 * taps, 0, st>>>(p.ws, grad, pl.ksplit, taps, Cout, Cin,
+                                                                              accumulate, alpha);
   CAN_CHECK_LAUNCH("wgrad_reduce");
   return 0;
 }
@@ -1002,10 +1010,8 @@ int can_pack_conv_weight_both(const float* w, void* dst_fwd, void* dst_dgrad, in
   if (!w || (!dst_fwd && !dst_dgrad) || cout <= 0 || cin <= 0 || taps <= 0 || taps > 9 || nsplit < 1 || nsplit > 3)
     return fail(-1, "pack_conv_weight_both: bad arguments");
   if (cout % 32 || cin % 32) return fail(-2, "pack_conv_weight_both: cout and cin must be multiples of 32");
-  pack_conv_weight_kernel_v2<<<dim3(cin / 32, cout / 32), 256, 32 * (32 * taps + 1) * sizeof(float),
-                               static_cast<cudaStream_t>(stream)>>>(w, static_cast<__nv_bfloat16*>(dst_fwd),
-                                                                    static_cast<__nv_bfloat16*>(dst_dgrad), cout, cin,
-                                                                    taps, nsplit);
+  launch_pack(w, static_cast<__nv_bfloat16*>(dst_fwd), static_cast<__nv_bfloat16*>(dst_dgrad), cout, cin, taps, nsplit,
+              static_cast<cudaStream_t>(stream));
   CAN_CHECK_LAUNCH("pack_conv_weight_both");
   return 0;
 }

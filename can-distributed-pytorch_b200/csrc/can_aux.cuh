@@ -160,6 +160,111 @@ pack_conv_weight_kernel_v2(const float* __restrict__ w, __nv_bfloat16* __restric
   }
 }
 
+// Third-generation reduction of the split-K partials (same contract as wgrad_reduce_kernel_v2):
+//   grad[co][ci][tap] = (accumulate ? grad : 0) + alpha * sum_s ws[s][tap][co][ci]
+// grid (ceil(cin/128), cout), block 32*taps: every thread owns four consecutive ci of one tap (16-byte loads,
+// up to four splits in flight), the block transposes 128 ci x taps through shared memory and writes
+// 128*taps contiguous floats.
+__global__ void wgrad_reduce_kernel_v3(const float* __restrict__ ws, float* __restrict__ grad, int splits, int taps,
+                                       int cout, int cin, int accumulate, float alpha) {
+  __shared__ float s_t[128 * 9];
+  const int co = blockIdx.y, ci0 = blockIdx.x * 128;
+  const int lane = threadIdx.x & 31, tap = threadIdx.x >> 5;
+  const int c4 = lane * 4;
+  const int nci = min(128, cin - ci0);
+  const long long slab = static_cast<long long>(taps) * cout * cin;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (c4 < nci) {
+    const float* src = ws + (static_cast<long long>(tap) * cout + co) * cin + ci0 + c4;
+    int sp = 0;
+    for (; sp + 4 <= splits; sp += 4) {
+      const float4 a0 = *reinterpret_cast<const float4*>(src + (sp + 0) * slab);
+      const float4 a1 = *reinterpret_cast<const float4*>(src + (sp + 1) * slab);
+      const float4 a2 = *reinterpret_cast<const float4*>(src + (sp + 2) * slab);
+      const float4 a3 = *reinterpret_cast<const float4*>(src + (sp + 3) * slab);
+      acc.x += (a0.x + a1.x) + (a2.x + a3.x);
+      acc.y += (a0.y + a1.y) + (a2.y + a3.y);
+      acc.z += (a0.z + a1.z) + (a2.z + a3.z);
+      acc.w += (a0.w + a1.w) + (a2.w + a3.w);
+    }
+    for (; sp < splits; ++sp) {
+      const float4 a = *reinterpret_cast<const float4*>(src + sp * slab);
+      acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+    }
+  }
+  s_t[(c4 + 0) * taps + tap] = acc.x;
+  s_t[(c4 + 1) * taps + tap] = acc.y;
+  s_t[(c4 + 2) * taps + tap] = acc.z;
+  s_t[(c4 + 3) * taps + tap] = acc.w;
+  __syncthreads();
+  float* g = grad + (static_cast<long long>(co) * cin + ci0) * taps;
+  const int n = nci * taps;
+  for (int j = threadIdx.x; j < n; j += blockDim.x) g[j] = (accumulate ? g[j] : 0.f) + alpha * s_t[j];
+}
+
+// Third-generation weight packing (same contract as pack_conv_weight_kernel_v2): all loads of a thread are
+// issued before the first dependent shared-memory store (the v2 loop paid the memory latency nine times).
+template <int TAPS>
+__global__ void __launch_bounds__(256)
+pack_conv_weight_kernel_v3(const float* __restrict__ w, __nv_bfloat16* __restrict__ fwd,
+                           __nv_bfloat16* __restrict__ dgrad, int cout, int cin, int nsplit) {
+  extern __shared__ float s_w[];  // [32 co][32*TAPS + 1]
+  constexpr int taps = TAPS;
+  const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 32;
+  constexpr int row = 32 * TAPS + 1;
+  constexpr int per_row = 32 * TAPS, tot = 32 * per_row;
+  constexpr int NL = (tot + 255) / 256;   // 36 (3x3) or 4 (1x1)
+  {
+    float v[NL];
+#pragma unroll
+    for (int u = 0; u < NL; ++u) {
+      const int i = threadIdx.x + u * 256;
+      const int r = i / per_row, o = i - r * per_row;
+      v[u] = (i < tot) ? __ldg(w + (static_cast<long long>(co0 + r) * cin + ci0) * taps + o) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < NL; ++u) {
+      const int i = threadIdx.x + u * 256;
+      const int r = i / per_row, o = i - r * per_row;
+      if (i < tot) s_w[r * row + o] = v[u];
+    }
+  }
+  __syncthreads();
+  const long long total = static_cast<long long>(cout) * cin * taps;
+  if (fwd) {
+    for (int idx = threadIdx.x; idx < 32 * taps * 4; idx += 256) {
+      const int qd = idx & 3, rt = idx >> 2;
+      const int r = rt / taps, tap = rt - r * taps;
+      float v[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] = s_w[r * row + (qd * 8 + e) * taps + tap];
+      __nv_bfloat16* d = fwd + (static_cast<long long>(co0 + r) * taps + tap) * cin + ci0 + qd * 8;
+      for (int pl = 0; pl < nsplit; ++pl) {
+        *reinterpret_cast<uint4*>(d + pl * total) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                               pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] -= bf16_round(v[e]);
+      }
+    }
+  }
+  if (dgrad) {
+    for (int idx = threadIdx.x; idx < 32 * taps * 4; idx += 256) {
+      const int qd = idx & 3, rt = idx >> 2;
+      const int ci = rt / taps, tap = rt - ci * taps;
+      float v[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] = s_w[(qd * 8 + e) * row + ci * taps + tap];
+      __nv_bfloat16* d = dgrad + (static_cast<long long>(ci0 + ci) * taps + (taps - 1 - tap)) * cout + co0 + qd * 8;
+      for (int pl = 0; pl < nsplit; ++pl) {
+        *reinterpret_cast<uint4*>(d + pl * total) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                               pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] -= bf16_round(v[e]);
+      }
+    }
+  }
+}
+
 // im2col of the 3-channel image (second generation): out[pl][n][y][x][k], k = ci*9 + r*3 + s for
 // k < 27, zero for 27 <= k < 64.  One block = one image row segment of 128 pixels: the 3 x 3 x 130
 // input window is staged in shared memory with coalesced loads; eight threads cooperate on one
