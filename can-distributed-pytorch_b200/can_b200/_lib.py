@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcan_b200.so")
+# CAN_B200_LIB: another build of the same library (A/B measurements of two builds inside one GPU session)
+LIB_PATH = os.environ.get("CAN_B200_LIB") or os.path.join(_HERE, "libcan_b200.so")
 
 MODE_STORE, MODE_POOL, MODE_HEAD, MODE_UNPOOL, MODE_CTX, MODE_CTX_BWD, MODE_DFV, MODE_CTX2, MODE_CTX2_BWD = range(9)
 

@@ -140,7 +140,9 @@ struct AccLayout {
   static constexpr int kCols = (GS >= 2) ? 512 : (BN < 32 ? 32 : BN);
   static constexpr int cols(int mode) { return (mode == MODE_CTX2 || mode == MODE_CTX2_BWD) ? 512 : kCols; }
   // two accumulator stages when they fit: the epilogue of tile i overlaps the MMAs of tile i+1
-  static constexpr int acc_stages(int mode) { return cols(mode) * 2 <= 512 ? 2 : 1; }
+  // up to four accumulator stages: with narrow tiles an MMA tile lasts ~1 us, so any hiccup of the epilogue
+  // (a barrier, a TMA hand-over) stalls the tensor pipe unless the MMA warp can run several tiles ahead
+  static constexpr int acc_stages(int mode) { return cols(mode) * 4 <= 512 ? 4 : (cols(mode) * 2 <= 512 ? 2 : 1); }
 };
 
 template <int NV>
@@ -225,9 +227,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint8_t* tail = ring + stages * stage_bytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
   uint64_t* empty_bar = full_bar + 8;
-  uint64_t* tmem_full_bar = empty_bar + 8;    // [2]
-  uint64_t* tmem_empty_bar = tmem_full_bar + 2;  // [2]
-  uint64_t* w_bar = tmem_empty_bar + 2;          // HALO: resident weights landed
+  uint64_t* tmem_full_bar = empty_bar + 8;    // [4]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 4;  // [4]
+  uint64_t* w_bar = tmem_empty_bar + 4;          // HALO: resident weights landed
   uint64_t* out_free_bar = w_bar + 1;            // [2] staged output: the TMA store has read this s_out buffer
   uint64_t* out_full_bar = out_free_bar + 2;     // [2] staged output: every epilogue thread has written its part of it
   uint64_t* mask_full_bar = out_full_bar + 2;    // [2] staged mask tile landed
@@ -275,7 +277,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_init(&full_bar[s], 1);
         mbar_init(&empty_bar[s], 1);
       }
-      for (int a = 0; a < 2; ++a) {
+      for (int a = 0; a < 4; ++a) {
         mbar_init(&tmem_full_bar[a], 1);
         mbar_init(&tmem_empty_bar[a], 32 * EW);  // every epilogue thread arrives
       }
@@ -534,8 +536,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     CAN_TILE_DECODE(tile)
     const int as = it % ACC_STAGES;
     const uint32_t aphase = static_cast<uint32_t>(it / ACC_STAGES) & 1u;
-    float* s_bias = s_bias2 + (it & 1) * BN;
-    for (int i = etid; i < BN; i += 32 * EW) s_bias[i] = p.bias ? p.bias[n0 + i] : 0.f;
+    // single n-tile: the bias slice never changes -> staged once (tile 0), no global load + barrier per tile
+    const bool bias_once = (p.n_tiles == 1) && MODE != MODE_CTX && MODE != MODE_CTX_BWD;
+    float* s_bias = s_bias2 + (bias_once ? 0 : (it & 1) * BN);
+    if (!bias_once || it == 0)
+      for (int i = etid; i < BN; i += 32 * EW) s_bias[i] = p.bias ? p.bias[n0 + i] : 0.f;
     if (MODE == MODE_CTX || MODE == MODE_CTX_BWD) {
       asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");  // everyone finished reading the previous tile's tables
       // tables of this image for the 64 channels of this n-tile: [2][50][64]
@@ -548,7 +553,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             *reinterpret_cast<const float4*>(gb + pos * 512 + c4);
       }
     }
-    asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
+    if (!bias_once || it == 0) asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
 
     const int y = y0 + ty, x = x0 + tx;
     const bool valid = (y < p.H) && (x < p.W);
