@@ -425,7 +425,8 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     int rc = make_tmap(&tmO, static_cast<__nv_bfloat16*>(a->out) + a->out_coff, 4, dimsO, strO, boxO);
     if (rc) return rc;
     g_tmO = &tmO;
-    p.out_stage_bytes = bn * 256;
+    p.out_bufs = (bn == 64 && env_int("CAN_B200_OUTBUFS", 2) == 2) ? 2 : 1;
+    p.out_stage_bytes = p.out_bufs * bn * 256;
     if (a->mask && a->mask_cs % 8 == 0 && a->mask_coff % 8 == 0 && (reinterpret_cast<uintptr_t>(a->mask) & 15) == 0 &&
         a->mode == CAN_MODE_STORE && env_int("CAN_B200_TMAMASK", 1) != 0) {
       const uint64_t mcs = static_cast<uint64_t>(a->mask_cs) * 2;
@@ -447,8 +448,14 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
            1024 + p.out_stage_bytes + p.mask_bufs * bn * 256 + p.w_bytes + 2 * p.halo_bytes + 8192 > kMaxSmem)
       --p.mask_bufs;
     if (!p.mask_bufs) g_tmM = nullptr;
+    if (a->mode == CAN_MODE_STORE && p.out_bufs == 2 &&
+        1024 + p.out_stage_bytes + p.mask_bufs * bn * 256 + p.w_bytes + 3 * p.halo_bytes + 8192 > kMaxSmem) {
+      p.out_bufs = 1;   // keep at least three halo stages
+      p.out_stage_bytes = bn * 256;
+    }
     if (p.out_stage_bytes && 1024 + p.out_stage_bytes + p.w_bytes + 2 * p.halo_bytes + 8192 > kMaxSmem) {
       p.out_stage_bytes = 0;
+      p.out_bufs = 0;
       g_tmO = nullptr;
     }
     CUtensorMap tmH;

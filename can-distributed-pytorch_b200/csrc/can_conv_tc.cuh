@@ -44,6 +44,7 @@ struct ConvTcParams {
   int w_bytes;         // HALO: bytes of the resident weight region (9 * kchunks * BN * 128)
   int halo_bytes;      // HALO: bytes of one activation stage ((TH + 2 dil) * TW * 128)
   int out_stage_bytes; // > 0: the epilogue stages the bf16 tile in shared memory (BN * 256 B) and writes it with TMA (tmO)
+  int out_bufs;        // MODE_STORE staged epilogue: 1 or 2 staging buffers of BN * 256 B (out_stage_bytes = their sum)
   int mask_bufs;       // staged epilogue: 0 = mask read from global memory, 1|2 = mask tiles (BN * 256 B each) brought in by TMA (tmM)
   int relu;
   const float* bias;   // [Cout] or null
@@ -483,15 +484,27 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       bulk_wait_group_read0();
       if (R > 0) mbar_arrive(&out_free_bar[(R - 1) & 1]);
     } else if (out_lane) {
+      const int nb = p.out_bufs;   // 1 or 2
       int it = 0;
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
         CAN_TILE_DECODE(tile)
-        mbar_wait(out_full_bar, static_cast<uint32_t>(it) & 1u);
+        const int b = it % nb;
+        mbar_wait(&out_full_bar[b], static_cast<uint32_t>(it / nb) & 1u);
 #pragma unroll
-        for (int blk = 0; blk < BN / 64; ++blk) tma_store_4d(&tmO, s_out + blk * 16384, n0 + blk * 64, x0, y0, n_img);
+        for (int blk = 0; blk < BN / 64; ++blk)
+          tma_store_4d(&tmO, s_out + b * (BN * 256) + blk * 16384, n0 + blk * 64, x0, y0, n_img);
         bulk_commit_group();
+        if (nb == 1) {
+          bulk_wait_group_read0();
+          mbar_arrive(&out_free_bar[0]);
+        } else {
+          bulk_wait_group_read1();                         // the previous tile's store has read its buffer
+          if (it > 0) mbar_arrive(&out_free_bar[b ^ 1]);
+        }
+      }
+      if (nb == 2 && it > 0) {
         bulk_wait_group_read0();
-        mbar_arrive(out_free_bar);
+        mbar_arrive(&out_free_bar[(it - 1) & 1]);
       }
     }
   } else if (warp == 3 + EW) {
@@ -590,7 +603,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tc_fence_after();
 
     const bool kStaged = (MODE == MODE_STORE) && NSPLIT == 1 && BN <= 128 && p.out_stage_bytes > 0;
-    if (kStaged) mbar_wait(out_free_bar, static_cast<uint32_t>(it & 1) ^ 1u);  // previous tile's store has read s_out
+    const int ob_i = kStaged ? it % p.out_bufs : 0;     // staging buffer of this tile
+    bool out_buf_ready = false;                         // (waited for as late as possible: just before the first write)
     const bool kMaskStaged = kStaged && p.mask_bufs > 0;
     const int mb_i = kMaskStaged ? it % p.mask_bufs : 0;
     if (kMaskStaged) mbar_wait(&mask_full_bar[mb_i], static_cast<uint32_t>(it / p.mask_bufs) & 1u);
@@ -637,8 +651,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
           }
           if (kStaged) {
+            if (!out_buf_ready) {   // the store that last used this buffer has read it
+              mbar_wait(&out_free_bar[ob_i], (static_cast<uint32_t>(it / p.out_bufs) & 1u) ^ 1u);
+              out_buf_ready = true;
+            }
             // 16-byte chunks into the 128B-swizzled [64-ch block][pixel][64 ch] staging tile
-            uint8_t* row = s_out + (c0 >> 6) * 16384 + m * 128;
+            uint8_t* row = s_out + ob_i * (BN * 256) + (c0 >> 6) * 16384 + m * 128;
 #pragma unroll
             for (int i = 0; i < 32; i += 8) {
               uint4 q;
@@ -1242,7 +1260,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // generic-proxy writes of s_out -> visible to the async proxy, then tell the output warp
       // (out-of-image pixels of edge tiles are clipped by the tensor map)
       fence_proxy_async();
-      mbar_arrive(out_full_bar);
+      mbar_arrive(&out_full_bar[ob_i]);
       if (kMaskStaged) mbar_arrive(&mask_free_bar[mb_i]);
     }
     }  // tile loop
