@@ -11,6 +11,7 @@ Nothing in the step reads a value back to the host: the loss stays on the device
 """
 from __future__ import annotations
 
+import os
 import sys
 
 import torch
@@ -62,10 +63,45 @@ class FusedTrainer:
         model._wcache.invalidate()
         if self.world > 1:  # identical initial weights on every rank (train.py:104-114 / DDP broadcast)
             dist.broadcast(self.arena, src=0, group=self.pg)
+        # Single-GPU steps of a fixed input shape are replayed from a CUDA graph after two eager steps: a step is
+        # ~120 kernel launches (~2.4 ms of host time), which a loop that reads the loss back every step would
+        # otherwise pay on the critical path.  CAN_B200_GRAPH=0 keeps every step eager.
+        self.use_graph = self.world == 1 and os.environ.get("CAN_B200_GRAPH", "1") != "0"
+        self._graphs = {}       # (img shape, gt shape) -> [eager steps seen, graph, static img, static gt, static loss]
 
     def step(self, img: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
         """One training step; returns the rank-mean of the local sum-losses as a device tensor [1]."""
+        if not self.use_graph or img.dtype != torch.float32 or gt.dtype != torch.float32:
+            return self._step_eager(img, gt)
+        key = (tuple(img.shape), tuple(gt.shape))
+        ent = self._graphs.setdefault(key, [0, None, None, None, None])
+        if ent[1] is None:
+            if ent[0] < 2 or self.first:
+                ent[0] += 1
+                return self._step_eager(img, gt)
+            try:
+                xs, gs = img.clone(), gt.clone()
+                graph = torch.cuda.CUDAGraph()
+                torch.cuda.synchronize()
+                with torch.cuda.graph(graph):
+                    loss = self._step_eager(xs, gs)
+                ent[1:] = [graph, xs, gs, loss]
+            except Exception as exc:  # noqa: BLE001 -- capture is an optimisation; eager stays correct
+                print(f"can_b200: CUDA graph capture of the training step failed ({exc}); staying eager", file=sys.stderr)
+                self.use_graph = False
+                torch.cuda.synchronize()
+                return self._step_eager(img, gt)
+        _, graph, xs, gs, loss = ent
+        xs.copy_(img, non_blocking=True)
+        gs.copy_(gt, non_blocking=True)
+        graph.replay()
+        ops.LAUNCHES += self._graph_launches
+        self.model._wcache.invalidate()   # the replay updated the arena: packed weights are stale for eager callers
+        return loss
+
+    def _step_eager(self, img: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
         m = self.model
+        launches0 = ops.LAUNCHES
         self.garena.zero_()  # bias / head gradients are accumulated with atomics (one 83 MB memset, ~13 us)
         out, saved = engine.forward(m, img, m.nsplit, save=True)
         loss, _, _, grad = ops.mse_count(out, gt, want_grad=True)
@@ -78,6 +114,7 @@ class FusedTrainer:
                               first=self.first)
         self.first = False
         m._wcache.invalidate()  # the arena changed in place: packed weights must be rebuilt
+        self._graph_launches = ops.LAUNCHES - launches0   # kernels of one step (what a graph replay launches)
         return loss
 
 

@@ -142,7 +142,8 @@ def test_backward_accumulates_like_autograd(dev):
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
 def test_fused_train_steps_match_oracle(dev, precision):
     """FusedTrainer (forward, fused loss, backward, fused SGD-momentum on the flat arena) against the
-    oracle's restatement of utils/train_eval_utils.py:28-52 + torch.optim.SGD, three steps."""
+    oracle's restatement of utils/train_eval_utils.py:28-52 + torch.optim.SGD, four steps (two eager, then the
+    CUDA-graph capture and a pure replay of the same step)."""
     from can_b200.utils.train_eval_utils import FusedTrainer
     regime, n, h, w = "he", 2, 48, 80
     sd = harness.make_state_dict(regime)
@@ -152,7 +153,7 @@ def test_fused_train_steps_match_oracle(dev, precision):
     m = _model(sd, precision, dev)
     tr = FusedTrainer(m, lr=lr, momentum=0.95)
     losses = []
-    for step in range(3):
+    for step in range(4):
         x, gt = harness.make_input(n, h, w, seed=100 + step), harness.make_gt(n, h, w, seed=200 + step)
         ref_losses.append(float(T.train_step(x.double(), gt.double(), ref_sd, bufs, lr, 0.95)))
         losses.append(float(tr.step(x.to(dev), gt.to(dev))))
