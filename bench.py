@@ -253,6 +253,8 @@ def main():
     # roofline of the dominant kernel: a second pass of the same steps with an event pair around
     # every conv_tc / wgrad launch (kept out of the timed region so it cannot perturb `value`)
     ops.PROFILE = []
+    if wl["train"]:
+        trainer.use_graph = False   # the event pairs live in the Python wrappers: this pass runs the same kernels eagerly
     torch.cuda.synchronize()
     for _ in range(min(args.steps, 5)):
         step_resident()

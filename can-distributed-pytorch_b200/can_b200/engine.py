@@ -237,8 +237,9 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
     dW2 = torch.empty(4, 512, 512, device=dev, dtype=torch.float32)
     ops.ctx_outer(da, 50 * 512, 512, 0, saved["pooled"], N, dW1)          # dW_j1 = sum da_j pool_j^T
     ops.ctx_outer(T, 64 * 4096, 4096, 512, saved["tabA"], N, dW2)         # dW_j2 = sum (U^T dz_j) a_j^T ...
+    # ... - dz_j fv^T: the four scales share fv, so one [2048 x 512] weight-gradient GEMM over all of them
+    ops.conv_wgrad(D.view(2048, 0), fv, dW2.view(2048, 512), taps=1, accumulate=True, alpha=-1.0)
     for j in range(4):
-        ops.conv_wgrad(D.view(512, j * 512), fv, dW2[j], taps=1, accumulate=True, alpha=-1.0)  # ... - dz_j fv^T
         grads[IDX_CTX + 2 * j].copy_(dW1[j].view(512, 512, 1, 1))
         grads[IDX_CTX + 2 * j + 1].copy_(dW2[j].view(512, 512, 1, 1))
     # dfv = dcat[:, :512] - sum_j W_j2^T dz_j + pool^T(dpool), gated by fv > 0  -> dZ of conv4_3

@@ -41,6 +41,8 @@ def main():
     torch.cuda.synchronize()
     print(f"plain step: {e0.elapsed_time(e1) / 5:.3f} ms (batch {B})")
     import time
+    if tr is not None:
+        tr.use_graph = False
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     step()
@@ -49,6 +51,8 @@ def main():
     torch.cuda.synchronize()
     print(f"host enqueue time: {(t1 - t0) / 2 * 1e3:.3f} ms per step")
     ops.PROFILE = []
+    if tr is not None:
+        tr.use_graph = False   # per-launch events need the eager wrappers
     step()
     torch.cuda.synchronize()
     prof, ops.PROFILE = ops.PROFILE, None
