@@ -178,6 +178,20 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
     tensors to fill, in parameter order, with bias / head entries already zeroed.
     ``on_ready(tag)`` is called after the gradients of 'backend', 'ctx' and 'frontend' have been
     enqueued (used to start the bucketed all-reduce while the rest of backward still runs)."""
+    gen = backward_steps(model, saved, grad_out, grads)
+    while True:
+        try:
+            tag = next(gen)
+        except StopIteration as done:
+            return done.value
+        if on_ready:
+            on_ready(tag)
+
+
+def backward_steps(model, saved, grad_out: torch.Tensor, grads=None):
+    """``backward`` as a generator: yields 'backend', 'ctx', 'frontend' right after the gradients of that bucket
+    have been enqueued, returns the gradient list.  (The data-parallel trainer captures each section as its own
+    CUDA graph and issues the NCCL all-reduces between the replays.)"""
     cache: WeightCache = model._wcache
     nsplit = saved["nsplit"]
     fr, bk = _conv_params(model)
@@ -209,8 +223,7 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
         else:
             ops.conv_tc(dz, wd, cin, dil=2, mode=MODE_STORE, relu=False, out=ndz)
             dcat = ndz
-    if on_ready:
-        on_ready("backend")
+    yield "backend"
 
     # ---- contextual module ----------------------------------------------------------
     w1s, w2s = _ctx_weights(model)
@@ -248,8 +261,7 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
     dz = ops.new_act(nsplit, N, h, w, 512, dev)
     ops.conv_tc(D.view(2048, 0), w2d, 512, taps=1, mode=MODE_DFV, relu=False, out=dz, mask=fv, add=dcat.view(512, 0),
                 tabA=dpool, db=grads[2 * 9 + 1])
-    if on_ready:
-        on_ready("ctx")
+    yield "ctx"
 
     # ---- frontend -------------------------------------------------------------------
     for li in range(9, 0, -1):
@@ -280,6 +292,5 @@ def backward(model, saved, grad_out: torch.Tensor, grads=None, on_ready=None):
         ops.conv_wgrad(dz, col, g0, taps=1)
         grads[0].copy_(g0[:, :27].reshape(64, 3, 3, 3))
     # (the bias gradient of conv1_1 was fused into conv1_2's dgrad)
-    if on_ready:
-        on_ready("frontend")
+    yield "frontend"
     return grads

@@ -66,8 +66,12 @@ class FusedTrainer:
         # Single-GPU steps of a fixed input shape are replayed from a CUDA graph after two eager steps: a step is
         # ~120 kernel launches (~2.4 ms of host time), which a loop that reads the loss back every step would
         # otherwise pay on the critical path.  CAN_B200_GRAPH=0 keeps every step eager.
-        self.use_graph = self.world == 1 and os.environ.get("CAN_B200_GRAPH", "1") != "0"
-        self._graphs = {}       # (img shape, gt shape) -> [eager steps seen, graph, static img, static gt, static loss]
+        # Data parallel: NCCL calls are not captured (capturing them hung here); the step is captured as four graphs
+        # (forward+loss+backend backward | contextual backward | frontend backward | SGD) sharing one memory pool,
+        # and the bucketed all-reduces are issued eagerly between the replays.
+        self.use_graph = os.environ.get("CAN_B200_GRAPH", "1") != "0" and (
+            self.world == 1 or (dist.get_backend(self.pg) == "nccl" and os.environ.get("CAN_B200_GRAPH_DP", "1") != "0"))
+        self._graphs = {}       # (img shape, gt shape) -> [eager steps seen, graph(s), static img, static gt, static loss]
 
     def step(self, img: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
         """One training step; returns the rank-mean of the local sum-losses as a device tensor [1]."""
@@ -81,10 +85,13 @@ class FusedTrainer:
                 return self._step_eager(img, gt)
             try:
                 xs, gs = img.clone(), gt.clone()
-                graph = torch.cuda.CUDAGraph()
                 torch.cuda.synchronize()
-                with torch.cuda.graph(graph):
-                    loss = self._step_eager(xs, gs)
+                if self.world == 1:
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph):
+                        loss = self._step_eager(xs, gs)
+                else:
+                    graph, loss = self._capture_dp(xs, gs)
                 ent[1:] = [graph, xs, gs, loss]
             except Exception as exc:  # noqa: BLE001 -- capture is an optimisation; eager stays correct
                 print(f"can_b200: CUDA graph capture of the training step failed ({exc}); staying eager", file=sys.stderr)
@@ -94,10 +101,44 @@ class FusedTrainer:
         _, graph, xs, gs, loss = ent
         xs.copy_(img, non_blocking=True)
         gs.copy_(gt, non_blocking=True)
-        graph.replay()
+        if self.world == 1:
+            graph.replay()
+        else:
+            for g, tag in zip(graph[:3], ("backend", "ctx", "frontend")):
+                g.replay()
+                self.buckets.ready(tag)
+            self.buckets.reduce_scalar(loss)   # (the static loss tensor; rewritten by the next replay)
+            self.buckets.wait()
+            graph[3].replay()
+            loss = loss / self.world
         ops.LAUNCHES += self._graph_launches
         self.model._wcache.invalidate()   # the replay updated the arena: packed weights are stale for eager callers
         return loss
+
+    def _capture_dp(self, xs, gs):
+        """Four graphs of one data-parallel step (no NCCL inside); nothing executes during capture."""
+        m = self.model
+        launches0 = ops.LAUNCHES
+        graphs = [torch.cuda.CUDAGraph() for _ in range(4)]
+        with torch.cuda.graph(graphs[0]):
+            self.garena.zero_()
+            out, saved = engine.forward(m, xs, m.nsplit, save=True)
+            loss, _, _, grad = ops.mse_count(out, gs, want_grad=True)
+            gen = engine.backward_steps(m, saved, grad, grads=self.gviews)
+            assert next(gen) == "backend"
+        pool = graphs[0].pool()
+        with torch.cuda.graph(graphs[1], pool=pool):
+            assert next(gen) == "ctx"
+        with torch.cuda.graph(graphs[2], pool=pool):
+            assert next(gen) == "frontend"
+            for _ in gen:   # runs the generator to its end (nothing left to enqueue)
+                pass
+        with torch.cuda.graph(graphs[3], pool=pool):
+            ops.sgd_momentum_step(self.arena, self.garena, self.buf, self.lr, self.momentum, self.buckets.grad_scale,
+                                  first=False)
+        self._graph_launches = ops.LAUNCHES - launches0
+        m._wcache.invalidate()
+        return graphs, loss
 
     def _step_eager(self, img: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
         m = self.model
