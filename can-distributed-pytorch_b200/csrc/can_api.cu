@@ -84,7 +84,7 @@ template <int BN, int NSPLIT, int MODE>
 int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p, dim3 grid, int stages_override,
                 cudaStream_t st) {
   using L = ConvTcSmem<BN, gemm_planes(NSPLIT, MODE)>;
-  const bool ctx = (MODE == MODE_CTX || MODE == MODE_CTX_BWD);
+  constexpr int ctx = MODE;   // (ConvTcSmem::bytes sizes the table region from the mode)
   const int staged_bytes = p.out_stage_bytes + p.mask_bufs * BN * 256;
   int stages = (kMaxSmem - L::bytes(0, ctx) - staged_bytes) / L::kStageBytes;
   if (stages > 8) stages = 8;
@@ -94,7 +94,7 @@ int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p,
   const int smem = L::bytes(stages, ctx) + staged_bytes;
   // eight epilogue warps for the narrow, epilogue-bound tiles of the bf16 path
   constexpr int EW = ((NSPLIT == 1 && BN <= 128 && (MODE == MODE_STORE || MODE == MODE_POOL || MODE == MODE_UNPOOL)) ||
-                      MODE == MODE_CTX2 || MODE == MODE_CTX2_BWD) ? 8 : 4;
+                      MODE == MODE_CTX2 || MODE == MODE_CTX2_BWD) ? 8 : 4;   // (MODE_DFV with 8: measured slower)
   auto kern = conv_tc_kernel<BN, NSPLIT, MODE, 0, EW>;
   static bool attr_done = false;  // per template instantiation
   static int attr_smem = 0;

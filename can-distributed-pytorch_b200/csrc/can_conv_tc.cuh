@@ -88,8 +88,12 @@ struct ConvTcSmem {
   static constexpr int kStageBytes = NSPLIT * (kABytes + kBBytes);
   static constexpr int kCtxTabBytes = 2 * 50 * 64 * 4;
   static constexpr int kTailBytes = 1024 + 2 * BN * 4 + 4096;  // barriers + tmem ptr, bias (double-buffered), s_db[1024]
-  static __host__ __device__ constexpr int bytes(int stages, bool ctx) {
-    return 1024 /*align slack*/ + stages * kStageBytes + kTailBytes + (ctx ? kCtxTabBytes : 0);
+  // table region after the tail: MODE_CTX / MODE_CTX_BWD [2][50][64] fp32, MODE_DFV [50][BN] fp32
+  static __host__ __device__ constexpr int tab_bytes(int mode) {
+    return (mode == MODE_CTX || mode == MODE_CTX_BWD) ? kCtxTabBytes : (mode == MODE_DFV ? 50 * BN * 4 : 0);
+  }
+  static __host__ __device__ constexpr int bytes(int stages, int mode) {
+    return 1024 /*align slack*/ + stages * kStageBytes + kTailBytes + tab_bytes(mode);
   }
 };
 
@@ -550,7 +554,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int as = it % ACC_STAGES;
     const uint32_t aphase = static_cast<uint32_t>(it / ACC_STAGES) & 1u;
     // single n-tile: the bias slice never changes -> staged once (tile 0), no global load + barrier per tile
-    const bool bias_once = (p.n_tiles == 1) && MODE != MODE_CTX && MODE != MODE_CTX_BWD;
+    const bool bias_once = (p.n_tiles == 1) && MODE != MODE_CTX && MODE != MODE_CTX_BWD && MODE != MODE_DFV;
     float* s_bias = s_bias2 + (bias_once ? 0 : (it & 1) * BN);
     if (!bias_once || it == 0)
       for (int i = etid; i < BN; i += 32 * EW) s_bias[i] = p.bias ? p.bias[n0 + i] : 0.f;
@@ -564,6 +568,28 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         *reinterpret_cast<float4*>(s_tab + pos * 64 + c4) = *reinterpret_cast<const float4*>(ga + pos * 512 + c4);
         *reinterpret_cast<float4*>(s_tab + 3200 + pos * 64 + c4) =
             *reinterpret_cast<const float4*>(gb + pos * 512 + c4);
+      }
+    }
+    if (MODE == MODE_DFV) {
+      // dpool table of this image for the BN channels of this n-tile -> shared memory ([50][BN] fp32).  The
+      // epilogue reads 13 of its rows per pixel and channel group; from global memory those reads miss the (small)
+      // L1 next to a 200 KB shared-memory carve-out and pay the L2 latency 104 times per 32 channels.
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");  // everyone finished reading the previous tile's table
+      const float* gt = p.tabA + (static_cast<long long>(n_img) * 50) * 512 + n0;
+      constexpr int kVec = 50 * BN / 4, kPer = (kVec + 32 * EW - 1) / (32 * EW), kHalf = (kPer + 1) / 2;
+#pragma unroll
+      for (int h2 = 0; h2 < 2; ++h2) {   // loads first, then stores (two batches bound the registers)
+        float4 tv[kHalf];
+#pragma unroll
+        for (int u = 0; u < kHalf; ++u) {
+          const int i = etid + (h2 * kHalf + u) * 32 * EW;
+          if (h2 * kHalf + u < kPer && i < kVec) tv[u] = __ldg(reinterpret_cast<const float4*>(gt + (i / (BN / 4)) * 512 + (i % (BN / 4)) * 4));
+        }
+#pragma unroll
+        for (int u = 0; u < kHalf; ++u) {
+          const int i = etid + (h2 * kHalf + u) * 32 * EW;
+          if (h2 * kHalf + u < kPer && i < kVec) *reinterpret_cast<float4*>(s_tab + (i / (BN / 4)) * BN + (i % (BN / 4)) * 4) = tv[u];
+        }
       }
     }
     if (!bias_once || it == 0) asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
@@ -1199,7 +1225,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               const bool on = (a == 0 || y2) && (b == 0 || x2);
               const int hh = adaptive_end(iy, p.H, S) - adaptive_start(iy, p.H, S);
               const int ww = adaptive_end(ix, p.W, S) - adaptive_start(ix, p.W, S);
-              spos[k] = (OFF[j] + iy * S + ix) * 512;
+              spos[k] = (OFF[j] + iy * S + ix) * BN;   // row of the staged table
               swgt[k] = on ? 1.f / static_cast<float>(hh * ww) : 0.f;
               ++k;
             }
@@ -1209,7 +1235,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       __nv_bfloat16* obase = p.out + pix * p.out_cs + p.out_coff + n0;
       const __nv_bfloat16* mbase = p.mask + pix * p.mask_cs + p.mask_coff + n0;
       const __nv_bfloat16* abase = p.add + pix * p.add_cs + p.add_coff + n0;
-      const float* tab = p.tabA + static_cast<long long>(n_img) * 50 * 512 + n0;
+      const float* tab = s_tab;
+      // upstream gradient (plane 0) and ReLU mask of the next column group are requested one group ahead
+      uint4 nx_a[4] = {}, nx_m[4] = {};
+      if (valid) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          nx_a[i] = *reinterpret_cast<const uint4*>(abase + cbeg + 8 * i);
+          nx_m[i] = *reinterpret_cast<const uint4*>(mbase + cbeg + 8 * i);
+        }
+      }
 #pragma unroll 1
       for (int c0 = cbeg; c0 < cend; c0 += 32) {
         float r[32];
@@ -1217,6 +1252,19 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         float v[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = 0.f;
+        uint4 cur_a[4], cur_m[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          cur_a[i] = nx_a[i];
+          cur_m[i] = nx_m[i];
+        }
+        if (valid && c0 + 32 < cend) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            nx_a[i] = *reinterpret_cast<const uint4*>(abase + c0 + 32 + 8 * i);
+            nx_m[i] = *reinterpret_cast<const uint4*>(mbase + c0 + 32 + 8 * i);
+          }
+        }
         if (valid) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = -r[i];
@@ -1226,7 +1274,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const float* tp = tab + spos[k] + c0;
 #pragma unroll
             for (int i = 0; i < 32; i += 4) {
-              const float4 t4 = __ldg(reinterpret_cast<const float4*>(tp + i));
+              const float4 t4 = *reinterpret_cast<const float4*>(tp + i);
               v[i] = fmaf(wk, t4.x, v[i]);
               v[i + 1] = fmaf(wk, t4.y, v[i + 1]);
               v[i + 2] = fmaf(wk, t4.z, v[i + 2]);
@@ -1237,12 +1285,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int i = 0; i < 32; i += 8) {
 #pragma unroll
             for (int pl = 0; pl < NSPLIT; ++pl) {
-              const uint4 aq = *reinterpret_cast<const uint4*>(abase + pl * p.add_plane + c0 + i);
+              const uint4 aq = pl == 0 ? cur_a[i >> 3] : *reinterpret_cast<const uint4*>(abase + pl * p.add_plane + c0 + i);
               const __nv_bfloat16* ab = reinterpret_cast<const __nv_bfloat16*>(&aq);
 #pragma unroll
               for (int e = 0; e < 8; ++e) v[i + e] += __bfloat162float(ab[e]);
             }
-            const uint4 mq = *reinterpret_cast<const uint4*>(mbase + c0 + i);
+            const uint4 mq = cur_m[i >> 3];
             const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mq);
 #pragma unroll
             for (int e = 0; e < 8; ++e)
