@@ -240,16 +240,21 @@ def backward_steps(model, saved, grad_out: torch.Tensor, grads=None):
         ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX_BWD, out=D, mask=dcat.view(512, 512), tabA=saved["tabA"],
                     tabB=saved["tabB"])
     wint = cache.get(("wint", nsplit, h, w), (), lambda: ops.ctx_wint(nsplit, 1, h, w, dev))
-    T = torch.empty(N, 64, 4096, device=dev, dtype=torch.float32)   # U^T [dz | ds] per image
-    for n in range(N):
-        ops.conv_wgrad(wint, D.image(n), T[n], taps=1)
+    if nsplit == 1:
+        T = ops.ctx_ut(wint, D)                      # U^T [dz | ds], [64 pos][N][4096]: one launch for the batch
+        t_ns, t_ps = 4096, N * 4096
+    else:
+        T = torch.empty(N, 64, 4096, device=dev, dtype=torch.float32)   # per image
+        for n in range(N):
+            ops.conv_wgrad(wint, D.image(n), T[n], taps=1)
+        t_ns, t_ps = 64 * 4096, 4096
     # da_j = U^T ds_j + W_j2^T (U^T dz_j);  dpool_j = W_j1^T da_j
-    da = ops.ctx_pos_gemv(w2t, T, 64 * 4096, 4096, 512, T.view(-1)[2048:], N)
+    da = ops.ctx_pos_gemv(w2t, T, t_ns, t_ps, 512, T.view(-1)[2048:], N)
     dpool = ops.ctx_pos_gemv(w1t, da, 50 * 512, 512, 0, None, N)
     dW1 = torch.empty(4, 512, 512, device=dev, dtype=torch.float32)
     dW2 = torch.empty(4, 512, 512, device=dev, dtype=torch.float32)
     ops.ctx_outer(da, 50 * 512, 512, 0, saved["pooled"], N, dW1)          # dW_j1 = sum da_j pool_j^T
-    ops.ctx_outer(T, 64 * 4096, 4096, 512, saved["tabA"], N, dW2)         # dW_j2 = sum (U^T dz_j) a_j^T ...
+    ops.ctx_outer(T, t_ns, t_ps, 512, saved["tabA"], N, dW2)              # dW_j2 = sum (U^T dz_j) a_j^T ...
     # ... - dz_j fv^T: the four scales share fv, so one [2048 x 512] weight-gradient GEMM over all of them
     ops.conv_wgrad(D.view(2048, 0), fv, dW2.view(2048, 512), taps=1, accumulate=True, alpha=-1.0)
     for j in range(4):

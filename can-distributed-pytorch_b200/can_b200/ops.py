@@ -339,6 +339,24 @@ def ctx_ttab(tabA, tabB):
     return T
 
 
+def ctx_ut(wint: Act, x: Act) -> torch.Tensor:
+    """U^T x for all images in one launch (bf16 path): returns [64 pos][B][C] fp32."""
+    assert wint.nsplit == 1 and x.nsplit == 1 and wint.N == 1 and wint.C == 64
+    B, H, W, Cc = x.N, x.H, x.W, x.C
+    dev = x.buf.device
+    need = lib().can_ctx_ut_workspace_bytes(B, H, W, Cc)
+    ws = _wgrad_ws.get(dev)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(max(need, 64 << 20), device=dev, dtype=torch.uint8)
+        _wgrad_ws[dev] = ws
+    out = torch.empty(64, B, Cc, device=dev, dtype=torch.float32)
+    _count(2)
+    with _Prof(2.0 * 64 * Cc * B * H * W, f"wgrad ut {Cc}->64 x{B} {H}x{W}"):
+        check(lib().can_ctx_ut(wint.buf.data_ptr(), wint.cs, x.buf.data_ptr(), x.cs, x.coff, B, H, W, Cc, out.data_ptr(),
+                               ws.data_ptr(), ws.numel(), _stream()), "ctx_ut")
+    return out
+
+
 def ctx_pos_gemv(Wm, inp, in_ns, in_ps, in_js, add, N):
     out = torch.empty(N, 50, 512, device=Wm.device, dtype=torch.float32)
     check(lib().can_ctx_pos_gemv(Wm.data_ptr(), inp.data_ptr(), in_ns, in_ps, in_js, _ptr(add), out.data_ptr(), N,

@@ -786,9 +786,45 @@ int64_t can_conv_wgrad_workspace_bytes(int N, int H, int W, int Cin, int Cout, i
   return static_cast<int64_t>(pl.ksplit) * taps * Cout * Cin * sizeof(float);
 }
 
+}  // extern "C"
+namespace {
+int conv_wgrad_impl(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, const void* x, int64_t x_plane, int x_cs,
+                    int x_coff, int nsplit, int N, int H, int W, int Cin, int Cout, int taps, int dil, float* grad,
+                    int accumulate, float alpha, void* ws, int64_t ws_bytes, void* stream, int x_images);
+}
+extern "C" {
+
 int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, const void* x, int64_t x_plane, int x_cs,
                    int x_coff, int nsplit, int N, int H, int W, int Cin, int Cout, int taps, int dil, float* grad,
                    int accumulate, float alpha, void* ws, int64_t ws_bytes, void* stream) {
+  return conv_wgrad_impl(dz, dz_plane, dz_cs, dz_coff, x, x_plane, x_cs, x_coff, nsplit, N, H, W, Cin, Cout, taps, dil, grad,
+                         accumulate, alpha, ws, ws_bytes, stream, 0);
+}
+
+int64_t can_ctx_ut_workspace_bytes(int B, int H, int W, int Cin) {
+  if (B <= 0 || H <= 0 || W <= 0 || Cin <= 0 || Cin % 256) return -1;
+  const WgradPlan pl = wgrad_plan(1, H, W, B * Cin, 64, 1, 1);
+  return static_cast<int64_t>(pl.ksplit) * 64 * B * Cin * sizeof(float);
+}
+
+int can_ctx_ut(const void* wint, int wint_cs, const void* x, int x_cs, int x_coff, int B, int H, int W, int Cin, float* out,
+               void* ws, int64_t ws_bytes, void* stream) {
+  if (B <= 0 || Cin % 256) return fail(-2, "ctx_ut: B=%d Cin=%d (Cin must be a multiple of 256)", B, Cin);
+  return conv_wgrad_impl(wint, 0, wint_cs, 0, x, 0, x_cs, x_coff, 1, 1, H, W, Cin, 64, 1, 1, out, 0, 1.f, ws, ws_bytes, stream, B);
+}
+
+}  // extern "C"
+namespace {
+// x_images == 0: the plain weight gradient.  x_images = B > 0 (single plane, taps == 1): dz is ONE image shared by the
+// B images of x; grad is [Cout][B][Cin].
+int conv_wgrad_impl(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, const void* x, int64_t x_plane, int x_cs,
+                    int x_coff, int nsplit, int N, int H, int W, int Cin, int Cout, int taps, int dil, float* grad,
+                    int accumulate, float alpha, void* ws, int64_t ws_bytes, void* stream, int x_images) {
+  const int cin_img = Cin;
+  if (x_images > 0) {
+    if (nsplit != 1 || taps != 1 || N != 1) return fail(-8, "ctx_ut: single plane, 1x1, one dz image only");
+    Cin = x_images * cin_img;   // n-tiles enumerate (image, cin tile); the result has B * Cin columns
+  }
   if (!dz || !x || !grad || !ws) return fail(-1, "conv_wgrad: null pointer");
   if (N <= 0 || H <= 0 || W <= 0) return fail(-2, "conv_wgrad: bad shape");
   if (Cin <= 0 || Cin % 64 || Cout <= 0 || Cout % 64) return fail(-3, "conv_wgrad: Cin/Cout must be multiples of 64");
@@ -819,8 +855,10 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
   if (nsplit == 1 && !pl.swap64) {
     rc = make_act_tmap_groups(&tmDZ, dz, dz_coff, Cout, dz_cs, N, H, W, pl.TW, pl.TH, p.m_groups);
     if (rc) return rc;
-    rc = make_act_tmap_groups(&tmX, x, x_coff, Cin, x_cs, N, H, W, pl.TW, pl.TH, pl.bn / 64);
+    rc = make_act_tmap_groups(&tmX, x, x_coff, x_images > 0 ? cin_img : Cin, x_cs, x_images > 0 ? x_images : N, H, W, pl.TW,
+                              pl.TH, pl.bn / 64);
     if (rc) return rc;
+    p.x_img_tiles = x_images > 0 ? cin_img / pl.bn : 0;
   }
   if (pl.swap64) {
     using L = WgradSwapSmem;
@@ -865,6 +903,9 @@ int can_conv_wgrad(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, con
   CAN_CHECK_LAUNCH("wgrad_reduce");
   return 0;
 }
+}  // namespace
+
+extern "C" {
 
 int can_im2col_first(const float* x_nchw, void* out, int64_t out_plane, int nsplit, int N, int H, int W, void* stream) {
   if (!x_nchw || !out || N <= 0 || H <= 0 || W <= 0 || nsplit < 1 || nsplit > 3) return fail(-1, "im2col_first: bad arguments");

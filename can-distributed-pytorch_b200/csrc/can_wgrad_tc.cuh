@@ -27,6 +27,8 @@ struct WgradTcParams {
   int total_patches;
   int stages;
   int m_groups;  // 64-channel groups of dZ actually loaded (1 when Cout == 64)
+  int x_img_tiles;  // > 0 (single plane): dZ is ONE image shared by B images of X; n_tile = image * x_img_tiles + cin tile,
+                    // the result is [Cout][B][Cin]  (U^T of the contextual backward for the whole batch in one launch)
   int tap_groups;  // ceil(taps / T)
   float* ws;     // [split][tap][Cout][Cin]
 };
@@ -116,11 +118,12 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
         if (NSPLIT == 1) {
           // single-plane maps carry the 64-channel group as their 4th dimension: one TMA op per operand tile
           tma_load_5d(sa, &tmDZ, &full_bar[stage], 0, x0, y0, m_tile * 2, n_img);
+          const int xg = p.x_img_tiles ? (n_tile % p.x_img_tiles) * (BN / 64) : n_tile * (BN / 64);
+          const int xn = p.x_img_tiles ? n_tile / p.x_img_tiles : n_img;
 #pragma unroll
           for (int tt = 0; tt < T; ++tt)
             if (tt < ntaps)
-              tma_load_5d(sb + tt * L::kBBytes, &tmX, &full_bar[stage], 0, x0 + tdx[tt], y0 + tdy[tt], n_tile * (BN / 64),
-                          n_img);
+              tma_load_5d(sb + tt * L::kBBytes, &tmX, &full_bar[stage], 0, x0 + tdx[tt], y0 + tdy[tt], xg, xn);
         } else
 #pragma unroll
         for (int pl = 0; pl < NSPLIT; ++pl) {

@@ -204,6 +204,13 @@ int can_head_bwd(const float* dout, const void* y5, int64_t y_plane, int nsplit,
  * can_ctx_outer: dW[scale][r][c] (+)= alpha * sum_{n,pos in scale} A(n,pos,r) * B[n][pos][c]
  *   (weight gradients of conv{S}_1 and the pooled-position part of conv{S}_2).                  */
 int can_ctx_wint(void* out, int64_t out_plane, int nsplit, int N, int H, int W, void* stream);
+/* U^T of a full-resolution tensor for the whole batch in one launch (bf16 path):
+ *   out[pos][b][c] = sum_{y,x} wint[y][x][pos] * x[b][y][x][c],  pos < 64, c < Cin (multiple of 256)
+ * wint: can_ctx_wint output for N = 1 (pixel stride wint_cs = 64); x: NHWC bf16, B images.  The tensor-core GEMM of
+ * can_conv_wgrad with the interpolation matrix as the shared `dz` operand; ws: can_ctx_ut_workspace_bytes(). */
+int64_t can_ctx_ut_workspace_bytes(int B, int H, int W, int Cin);
+int can_ctx_ut(const void* wint, int wint_cs, const void* x, int x_cs, int x_coff, int B, int H, int W, int Cin, float* out,
+               void* ws, int64_t ws_bytes, void* stream);
 /* CTX2 operands: T[0][n][(cc*4+j)*64+c][pos] = -tabB[n][pos][cc*64+c], T[1] = +tabA (zero outside scale j). */
 int can_ctx_ttab(const float* tabA, const float* tabB, void* T, int N, void* stream);
 int can_ctx_pos_gemv(const float* Wm, const float* in, int64_t in_ns, int64_t in_ps, int64_t in_js,
