@@ -639,7 +639,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // bring-up experiment: no epilogue work at all
     } else if (MODE == MODE_STORE) {
       const long long pix = (static_cast<long long>(n_img) * p.H + y) * p.W + x;
-      __nv_bfloat16* obase = p.out + ((p.dbg & 32) ? (pix & 0xfff) : pix) * p.out_cs + p.out_coff + n0;
+      __nv_bfloat16* obase = p.out + pix * p.out_cs + p.out_coff + n0;
       const __nv_bfloat16* mbase = p.mask ? p.mask + pix * p.mask_cs + p.mask_coff + n0 : nullptr;
       float* fbase = p.out_f32 ? p.out_f32 + pix * p.out_cs + p.out_coff + n0 : nullptr;
 #pragma unroll 1
