@@ -164,6 +164,10 @@ struct WgradPlan {
 WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nsplit) {
   WgradPlan pl;
   pl.bn = Cin < 256 ? Cin : (nsplit > 1 ? 128 : 256);
+  // 512-wide layers: nine taps in pairs (BN = 256) leave a half-loaded fifth tap group and 120 CTAs for 148 SMs;
+  // three balanced groups of three taps at BN = 128 fill 144 (measured: 512->512 186 -> 172 us, 1024->512 369 -> 334 us;
+  // the 256-wide layers are better off with BN = 256)
+  if (nsplit == 1 && taps == 9 && Cin >= 512 && Cout >= 512 && env_int("CAN_B200_WGBN", 128) == 128) pl.bn = 128;
   // widest tiles (bf16 path, BN = 256, two taps): an 80 KB stage would leave a 2-deep pipeline -> 32-pixel patches
   pl.pix = (nsplit == 1 && taps > 1 && pl.bn == 256 && env_int("CAN_B200_WGPIX", 32) == 32) ? 32 : 64;
   pl.TW = (W >= 16) ? 16 : 8;
