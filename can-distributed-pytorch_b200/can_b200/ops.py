@@ -308,6 +308,28 @@ def conv_first_wgrad(dz: Act, x: torch.Tensor, grad: torch.Tensor, accumulate=Fa
               "conv_first_wgrad")
 
 
+def crowd_sample(img_u8: torch.Tensor, dmap: torch.Tensor = None, flip: bool = False, ds: int = 8):
+    """model/CrowdDataset.py:38-66 for one sample on the device: img uint8 [H,W] or [H,W,3] (cuda) and the optional float32
+    density map [H,W] -> (img float32 [3, H//ds*ds, W//ds*ds] normalised, dmap float32 [1, H//ds, W//ds] * ds^2 or None)."""
+    if img_u8.dtype != torch.uint8 or not img_u8.is_cuda or img_u8.dim() not in (2, 3):
+        raise ValueError("crowd_sample: img must be a CUDA uint8 tensor [H,W] or [H,W,3]")
+    img_u8 = img_u8.contiguous()
+    H, W = img_u8.shape[:2]
+    Cc = 1 if img_u8.dim() == 2 else img_u8.shape[2]
+    rows, cols = H // ds, W // ds
+    out = torch.empty(3, rows * ds, cols * ds, device=img_u8.device, dtype=torch.float32)
+    od = None
+    if dmap is not None:
+        if dmap.dtype != torch.float32 or tuple(dmap.shape) != (H, W) or dmap.device != img_u8.device:
+            raise ValueError("crowd_sample: dmap must be float32 [H,W] on the image's device")
+        dmap = dmap.contiguous()
+        od = torch.empty(1, rows, cols, device=img_u8.device, dtype=torch.float32)
+    check(lib().can_crowd_sample(img_u8.data_ptr(), H, W, Cc, _ptr(dmap), int(flip), ds, out.data_ptr(), _ptr(od), _stream()),
+          "crowd_sample")
+    _count(2 if dmap is not None else 1)
+    return out, od
+
+
 def bias_grad(dz: Act, db: torch.Tensor):
     """db[c] += sum_pixels dz[pix][c]; db fp32 [C], already initialised."""
     check(lib().can_bias_grad(dz.buf.data_ptr(), dz.plane, dz.nsplit, dz.cs, dz.coff, dz.C, dz.N * dz.H * dz.W,

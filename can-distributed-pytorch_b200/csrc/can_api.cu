@@ -14,6 +14,7 @@
 #include "can_wgrad_tc.cuh"
 #include "can_aux.cuh"
 #include "can_first_tc.cuh"
+#include "can_data.cuh"
 
 using namespace canb;
 
@@ -1000,6 +1001,24 @@ int can_conv_first_wgrad(const void* dz, int dz_cs, int dz_coff, const float* x_
   CAN_CHECK_LAUNCH("wgrad_first_tc");
   wgrad_first_reduce_kernel<<<64, 256, 0, st>>>(p.ws, grad, ctas, accumulate, alpha);
   CAN_CHECK_LAUNCH("wgrad_first_reduce");
+  return 0;
+}
+
+int can_crowd_sample(const uint8_t* img, int H, int W, int C, const float* dmap, int flip, int ds, float* out_img,
+                     float* out_dmap, void* stream) {
+  if (!img || !out_img || H <= 0 || W <= 0 || (C != 1 && C != 3) || ds < 1) return fail(-1, "crowd_sample: bad arguments");
+  const int rows = H / ds, cols = W / ds;
+  if (rows <= 0 || cols <= 0 || rows * ds > 65535 || rows > 65535) return fail(-2, "crowd_sample: image %dx%d vs downsample %d", H, W, ds);
+  if ((dmap == nullptr) != (out_dmap == nullptr)) return fail(-3, "crowd_sample: dmap and out_dmap go together");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int OH = rows * ds, OW = cols * ds;
+  crowd_image_kernel<<<dim3((OW + 255) / 256, OH), 256, 0, st>>>(img, H, W, C, flip ? 1 : 0, out_img, OH, OW);
+  CAN_CHECK_LAUNCH("crowd_image");
+  if (dmap) {
+    crowd_dmap_kernel<<<dim3((cols + 127) / 128, rows), 128, 0, st>>>(dmap, H, W, flip ? 1 : 0, out_dmap, rows, cols,
+                                                                      static_cast<float>(ds) * static_cast<float>(ds));
+    CAN_CHECK_LAUNCH("crowd_dmap");
+  }
   return 0;
 }
 

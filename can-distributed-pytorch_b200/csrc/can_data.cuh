@@ -1,0 +1,90 @@
+// Per-sample data path of the reference (model/CrowdDataset.py:38-66) on the GPU: /255, gray -> RGB, horizontal
+// flip, cv2.resize(INTER_LINEAR) of the image to a multiple of 8 and of the density map to 1/8 (x 64), ImageNet
+// normalisation -- NCHW fp32 out, which is what conv1_1 reads.  HBM-bound and tiny (2.4 MB in, 9.4 MB out for a
+// 768x1024 image); the arithmetic mirrors the oracle operation by operation (no FMA contraction: explicit _rn
+// intrinsics), so the image path is bit-exact against cv2's float64 pipeline + torchvision's float32 normalize.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace canb {
+
+// cv2 INTER_LINEAR: source index and fractional weight of destination index d (half-pixel centres, clamped)
+__device__ __forceinline__ void cv_linear_coeff(int d, int n_dst, int n_src, int& s, double& f) {
+  const double scale = static_cast<double>(n_src) / static_cast<double>(n_dst);
+  f = __dadd_rn(__dmul_rn(static_cast<double>(d) + 0.5, scale), -0.5);
+  const double fl = floor(f);
+  s = static_cast<int>(fl);
+  f = __dadd_rn(f, -fl);
+  if (s < 0) {
+    s = 0;
+    f = 0.0;
+  }
+  if (s >= n_src - 1) {
+    s = n_src - 1;
+    f = 0.0;
+  }
+}
+
+// img: uint8 [H][W][C] (C = 1 or 3); out: float [3][OH][OW]
+__global__ void crowd_image_kernel(const uint8_t* __restrict__ img, int H, int W, int C, int flip, float* __restrict__ out,
+                                   int OH, int OW) {
+  const int ox = blockIdx.x * blockDim.x + threadIdx.x, oy = blockIdx.y;
+  if (ox >= OW) return;
+  const float mean[3] = {0.485f, 0.456f, 0.406f}, stdv[3] = {0.229f, 0.224f, 0.225f};
+  int sx = ox, sy = oy;
+  double fx = 0.0, fy = 0.0;
+  const bool same = (OH == H) && (OW == W);   // cv2.resize copies when the size does not change
+  if (!same) {
+    cv_linear_coeff(ox, OW, W, sx, fx);
+    cv_linear_coeff(oy, OH, H, sy, fy);
+  }
+  const int sx1 = min(sx + 1, W - 1), sy1 = min(sy + 1, H - 1);
+  // the flip (CrowdDataset.py:48-50) happens before the resize: column x of the flipped image is column W-1-x
+  const int cx0 = flip ? W - 1 - sx : sx, cx1 = flip ? W - 1 - sx1 : sx1;
+  const double a1 = fx, a0 = __dadd_rn(1.0, -fx), b1 = fy, b0 = __dadd_rn(1.0, -fy);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const int cc = (C == 1) ? 0 : c;
+    const double p00 = static_cast<double>(img[(static_cast<long long>(sy) * W + cx0) * C + cc]) / 255.0;
+    double v = p00;
+    if (!same) {
+      const double p01 = static_cast<double>(img[(static_cast<long long>(sy) * W + cx1) * C + cc]) / 255.0;
+      const double p10 = static_cast<double>(img[(static_cast<long long>(sy1) * W + cx0) * C + cc]) / 255.0;
+      const double p11 = static_cast<double>(img[(static_cast<long long>(sy1) * W + cx1) * C + cc]) / 255.0;
+      const double r0 = __dadd_rn(__dmul_rn(p00, a0), __dmul_rn(p01, a1));   // horizontal pass, row sy
+      const double r1 = __dadd_rn(__dmul_rn(p10, a0), __dmul_rn(p11, a1));   // horizontal pass, row sy + 1
+      v = __dadd_rn(__dmul_rn(r0, b0), __dmul_rn(r1, b1));                   // vertical pass
+    }
+    const float xf = static_cast<float>(v);                                   // torch.tensor(img, dtype=torch.float)
+    out[(static_cast<long long>(c) * OH + oy) * OW + ox] = __fdiv_rn(__fsub_rn(xf, mean[c]), stdv[c]);
+  }
+}
+
+// dmap: float [H][W]; out: float [OH][OW] = cv2.resize(dmap, (OW, OH)) * scale   (float32 pipeline)
+__global__ void crowd_dmap_kernel(const float* __restrict__ dmap, int H, int W, int flip, float* __restrict__ out, int OH,
+                                  int OW, float scale) {
+  const int ox = blockIdx.x * blockDim.x + threadIdx.x, oy = blockIdx.y;
+  if (ox >= OW) return;
+  int sx = ox, sy = oy;
+  double fxd = 0.0, fyd = 0.0;
+  const bool same = (OH == H) && (OW == W);
+  if (!same) {
+    cv_linear_coeff(ox, OW, W, sx, fxd);
+    cv_linear_coeff(oy, OH, H, sy, fyd);
+  }
+  const int sx1 = min(sx + 1, W - 1), sy1 = min(sy + 1, H - 1);
+  const int cx0 = flip ? W - 1 - sx : sx, cx1 = flip ? W - 1 - sx1 : sx1;
+  const float a1 = static_cast<float>(fxd), a0 = __fsub_rn(1.f, a1), b1 = static_cast<float>(fyd), b0 = __fsub_rn(1.f, b1);
+  float v = dmap[static_cast<long long>(sy) * W + cx0];
+  if (!same) {
+    const float p00 = v, p01 = dmap[static_cast<long long>(sy) * W + cx1];
+    const float p10 = dmap[static_cast<long long>(sy1) * W + cx0], p11 = dmap[static_cast<long long>(sy1) * W + cx1];
+    const float r0 = __fadd_rn(__fmul_rn(p00, a0), __fmul_rn(p01, a1));
+    const float r1 = __fadd_rn(__fmul_rn(p10, a0), __fmul_rn(p11, a1));
+    v = __fadd_rn(__fmul_rn(r0, b0), __fmul_rn(r1, b1));
+  }
+  out[static_cast<long long>(oy) * OW + ox] = __fmul_rn(v, scale);
+}
+
+}  // namespace canb

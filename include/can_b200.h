@@ -185,6 +185,14 @@ int64_t can_conv_first_wgrad_workspace_bytes(void);
 int can_conv_first_wgrad(const void* dz, int dz_cs, int dz_coff, const float* x_nchw, int N, int H, int W, float* grad,
                          int accumulate, float alpha, void* ws, int64_t ws_bytes, void* stream);
 
+/* One sample of the reference's data path (model/CrowdDataset.py:38-66) on the device:
+ *   out_img  [3][H/ds*ds][W/ds*ds] fp32 = normalize( cv2.resize( flip( gray->RGB( img / 255 ) ) ) )   (ImageNet mean/std)
+ *   out_dmap [H/ds][W/ds]          fp32 = cv2.resize( flip( dmap ), (W/ds, H/ds) ) * ds^2             (optional: dmap may be NULL)
+ * img: uint8 [H][W][C], C = 1 or 3 (device memory); cv2.resize = INTER_LINEAR, half-pixel centres, a plain copy when the size
+ * does not change.  The image path is bit-exact against cv2 (float64) + torchvision normalize (float32).        */
+int can_crowd_sample(const uint8_t* img, int H, int W, int C, const float* dmap, int flip, int ds, float* out_img,
+                     float* out_dmap, void* stream);
+
 /* db[c] += sum_pixels dz[pixel][c]  (bias gradient of every conv; db must be initialised).    */
 int can_bias_grad(const void* dz, int64_t plane, int nsplit, int cs, int coff, int C, int64_t npix, float* db,
                   void* stream);

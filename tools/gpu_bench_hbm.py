@@ -52,6 +52,12 @@ def main():
     t = timeit(lambda: ops.sgd_momentum_step(pa, ga, ba, 1e-7, 0.95, 1.0, first=False))
     b = 5 * n * 4
     out.append(dict(kernel="sgd_momentum_step, 82.9 M floats", bytes=b, us=t * 1e6, GBps=b / t / 1e9))
+    # data path: one 1536x2048 RGB sample (uint8 in, normalised fp32 NCHW + density map /8 out)
+    img = torch.randint(0, 256, (1539, 2051, 3), dtype=torch.uint8, device=dev)
+    dm = torch.rand(1539, 2051, device=dev)
+    t = timeit(lambda: ops.crowd_sample(img, dm, flip=True))
+    b = img.numel() + dm.numel() * 4 // 64 * 4 + 3 * 1536 * 2048 * 4 + 192 * 256 * 4   # dmap: 4 taps per output pixel
+    out.append(dict(kernel="crowd_sample (image + dmap), 1539x2051 -> 3x1536x2048", bytes=b, us=t * 1e6, GBps=b / t / 1e9))
     for o in out:
         o["frac_of_measured_hbm"] = o["GBps"] / peak
         print("HBM " + json.dumps({k: (round(v, 3) if isinstance(v, float) else v) for k, v in o.items()}), flush=True)
