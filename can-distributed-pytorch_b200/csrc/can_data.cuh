@@ -26,9 +26,14 @@ __device__ __forceinline__ void cv_linear_coeff(int d, int n_dst, int n_src, int
   }
 }
 
-// img: uint8 [H][W][C] (C = 1 or 3); out: float [3][OH][OW]
-__global__ void crowd_image_kernel(const uint8_t* __restrict__ img, int H, int W, int C, int flip, float* __restrict__ out,
-                                   int OH, int OW) {
+// img: uint8 [H][W][C] (C = 1 or 3); out: float [3][OH][OW].  256 threads per block.
+// u / 255 in double (the reference's `img / 255`) comes from a 256-entry table built with exactly that division
+// (a double division per tap and channel made the kernel FP64-bound: 81 us for a 1539x2051 sample).
+__global__ void __launch_bounds__(256)
+crowd_image_kernel(const uint8_t* __restrict__ img, int H, int W, int C, int flip, float* __restrict__ out, int OH, int OW) {
+  __shared__ double s_u[256];
+  s_u[threadIdx.x] = static_cast<double>(threadIdx.x) / 255.0;
+  __syncthreads();
   const int ox = blockIdx.x * blockDim.x + threadIdx.x, oy = blockIdx.y;
   if (ox >= OW) return;
   const float mean[3] = {0.485f, 0.456f, 0.406f}, stdv[3] = {0.229f, 0.224f, 0.225f};
@@ -46,12 +51,12 @@ __global__ void crowd_image_kernel(const uint8_t* __restrict__ img, int H, int W
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     const int cc = (C == 1) ? 0 : c;
-    const double p00 = static_cast<double>(img[(static_cast<long long>(sy) * W + cx0) * C + cc]) / 255.0;
+    const double p00 = s_u[img[(static_cast<long long>(sy) * W + cx0) * C + cc]];
     double v = p00;
     if (!same) {
-      const double p01 = static_cast<double>(img[(static_cast<long long>(sy) * W + cx1) * C + cc]) / 255.0;
-      const double p10 = static_cast<double>(img[(static_cast<long long>(sy1) * W + cx0) * C + cc]) / 255.0;
-      const double p11 = static_cast<double>(img[(static_cast<long long>(sy1) * W + cx1) * C + cc]) / 255.0;
+      const double p01 = s_u[img[(static_cast<long long>(sy) * W + cx1) * C + cc]];
+      const double p10 = s_u[img[(static_cast<long long>(sy1) * W + cx0) * C + cc]];
+      const double p11 = s_u[img[(static_cast<long long>(sy1) * W + cx1) * C + cc]];
       const double r0 = __dadd_rn(__dmul_rn(p00, a0), __dmul_rn(p01, a1));   // horizontal pass, row sy
       const double r1 = __dadd_rn(__dmul_rn(p10, a0), __dmul_rn(p11, a1));   // horizontal pass, row sy + 1
       v = __dadd_rn(__dmul_rn(r0, b0), __dmul_rn(r1, b1));                   // vertical pass
