@@ -330,6 +330,20 @@ def crowd_sample(img_u8: torch.Tensor, dmap: torch.Tensor = None, flip: bool = F
     return out, od
 
 
+def density_map(points_xy: torch.Tensor, H: int, W: int) -> torch.Tensor:
+    """data_preparation/k_nearest_gaussian_kernel.py:14-54 on the device: points [n,2] float64 (col,row) -> float32 [H,W]."""
+    pts = points_xy.reshape(-1, 2).contiguous()
+    if pts.dtype != torch.float64 or not pts.is_cuda:
+        raise ValueError("density_map: points must be a CUDA float64 tensor [n, 2] of (col, row)")
+    n = pts.shape[0]
+    out = torch.empty(H, W, device=pts.device, dtype=torch.float32)
+    ws = torch.empty(lib().can_density_map_workspace_bytes(n), device=pts.device, dtype=torch.uint8)
+    check(lib().can_density_map(pts.data_ptr() if n else None, n, H, W, out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()),
+          "density_map")
+    _count(2 if n else 1)
+    return out
+
+
 def bias_grad(dz: Act, db: torch.Tensor):
     """db[c] += sum_pixels dz[pix][c]; db fp32 [C], already initialised."""
     check(lib().can_bias_grad(dz.buf.data_ptr(), dz.plane, dz.nsplit, dz.cs, dz.coff, dz.C, dz.N * dz.H * dz.W,

@@ -1022,6 +1022,26 @@ int can_crowd_sample(const uint8_t* img, int H, int W, int C, const float* dmap,
   return 0;
 }
 
+int64_t can_density_map_workspace_bytes(int npts) { return static_cast<int64_t>(npts > 0 ? npts : 1) * sizeof(HeadPar); }
+
+int can_density_map(const double* points_xy, int npts, int H, int W, float* density, void* ws, int64_t ws_bytes,
+                    void* stream) {
+  if (!density || H <= 0 || W <= 0 || npts < 0 || (npts > 0 && (!points_xy || !ws))) return fail(-1, "density_map: bad arguments");
+  if (npts == 2 || npts == 3)
+    return fail(-3, "density_map: the reference is undefined for 2 or 3 heads (missing neighbours are inf)");
+  if (ws_bytes < can_density_map_workspace_bytes(npts)) return fail(-2, "density_map: workspace too small");
+  if ((H + 7) / 8 > 65535) return fail(-4, "density_map: image too tall");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  HeadPar* par = static_cast<HeadPar*>(ws);
+  if (npts > 0) {
+    density_sigma_kernel<<<(npts + 127) / 128, 128, 0, st>>>(points_xy, npts, H, W, par);
+    CAN_CHECK_LAUNCH("density_sigma");
+  }
+  density_gather_kernel<<<dim3((W + 31) / 32, (H + 7) / 8), 256, 0, st>>>(par, npts, H, W, density);
+  CAN_CHECK_LAUNCH("density_gather");
+  return 0;
+}
+
 int can_bias_grad(const void* dz, int64_t plane, int nsplit, int cs, int coff, int C, int64_t npix, float* db,
                   void* stream) {
   if (!dz || !db || C <= 0 || C > 1024 || C % 2 || npix <= 0 || cs % 2 || coff % 2) return fail(-1, "bias_grad: bad arguments");

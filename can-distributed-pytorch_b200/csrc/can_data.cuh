@@ -93,3 +93,81 @@ __global__ void crowd_dmap_kernel(const float* __restrict__ dmap, int H, int W, 
 }
 
 }  // namespace canb
+
+namespace canb {
+
+// Ground-truth density maps (data_preparation/k_nearest_gaussian_kernel.py:14-54): one truncated, normalised, separable
+// Gaussian per annotated head, sigma = 0.1 x (sum of the distances to the three nearest other heads).
+// head_par[i] = { row, col, radius (or -1: skipped), -0.5 / sigma^2, sum_k exp(-0.5 k^2 / sigma^2) }
+struct HeadPar {
+  int r, c, R, pad;
+  double coef, sum;
+};
+
+// one thread per head: brute-force 4 smallest distances (the head itself included, as KDTree.query(k=4) does)
+__global__ void density_sigma_kernel(const double* __restrict__ pts, int n, int H, int W, HeadPar* __restrict__ par) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double px = pts[2 * i], py = pts[2 * i + 1];
+  double sigma;
+  if (n == 1) {
+    sigma = (static_cast<double>(H) + static_cast<double>(W)) / 2.0 / 2.0 / 2.0;   // np.average(shape) / 2 / 2
+  } else {
+    double best[4] = {1e300, 1e300, 1e300, 1e300};
+    for (int j = 0; j < n; ++j) {
+      const double dx = px - pts[2 * j], dy = py - pts[2 * j + 1];
+      double d = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {   // insertion into the sorted quadruple
+        if (d < best[k]) {
+          const double t = best[k];
+          best[k] = d;
+          d = t;
+        }
+      }
+    }
+    sigma = __dmul_rn(__dadd_rn(__dadd_rn(best[1], best[2]), best[3]), 0.1);
+  }
+  HeadPar hp;
+  hp.r = static_cast<int>(py);
+  hp.c = static_cast<int>(px);
+  hp.pad = 0;
+  const bool inside = hp.r < H && hp.c < W && py >= 0.0 && px >= 0.0;
+  const int R = static_cast<int>(__dadd_rn(__dmul_rn(4.0, sigma), 0.5));
+  hp.R = inside ? R : -1;
+  hp.coef = -0.5 / __dmul_rn(sigma, sigma);
+  double s = 0.0;
+  for (int k = -R; k <= R; ++k) s += exp(__dmul_rn(hp.coef, static_cast<double>(k) * static_cast<double>(k)));
+  hp.sum = s;
+  par[i] = hp;
+}
+
+// one thread per pixel, heads in annotation order (the float32 running sum of the reference's `density +=`)
+__global__ void __launch_bounds__(256)
+density_gather_kernel(const HeadPar* __restrict__ par, int n, int H, int W, float* __restrict__ density) {
+  __shared__ HeadPar s_par[128];
+  const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+  const int bx0 = blockIdx.x * 32, bx1 = bx0 + 31, by0 = blockIdx.y * 8, by1 = by0 + 7;
+  float acc = 0.f;
+  for (int base = 0; base < n; base += 128) {
+    const int cnt = min(128, n - base);
+    __syncthreads();
+    if (threadIdx.x < cnt) s_par[threadIdx.x] = par[base + threadIdx.x];
+    __syncthreads();
+    for (int i = 0; i < cnt; ++i) {
+      const int R = s_par[i].R, r = s_par[i].r, c = s_par[i].c;
+      // whole block outside this head's support (uniform branch)
+      if (R < 0 || r + R < by0 || r - R > by1 || c + R < bx0 || c - R > bx1) continue;
+      const int dy = y - r, dx = x - c;
+      if (dy < -R || dy > R || dx < -R || dx > R) continue;
+      const double coef = s_par[i].coef, sum = s_par[i].sum;
+      const double wy = exp(__dmul_rn(coef, static_cast<double>(dy * dy))) / sum;
+      const double wx = exp(__dmul_rn(coef, static_cast<double>(dx * dx))) / sum;
+      const double col = static_cast<double>(static_cast<float>(wy));   // first pass (rows) stored as float32
+      acc = __fadd_rn(acc, static_cast<float>(__dmul_rn(col, wx)));     // second pass, float32 image, float32 sum
+    }
+  }
+  if (x < W && y < H) density[static_cast<long long>(y) * W + x] = acc;
+}
+
+}  // namespace canb

@@ -193,6 +193,15 @@ int can_conv_first_wgrad(const void* dz, int dz_cs, int dz_coff, const float* x_
 int can_crowd_sample(const uint8_t* img, int H, int W, int C, const float* dmap, int flip, int ds, float* out_img,
                      float* out_dmap, void* stream);
 
+/* Ground-truth density map of one image (data_preparation/k_nearest_gaussian_kernel.py:14-54): for every annotated head
+ * (points_xy = [n][2] doubles, (col, row), device memory) a unit impulse at (int(row), int(col)) blurred by
+ * scipy.ndimage.gaussian_filter(sigma, mode='constant') with sigma = 0.1 * (distances to the three nearest other heads)
+ * (one head: mean(H, W) / 4); heads outside the image are skipped; float32 accumulation in annotation order.
+ * density: [H][W] fp32.  n = 2 or 3 is rejected (the reference itself fails there).  ws: can_density_map_workspace_bytes(n). */
+int64_t can_density_map_workspace_bytes(int npts);
+int can_density_map(const double* points_xy, int npts, int H, int W, float* density, void* ws, int64_t ws_bytes,
+                    void* stream);
+
 /* db[c] += sum_pixels dz[pixel][c]  (bias gradient of every conv; db must be initialised).    */
 int can_bias_grad(const void* dz, int64_t plane, int nsplit, int cs, int coff, int C, int64_t npix, float* db,
                   void* stream);

@@ -58,6 +58,13 @@ def main():
     t = timeit(lambda: ops.crowd_sample(img, dm, flip=True))
     b = img.numel() + dm.numel() * 4 // 64 * 4 + 3 * 1536 * 2048 * 4 + 192 * 256 * 4   # dmap: 4 taps per output pixel
     out.append(dict(kernel="crowd_sample (image + dmap), 1539x2051 -> 3x1536x2048", bytes=b, us=t * 1e6, GBps=b / t / 1e9))
+    # ground-truth generator: 1000 heads on a 768x1024 image (compute-bound: double exp per pixel and head in range)
+    import numpy as np
+    rng = np.random.default_rng(0)
+    pts = torch.from_numpy(np.stack([rng.random(1000) * 1024, rng.random(1000) * 768], 1)).to(dev)
+    t = timeit(lambda: ops.density_map(pts, 768, 1024), iters=5)
+    b = 768 * 1024 * 4
+    out.append(dict(kernel="density_map, 1000 heads, 768x1024 (FP64-bound, bytes = output only)", bytes=b, us=t * 1e6, GBps=b / t / 1e9))
     for o in out:
         o["frac_of_measured_hbm"] = o["GBps"] / peak
         print("HBM " + json.dumps({k: (round(v, 3) if isinstance(v, float) else v) for k, v in o.items()}), flush=True)
