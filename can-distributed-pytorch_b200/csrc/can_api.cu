@@ -856,6 +856,7 @@ int conv_wgrad_impl(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, co
   p.m_groups = Cout >= 128 ? 2 : 1;
   p.ws = static_cast<float*>(ws);
   p.tap_groups = pl.tap_groups;
+  p.dbg = env_int("CAN_B200_DBG", 0);
   dim3 grid(pl.m_tiles * pl.n_tiles * pl.tap_groups, pl.ksplit);
   if (nsplit == 1 && !pl.swap64) {
     rc = make_act_tmap_groups(&tmDZ, dz, dz_coff, Cout, dz_cs, N, H, W, pl.TW, pl.TH, p.m_groups);

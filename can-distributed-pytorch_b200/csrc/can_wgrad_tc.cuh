@@ -30,6 +30,7 @@ struct WgradTcParams {
   int x_img_tiles;  // > 0 (single plane): dZ is ONE image shared by B images of X; n_tile = image * x_img_tiles + cin tile,
                     // the result is [Cout][B][Cin]  (U^T of the contextual backward for the whole batch in one launch)
   int tap_groups;  // ceil(taps / T)
+  int dbg;         // bring-up experiments only (bit 0: skip the partial-tile stores)
   float* ws;     // [split][tap][Cout][Cin]
 };
 
@@ -214,7 +215,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
         uint32_t r[32];
         tmem_ld_32x32(taddr + tt * BN + c0, r);
         tmem_ld_wait();
-        if (valid) {
+        if (valid && !(p.dbg & 1)) {
 #pragma unroll
           for (int i = 0; i < 32; i += 4)
             *reinterpret_cast<float4*>(dst + c0 + i) = make_float4(__uint_as_float(r[i]), __uint_as_float(r[i + 1]),
