@@ -53,13 +53,13 @@ PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
 
 // bf16 tensor map with a 128-byte swizzled box whose innermost extent is 64 elements.
 int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-              const uint32_t* box, bool swizzle128 = true, const uint32_t* elem_strides = nullptr) {
+              const uint32_t* box, bool swizzle128 = true, const uint32_t* elem_strides = nullptr, bool fp32 = false) {
   auto enc = get_encode();
   if (!enc) return fail(-100, "cuTensorMapEncodeTiled entry point not available");
   uint32_t estr[5] = {1, 1, 1, 1, 1};
   if (elem_strides)
     for (int i = 0; i < rank; ++i) estr[i] = elem_strides[i];
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
+  CUresult r = enc(m, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -215,6 +215,8 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   return pl;
 }
 
+thread_local const CUtensorMap* g_tmWS = nullptr;   // fp32 map of the split-K workspace (null -> per-lane stores)
+
 template <int BN, int NSPLIT, int T, int PIX = 64>
 int launch_wgrad(const CUtensorMap& tmDZ, const CUtensorMap& tmX, WgradTcParams& p, dim3 grid, cudaStream_t st) {
   using L = WgradTcSmem<BN, NSPLIT, T, PIX>;
@@ -229,7 +231,8 @@ int launch_wgrad(const CUtensorMap& tmDZ, const CUtensorMap& tmX, WgradTcParams&
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(wgrad_tc)");
     attr_done = true;
   }
-  kern<<<grid, 192, L::bytes(stages), st>>>(tmDZ, tmX, p);
+  p.ws_tma = g_tmWS ? 1 : 0;
+  kern<<<grid, 192, L::bytes(stages), st>>>(tmDZ, tmX, g_tmWS ? *g_tmWS : tmDZ, p);
   CAN_CHECK_LAUNCH("wgrad_tc launch");
   return 0;
 }
@@ -858,6 +861,16 @@ int conv_wgrad_impl(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, co
   p.tap_groups = pl.tap_groups;
   p.dbg = env_int("CAN_B200_DBG", 0);
   dim3 grid(pl.m_tiles * pl.n_tiles * pl.tap_groups, pl.ksplit);
+  CUtensorMap tmWS;
+  g_tmWS = nullptr;
+  if (!pl.swap64 && Cin % 32 == 0 && (reinterpret_cast<uintptr_t>(ws) & 15) == 0 && env_int("CAN_B200_WSTMA", 1) != 0) {
+    const uint64_t dimsW[3] = {static_cast<uint64_t>(Cin), static_cast<uint64_t>(Cout), static_cast<uint64_t>(pl.ksplit) * taps};
+    const uint64_t strW[2] = {static_cast<uint64_t>(Cin) * 4, static_cast<uint64_t>(Cin) * Cout * 4};
+    const uint32_t boxW[3] = {32, 128, 1};
+    rc = make_tmap(&tmWS, ws, 3, dimsW, strW, boxW, true, nullptr, true);
+    if (rc) return rc;
+    g_tmWS = &tmWS;
+  }
   if (nsplit == 1 && !pl.swap64) {
     rc = make_act_tmap_groups(&tmDZ, dz, dz_coff, Cout, dz_cs, N, H, W, pl.TW, pl.TH, p.m_groups);
     if (rc) return rc;

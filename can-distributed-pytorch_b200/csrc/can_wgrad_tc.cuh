@@ -31,6 +31,7 @@ struct WgradTcParams {
                     // the result is [Cout][B][Cin]  (U^T of the contextual backward for the whole batch in one launch)
   int tap_groups;  // ceil(taps / T)
   int dbg;         // bring-up experiments only (bit 0: skip the partial-tile stores)
+  int ws_tma;      // partial tiles leave through TMA stores (tmWS) instead of per-lane stores
   float* ws;     // [split][tap][Cout][Cin]
 };
 
@@ -47,7 +48,7 @@ struct WgradTcSmem {
 template <int BN, int NSPLIT, int T, int PIX = 64>
 __global__ void __launch_bounds__(192, 1)
 wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant__ CUtensorMap tmX,
-                const WgradTcParams p) {
+                const __grid_constant__ CUtensorMap tmWS, const WgradTcParams p) {
   using L = WgradTcSmem<BN, NSPLIT, T, PIX>;
   static_assert(T * BN <= 512, "accumulators of one tap group must fit TMEM");
   extern __shared__ uint8_t smem_raw[];
@@ -207,6 +208,34 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
     const bool valid = (co < p.Cout) && (patch_end > patch_begin);
+    if (p.ws_tma) {
+      // The operand ring is idle now: 32-column slabs of the accumulator go through two 16 KB staging tiles
+      // ([128 rows][32 fp32], 128B swizzle) and leave as TMA stores -- a row-per-lane store pattern (every lane its own
+      // 128-byte line) runs at 4-5 B/cycle/SM and cost 6 % of all weight-gradient time.  tmWS: (Cin, Cout, split*tap),
+      // box (32, 128, 1): rows past Cout are clipped by the map.
+      const int row = q * 32 + lane, etid = threadIdx.x - 64;
+      int chunk = 0;
+      for (int tt = 0; tt < ntaps; ++tt) {
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32, ++chunk) {
+          uint32_t r[32];
+          tmem_ld_32x32(taddr + tt * BN + c0, r);
+          tmem_ld_wait();
+          uint8_t* tile = smem + (chunk & 1) * 16384 + row * 128;
+#pragma unroll
+          for (int i = 0; i < 32; i += 4)
+            *reinterpret_cast<uint4*>(tile + (((i >> 2) ^ (row & 7)) << 4)) = make_uint4(r[i], r[i + 1], r[i + 2], r[i + 3]);
+          fence_proxy_async();
+          if (etid == 0) bulk_wait_group_read0();   // every earlier store (incl. the last user of the other tile) has read
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (etid == 0 && patch_end > patch_begin) {
+            tma_store_3d(&tmWS, smem + (chunk & 1) * 16384, n_tile * BN + c0, m_tile * 128, split * p.taps + tap0 + tt);
+            bulk_commit_group();
+          }
+        }
+      }
+      if (etid == 0) bulk_wait_group_read0();
+    } else
     for (int tt = 0; tt < ntaps; ++tt) {
       float* dst =
           p.ws + ((static_cast<long long>(split) * p.taps + tap0 + tt) * p.Cout + co) * p.Cin + n_tile * BN;
