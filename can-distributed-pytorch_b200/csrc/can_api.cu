@@ -424,6 +424,20 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     g_tmO = &tmO;
     p.out_stage_bytes = 2 * bn * 256;
   }
+  if (ns == 1 && a->mode == CAN_MODE_STORE && bn == 256 && a->out && !a->out_f32 && env_int("CAN_B200_STAGE256", 1) != 0 &&
+      env_int("CAN_B200_TMASTORE", 1) != 0) {
+    // widest tiles: 64-channel blocks through two 16 KB staging tiles (the operand ring keeps 3-4 stages)
+    const uint64_t cs = static_cast<uint64_t>(a->out_cs) * 2;
+    const uint64_t dimsO[4] = {static_cast<uint64_t>(a->Cout), static_cast<uint64_t>(a->W), static_cast<uint64_t>(a->H),
+                               static_cast<uint64_t>(a->N)};
+    const uint64_t strO[3] = {cs, cs * a->W, cs * a->W * a->H};
+    const uint32_t boxO[4] = {64, static_cast<uint32_t>(p.TW), static_cast<uint32_t>(p.TH), 1};
+    int rc = make_tmap(&tmO, static_cast<__nv_bfloat16*>(a->out) + a->out_coff, 4, dimsO, strO, boxO);
+    if (rc) return rc;
+    g_tmO = &tmO;
+    p.out_bufs = 2;
+    p.out_stage_bytes = 32768;
+  }
   if (ns == 1 && a->mode == CAN_MODE_STORE && (bn == 64 || bn == 128) && a->out && env_int("CAN_B200_TMASTORE", 1) != 0) {
     const uint64_t cs = static_cast<uint64_t>(a->out_cs) * 2;
     const uint64_t dimsO[4] = {static_cast<uint64_t>(a->Cout), static_cast<uint64_t>(a->W), static_cast<uint64_t>(a->H),

@@ -487,6 +487,22 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       bulk_wait_group_read0();
       if (R > 0) mbar_arrive(&out_free_bar[(R - 1) & 1]);
+    } else if (MODE == MODE_STORE && BN == 256 && out_lane) {
+      // BN = 256: four 64-channel blocks per tile, two 16 KB staging tiles (round = block)
+      int R = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        CAN_TILE_DECODE(tile)
+        for (int blk = 0; blk < BN / 64; ++blk, ++R) {
+          const int b = R & 1;
+          mbar_wait(&out_full_bar[b], static_cast<uint32_t>(R >> 1) & 1u);
+          tma_store_4d(&tmO, s_out + b * 16384, n0 + blk * 64, x0, y0, n_img);
+          bulk_commit_group();
+          bulk_wait_group_read1();
+          if (R > 0) mbar_arrive(&out_free_bar[b ^ 1]);
+        }
+      }
+      bulk_wait_group_read0();
+      if (R > 0) mbar_arrive(&out_free_bar[(R - 1) & 1]);
     } else if (out_lane) {
       const int nb = p.out_bufs;   // 1 or 2
       int it = 0;
@@ -629,6 +645,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tc_fence_after();
 
     const bool kStaged = (MODE == MODE_STORE) && NSPLIT == 1 && BN <= 128 && p.out_stage_bytes > 0;
+    const bool kBlockStaged = (MODE == MODE_STORE) && NSPLIT == 1 && BN == 256 && EW == 4 && p.out_stage_bytes > 0;
     const int ob_i = kStaged ? it % p.out_bufs : 0;     // staging buffer of this tile
     bool out_buf_ready = false;                         // (waited for as late as possible: just before the first write)
     const bool kMaskStaged = kStaged && p.mask_bufs > 0;
@@ -651,6 +668,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int i = 0; i < 32; ++i) {
           v[i] = r[i] + s_bias[c0 + i];
           if (p.relu) v[i] = fmaxf(v[i], 0.f);
+        }
+        // Staging-buffer waits are taken by EVERY thread (also those of out-of-image rows, which write nothing): a
+        // thread that skipped them could run several tiles ahead and arrive twice in one phase of out_full.
+        if (kStaged && !out_buf_ready) {   // the store that last used this buffer has read it
+          mbar_wait(&out_free_bar[ob_i], (static_cast<uint32_t>(it / p.out_bufs) & 1u) ^ 1u);
+          out_buf_ready = true;
+        }
+        if (kBlockStaged && (c0 & 63) == 0) {
+          const int R = it * (BN / 64) + (c0 >> 6);
+          mbar_wait(&out_free_bar[R & 1], (static_cast<uint32_t>(R >> 1) & 1u) ^ 1u);
         }
         if (valid) {
           if (mbase) {
@@ -676,11 +703,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (!(__bfloat162float(mb[e]) > 0.f)) v[i + e] = 0.f;
             }
           }
-          if (kStaged) {
-            if (!out_buf_ready) {   // the store that last used this buffer has read it
-              mbar_wait(&out_free_bar[ob_i], (static_cast<uint32_t>(it / p.out_bufs) & 1u) ^ 1u);
-              out_buf_ready = true;
+          if (kBlockStaged) {
+            // BN = 256: 64-channel blocks go through two 16 KB staging tiles as they are produced (round = block)
+            const int b = (it * (BN / 64) + (c0 >> 6)) & 1;
+            uint8_t* row = s_out + b * 16384 + m * 128;
+#pragma unroll
+            for (int i = 0; i < 32; i += 8) {
+              const int chunk = ((c0 & 63) + i) >> 3;
+              *reinterpret_cast<uint4*>(row + ((chunk ^ (m & 7)) << 4)) =
+                  make_uint4(pack_bf16x2(v[i], v[i + 1]), pack_bf16x2(v[i + 2], v[i + 3]), pack_bf16x2(v[i + 4], v[i + 5]),
+                             pack_bf16x2(v[i + 6], v[i + 7]));
             }
+          } else if (kStaged) {
             // 16-byte chunks into the 128B-swizzled [64-ch block][pixel][64 ch] staging tile
             uint8_t* row = s_out + ob_i * (BN * 256) + (c0 >> 6) * 16384 + m * 128;
 #pragma unroll
@@ -701,6 +735,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for (int i = 0; i < 32; i += 4)
               *reinterpret_cast<float4*>(fbase + c0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
           }
+        }
+        if (kBlockStaged && (c0 & 63) == 32) {   // this 64-channel block is complete: hand it to the output warp
+          fence_proxy_async();
+          mbar_arrive(&out_full_bar[(it * (BN / 64) + (c0 >> 6)) & 1]);
         }
         if (kDbRegMode && db_reg) {
 #pragma unroll
