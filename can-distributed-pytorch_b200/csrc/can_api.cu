@@ -424,9 +424,10 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     g_tmO = &tmO;
     p.out_stage_bytes = 2 * bn * 256;
   }
-  if (ns == 1 && a->mode == CAN_MODE_STORE && bn == 256 && a->out && !a->out_f32 && env_int("CAN_B200_STAGE256", 1) != 0 &&
+  if (ns == 1 && a->mode == CAN_MODE_STORE && bn == 256 && a->out && !a->out_f32 && env_int("CAN_B200_STAGE256", 0) != 0 &&
       env_int("CAN_B200_TMASTORE", 1) != 0) {
-    // widest tiles: 64-channel blocks through two 16 KB staging tiles (the operand ring keeps 3-4 stages)
+    // widest tiles (opt-in experiment): 64-channel blocks through two 16 KB staging tiles.  Measured 3 % SLOWER on the
+    // training step: the staging takes a fourth stage away from the operand ring, which matters more than the stores
     const uint64_t cs = static_cast<uint64_t>(a->out_cs) * 2;
     const uint64_t dimsO[4] = {static_cast<uint64_t>(a->Cout), static_cast<uint64_t>(a->W), static_cast<uint64_t>(a->H),
                                static_cast<uint64_t>(a->N)};
