@@ -608,16 +608,18 @@ ctx_outer_kernel(const float* __restrict__ A, long long a_ns, long long a_ps, lo
       s_a[i >> 4][i & 15] = A[n * a_ns + (OFF[j] + (i >> 4)) * a_ps + j * a_js + r0 + (i & 15)];
     __syncthreads();
     const float* bp = B + (static_cast<long long>(n) * 50 + OFF[j]) * 512;
-    for (int p = 0; p < S2; p += 4) {
-      float b0[4], b1[4];
+    constexpr int kU = 12;   // positions of loads in flight (the loop is bound by the L2 latency of the B rows)
+    for (int p = 0; p < S2; p += kU) {
+      float b0[kU], b1[kU];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {  // four positions of loads in flight
+      for (int u = 0; u < kU; ++u) {
         const bool on = (p + u) < S2;
         b0[u] = on ? bp[(p + u) * 512 + c] : 0.f;
         b1[u] = on ? bp[(p + u) * 512 + c + 256] : 0.f;
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < kU; ++u) {
+        if (p + u >= S2) break;
         const int pp = min(p + u, S2 - 1);
 #pragma unroll
         for (int r = 0; r < 16; ++r) {
