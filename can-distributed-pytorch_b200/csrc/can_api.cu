@@ -436,8 +436,8 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     int rc = make_tmap(&tmO, static_cast<__nv_bfloat16*>(a->out) + a->out_coff, 4, dimsO, strO, boxO);
     if (rc) return rc;
     g_tmO = &tmO;
-    p.out_bufs = 2;
-    p.out_stage_bytes = 32768;
+    p.out_bufs = env_int("CAN_B200_STAGE256", 0) == 2 ? 2 : 1;
+    p.out_stage_bytes = p.out_bufs * 16384;
   }
   if (ns == 1 && a->mode == CAN_MODE_STORE && (bn == 64 || bn == 128) && a->out && env_int("CAN_B200_TMASTORE", 1) != 0) {
     const uint64_t cs = static_cast<uint64_t>(a->out_cs) * 2;

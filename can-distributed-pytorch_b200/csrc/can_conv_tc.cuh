@@ -493,16 +493,23 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
         CAN_TILE_DECODE(tile)
         for (int blk = 0; blk < BN / 64; ++blk, ++R) {
-          const int b = R & 1;
-          mbar_wait(&out_full_bar[b], static_cast<uint32_t>(R >> 1) & 1u);
+          const int nb = p.out_bufs, b = R % nb;
+          mbar_wait(&out_full_bar[b], static_cast<uint32_t>(R / nb) & 1u);
           tma_store_4d(&tmO, s_out + b * 16384, n0 + blk * 64, x0, y0, n_img);
           bulk_commit_group();
-          bulk_wait_group_read1();
-          if (R > 0) mbar_arrive(&out_free_bar[b ^ 1]);
+          if (nb == 1) {
+            bulk_wait_group_read0();
+            mbar_arrive(&out_free_bar[0]);
+          } else {
+            bulk_wait_group_read1();
+            if (R > 0) mbar_arrive(&out_free_bar[b ^ 1]);
+          }
         }
       }
-      bulk_wait_group_read0();
-      if (R > 0) mbar_arrive(&out_free_bar[(R - 1) & 1]);
+      if (p.out_bufs == 2) {
+        bulk_wait_group_read0();
+        if (R > 0) mbar_arrive(&out_free_bar[(R - 1) & 1]);
+      }
     } else if (out_lane) {
       const int nb = p.out_bufs;   // 1 or 2
       int it = 0;
@@ -677,7 +684,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         if (kBlockStaged && (c0 & 63) == 0) {
           const int R = it * (BN / 64) + (c0 >> 6);
-          mbar_wait(&out_free_bar[R & 1], (static_cast<uint32_t>(R >> 1) & 1u) ^ 1u);
+          mbar_wait(&out_free_bar[R % p.out_bufs], (static_cast<uint32_t>(R / p.out_bufs) & 1u) ^ 1u);
         }
         if (valid) {
           if (mbase) {
@@ -705,7 +712,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
           if (kBlockStaged) {
             // BN = 256: 64-channel blocks go through two 16 KB staging tiles as they are produced (round = block)
-            const int b = (it * (BN / 64) + (c0 >> 6)) & 1;
+            const int b = (it * (BN / 64) + (c0 >> 6)) % p.out_bufs;
             uint8_t* row = s_out + b * 16384 + m * 128;
 #pragma unroll
             for (int i = 0; i < 32; i += 8) {
@@ -738,7 +745,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         if (kBlockStaged && (c0 & 63) == 32) {   // this 64-channel block is complete: hand it to the output warp
           fence_proxy_async();
-          mbar_arrive(&out_full_bar[(it * (BN / 64) + (c0 >> 6)) & 1]);
+          mbar_arrive(&out_full_bar[(it * (BN / 64) + (c0 >> 6)) % p.out_bufs]);
         }
         if (kDbRegMode && db_reg) {
 #pragma unroll
