@@ -169,8 +169,9 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   // three balanced groups of three taps at BN = 128 fill 144 (measured: 512->512 186 -> 172 us, 1024->512 369 -> 334 us;
   // the 256-wide layers are better off with BN = 256)
   if (nsplit == 1 && taps == 9 && Cin >= 512 && Cout >= 512 && env_int("CAN_B200_WGBN", 128) == 128) pl.bn = 128;
-  // widest tiles (bf16 path, BN = 256, two taps): an 80 KB stage would leave a 2-deep pipeline -> 32-pixel patches
-  pl.pix = (nsplit == 1 && taps > 1 && pl.bn == 256 && env_int("CAN_B200_WGPIX", 32) == 32) ? 32 : 64;
+  // multi-tap tiles (bf16 path, BN >= 128): 64-80 KB stages would leave a 2-3 deep pipeline -> 32-pixel patches
+  pl.pix = (nsplit == 1 && taps > 1 && (pl.bn == 256 || (pl.bn == 128 && env_int("CAN_B200_WGPIX128", 32) == 32)) &&
+            env_int("CAN_B200_WGPIX", 32) == 32) ? 32 : 64;
   pl.TW = (W >= 16) ? 16 : 8;
   pl.TH = pl.pix / pl.TW;
   pl.tiles_x = (W + pl.TW - 1) / pl.TW;
@@ -917,6 +918,7 @@ int conv_wgrad_impl(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, co
   }
   if (pl.T > 1) {  // bf16 path, several taps per CTA
     if (pl.bn == 64) rc = launch_wgrad<64, 1, 3>(tmDZ, tmX, p, grid, st);
+    else if (pl.bn == 128 && pl.pix == 32) rc = launch_wgrad<128, 1, 3, 32>(tmDZ, tmX, p, grid, st);
     else if (pl.bn == 128) rc = launch_wgrad<128, 1, 3>(tmDZ, tmX, p, grid, st);
     else if (pl.pix == 32) rc = launch_wgrad<256, 1, 2, 32>(tmDZ, tmX, p, grid, st);
     else rc = launch_wgrad<256, 1, 2>(tmDZ, tmX, p, grid, st);
