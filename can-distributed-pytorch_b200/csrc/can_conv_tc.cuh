@@ -2,13 +2,16 @@
 //
 //   D[pixel][cout] = sum_{tap, cin} X[pixel + off(tap)][cin] * Wp[cout][tap][cin]
 //
-// One CTA computes a 128-pixel (TH x TW spatial patch of one image) x BN-channel tile:
-//   warp 0   TMA producer: per k-block one 5-D box of the NHWC activation shifted by the
-//            tap offset (out-of-image pixels are zero-filled by TMA = conv padding) and
-//            one box of the K-major packed weights, both 128B-swizzled.
-//   warp 1   allocates TMEM and issues tcgen05.mma (M=128, N=BN, K=16) x4 per k-block.
-//   warps2-5 epilogue: tcgen05.ld the fp32 accumulator, fuse bias / ReLU / 2x2 max-pool /
-//            1x1 density head / ReLU-mask / max-unpool scatter / contextual fusion, store.
+// Persistent CTAs (one per SM) stride over 128-pixel (TH x TW spatial patch of one image) x BN-channel tiles:
+//   warp 0        TMA producer: per k-block one 5-D box of the NHWC activation shifted by the
+//                 tap offset (out-of-image pixels are zero-filled by TMA = conv padding) and
+//                 one box of the K-major packed weights, both 128B-swizzled.
+//   warp 1        allocates TMEM (2-4 accumulator stages) and issues tcgen05.mma (M=128, N=BN, K=16).
+//   warps 2..2+EW epilogue (EW = 4 or 8): tcgen05.ld the fp32 accumulator, fuse bias / ReLU / 2x2 max-pool /
+//                 1x1 density head / ReLU-mask / max-unpool scatter / contextual fusion.
+//   warp 2+EW     output warp (staged epilogues): hands bf16 tiles staged in shared memory to TMA stores.
+//   warp 3+EW     mask warp (staged dgrad epilogue): brings ReLU-mask tiles in by TMA.
+// Producer, MMA issuer and the two helper warps each run on one lane chosen with elect.sync.
 // NSPLIT > 1 is the fp32-parity mode: activations and weights are carried as NSPLIT bf16
 // planes (x = hi + lo [+ lo2]) and the products hi*hi, hi*lo, lo*hi (...) are accumulated
 // in the same fp32 TMEM tile.
