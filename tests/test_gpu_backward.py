@@ -38,7 +38,8 @@ def _cos(a, b):
 # ---------------------------------------------------------------- single kernels
 @pytest.mark.parametrize("case", [(1, 16, 16, 64, 64, 1), (2, 24, 40, 64, 128, 1), (1, 13, 17, 1024, 512, 2),
                                   (1, 24, 32, 128, 64, 2), (1, 16, 8, 256, 256, 1),
-                                  (1, 128, 400, 64, 64, 1)])   # > 5 patches per CTA: the swapped 64->64 wgrad wraps its stage ring
+                                  (1, 128, 400, 64, 64, 1),    # > 5 patches per CTA: the swapped 64->64 wgrad wraps its stage ring
+                                  (2, 13, 21, 64, 64, 1), (1, 11, 19, 128, 128, 1)])   # partial tiles through the staged TMA epilogues
 @pytest.mark.parametrize("nsplit", [1, 2])
 def test_wgrad_dgrad_bias_match_autograd_oracle(dev, case, nsplit):
     import torch.nn.functional as F
@@ -70,27 +71,29 @@ def test_wgrad_dgrad_bias_match_autograd_oracle(dev, case, nsplit):
     assert harness.rel_l2(db.cpu(), dzr.sum((0, 2, 3))) < 1e-5
 
 
-def test_unpool_routes_gradient_to_first_max(dev):
-    """conv (dgrad) + max-unpool epilogue against autograd of max_pool2d(relu(.)) on the CPU."""
+@pytest.mark.parametrize("shape", [(1, 12, 20, 24, 40, 64, 128), (2, 6, 9, 13, 19, 64, 128), (1, 10, 11, 21, 23, 128, 256)])
+def test_unpool_routes_gradient_to_first_max(dev, shape):
+    """conv (dgrad) + max-unpool epilogue against autograd of max_pool2d(relu(.)) on the CPU; the odd full-resolution
+    sizes leave a last row / column that no window covers (must stay zero) and partial tiles for the strided TMA stores."""
     import torch.nn.functional as F
     from can_b200 import ops
-    N, H, W, C = 1, 12, 20, 64       # pooled grid; the full-resolution map is 24 x 40
+    N, H, W, FH, FW, C, C2 = shape   # pooled grid H x W of a FH x FW map (floor-mode 2x2 pooling)
     g = torch.Generator().manual_seed(13)
-    pre = torch.randn(N, C, 2 * H, 2 * W, generator=g)
+    pre = torch.randn(N, C, FH, FW, generator=g)
     w_prev = torch.randn(C, C, 3, 3, generator=g) * 0.05
-    w = torch.randn(128, C, 3, 3, generator=g) * 0.05
-    dz = torch.randn(N, 128, H, W, generator=g)
+    w = torch.randn(C2, C, 3, 3, generator=g) * 0.05
+    dz = torch.randn(N, C2, H, W, generator=g)
     pa = ops.act_from_nchw(pre.to(dev), 1)
     pooled = ops.new_act(1, N, H, W, C, dev)
     arg = torch.empty(N, H, W, C, device=dev, dtype=torch.uint8)
     zero_bias = torch.zeros(C, device=dev)
     ops.conv_tc(pa, ops.pack_conv_weight(w_prev.to(dev), 1), C, mode=ops.MODE_POOL, bias=zero_bias, out=pooled, arg=arg)
-    full = ops.new_act(1, N, 2 * H, 2 * W, C, dev)
+    full = ops.new_act(1, N, FH, FW, C, dev)
     ops.conv_tc(pa, ops.pack_conv_weight(w_prev.to(dev), 1), C, mode=ops.MODE_STORE, relu=True, bias=zero_bias, out=full)
     dza = ops.act_from_nchw(dz.to(dev), 1)
-    out = ops.new_act(1, N, 2 * H, 2 * W, C, dev, zero=True)
+    out = ops.new_act(1, N, FH, FW, C, dev, zero=True)
     ops.conv_tc(dza, ops.pack_conv_weight(w.to(dev), 1, dgrad=True), C, mode=ops.MODE_UNPOOL, relu=False, out=out,
-                mask=pooled, arg=arg, OH=2 * H, OW=2 * W)
+                mask=pooled, arg=arg, OH=FH, OW=FW)
     # CPU truth: y = relu(conv_prev) (taken from the device, so ties are identical), X = maxpool(y)
     y = full.to_nchw().cpu().double().requires_grad_(True)
     X = F.max_pool2d(y, 2, 2)
