@@ -260,3 +260,25 @@ def test_sgd_matches_oracle(dev):
         pn, buf_n = O.sgd_momentum_step(pn, gr.double().numpy(), buf_n, 1e-3, 0.95)
     assert np.allclose(pd.cpu().numpy(), pn, rtol=1e-6, atol=1e-7)
     assert np.allclose(bd.cpu().numpy(), buf_n, rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cout", [64, 128])
+def test_conv_store_into_a_channel_window(dev, cout):
+    """The staged (TMA-store) epilogue writing a channel window [coff, coff + Cout) of a wider NHWC buffer, ragged tiles:
+    same values as a store into a dense tensor, and the neighbouring channels untouched."""
+    from can_b200 import ops
+    N, H, W, Cin = 2, 19, 37, 64
+    g = torch.Generator().manual_seed(8)
+    x = ops.act_from_nchw(torch.randn(N, Cin, H, W, generator=g).to(dev), 1)
+    w = (torch.randn(cout, Cin, 3, 3, generator=g) * 0.06).to(dev)
+    b = (torch.randn(cout, generator=g) * 0.1).to(dev)
+    wp = ops.pack_conv_weight(w, 1)
+    dense = ops.new_act(1, N, H, W, cout, dev, zero=True)
+    ops.conv_tc(x, wp, cout, mode=ops.MODE_STORE, relu=True, bias=b, out=dense)
+    wide = ops.new_act(1, N, H, W, cout + 128, dev, zero=True)
+    wide.buf.fill_(7.0)
+    ops.conv_tc(x, wp, cout, mode=ops.MODE_STORE, relu=True, bias=b, out=wide.view(cout, 64))
+    got = wide.buf.view(N, H, W, cout + 128)
+    assert torch.equal(got[..., 64:64 + cout], dense.buf.view(N, H, W, cout))
+    assert bool((got[..., :64] == 7.0).all()) and bool((got[..., 64 + cout:] == 7.0).all())
