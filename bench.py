@@ -287,6 +287,8 @@ def main():
     ops.PROFILE = []
     if wl["train"]:
         trainer.use_graph = False   # the event pairs live in the Python wrappers: this pass runs the same kernels eagerly
+    else:
+        os.environ["CAN_B200_GRAPH_INFER"] = "0"   # same for the inference graph of CANNet.forward
     torch.cuda.synchronize()
     for _ in range(min(args.steps, 5)):
         step_resident()

@@ -34,6 +34,7 @@ class WeightCache:
 
     def __init__(self):
         self._store = {}
+        self.epoch = 0      # bumped by invalidate(): lets graph replays notice in-place parameter updates
 
     def get(self, key, params, build):
         tag = tuple((p.data_ptr(), p._version, p.device) for p in params)
@@ -48,6 +49,7 @@ class WeightCache:
         """Drop every entry derived from parameters (after an in-place arena update, which does
         not bump version counters); shape-only entries (empty tag) are kept."""
         self._store = {k: v for k, v in self._store.items() if v[0] == ()}
+        self.epoch += 1
 
 
 def _packed(cache, tag, li, wt, nsplit, both):

@@ -282,3 +282,24 @@ def test_conv_store_into_a_channel_window(dev, cout):
     got = wide.buf.view(N, H, W, cout + 128)
     assert torch.equal(got[..., 64:64 + cout], dense.buf.view(N, H, W, cout))
     assert bool((got[..., :64] == 7.0).all()) and bool((got[..., 64 + cout:] == 7.0).all())
+
+
+@pytest.mark.gpu
+def test_inference_graph_replay_equals_eager_and_follows_weight_changes(dev):
+    """no_grad calls of one shape replay a CUDA graph from the third call on: same output as the eager pass, results do
+    not alias each other, and a parameter change (load_state_dict / in-place update + cache invalidation) is picked up."""
+    m = _model("he", "bf16", dev)
+    x = harness.make_input(2, 64, 96).to(dev)
+    x2 = harness.make_input(2, 64, 96, seed=77).to(dev)
+    with torch.no_grad():
+        outs = [m(x) for _ in range(4)]           # eager, eager, capture + replay, replay
+        assert all(torch.equal(outs[0], o) for o in outs[1:])
+        o2 = m(x2)                                # replay with other data
+        assert not torch.equal(o2, outs[0]) and torch.equal(outs[3], outs[0])   # earlier results were not overwritten
+        m.load_state_dict(harness.make_state_dict("default"))
+        ref = _model("default", "bf16", dev)(x)
+        assert torch.equal(m(x), ref)             # new weights -> graph dropped, eager again
+        with torch.no_grad():
+            m.backend[10].bias.data.add_(0.5)     # in-place change without a version bump on .data ...
+        m._wcache.invalidate()                    # ... announced the way FusedTrainer does
+        assert not torch.equal(m(x), ref)
