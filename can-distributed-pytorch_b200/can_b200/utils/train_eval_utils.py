@@ -171,7 +171,9 @@ def train_one_epoch(model, optimizer, train_loader, device, epoch):
         except Exception:
             pass
     fused = isinstance(optimizer, FusedTrainer)
-    for step, (img, gt_dmap) in enumerate(train_loader):
+    # the next batch's host->device copies run on a side stream while this step computes (pinned loaders overlap fully)
+    batches = DevicePrefetcher(train_loader, device) if torch.device(device).type == "cuda" else train_loader
+    for step, (img, gt_dmap) in enumerate(batches):
         img = img.to(device, non_blocking=True)
         gt_dmap = gt_dmap.to(device, non_blocking=True)
         if fused:
@@ -199,7 +201,8 @@ def evaluate(model, test_loader, device, epoch=0, show_images=False, use_wandb=F
     image; like the reference (:83) the absolute difference is taken over the whole batch tensor."""
     model.eval()
     mae = torch.zeros(1, device=device)
-    for img, gt_dmap in test_loader:
+    batches = DevicePrefetcher(test_loader, device) if torch.device(device).type == "cuda" else test_loader
+    for img, gt_dmap in batches:
         img = img.to(device, non_blocking=True)
         gt_dmap = gt_dmap.to(device, non_blocking=True)
         et = model(img)
