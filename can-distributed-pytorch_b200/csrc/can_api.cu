@@ -105,6 +105,25 @@ int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p,
     attr_done = true;
     attr_smem = kMaxSmem;
   }
+  if (p.cluster) {
+    // clusters of two CTAs (weight tiles shared through TMA multicast): extended launch with the cluster dimension
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(128 + 32 * EW);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA,
+                                       g_tmO ? *g_tmO : tmA, g_tmM ? *g_tmM : tmA, p);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(conv_tc, cluster 2)");
+    return 0;
+  }
   kern<<<grid, 128 + 32 * EW, smem, st>>>(tmA, tmB, g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA, g_tmO ? *g_tmO : tmA,
                                          g_tmM ? *g_tmM : tmA, p);
   CAN_CHECK_LAUNCH("conv_tc launch");
@@ -541,6 +560,28 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
            : ns == 2 ? dispatch_mode<128, 2>(a->mode, tmA, tmB, p, grid, so, st)
                      : dispatch_mode<128, 3>(a->mode, tmA, tmB, p, grid, so, st);
   if (ns == 3) return fail(-13, "conv_tc: bn=256 does not fit with 3 planes");
+  // widest tiles, bf16 path: the kernel is bound by L2 -> SM operand traffic (2/3 of it weights); pairs of CTAs
+  // working on the same n-tile fetch each weight tile once and multicast it
+  CUtensorMap tmBh;
+  if (ns == 1 && a->mode == CAN_MODE_STORE && !p.out_stage_bytes && !p.mask_bufs && ctas >= 2 &&
+      env_int("CAN_B200_CLUSTER", 1) != 0) {
+    const uint64_t K = static_cast<uint64_t>(a->taps) * a->Cin;
+    const uint64_t dimsB[3] = {K, static_cast<uint64_t>(a->Cout), 1};
+    const uint64_t strB[2] = {K * 2, K * 2 * a->Cout};
+    const uint32_t boxB[3] = {64, 128, 1};
+    int rc = make_tmap(&tmBh, a->w, 3, dimsB, strB, boxB);
+    if (rc) return rc;
+    g_tmT = &tmBh;
+    p.cluster = 1;
+    p.pix_tiles = p.tiles_x * p.tiles_y * a->N;
+    p.num_pair_tiles = ((p.pix_tiles + 1) / 2) * p.n_tiles;
+    int pairs = ctas / 2;
+    if (pairs > p.num_pair_tiles) pairs = p.num_pair_tiles;
+    grid = dim3(2 * pairs);
+    rc = dispatch_mode<256, 1>(a->mode, tmA, tmB, p, grid, so, st);
+    g_tmT = nullptr;
+    return rc;
+  }
   return ns == 1 ? dispatch_mode<256, 1>(a->mode, tmA, tmB, p, grid, so, st)
                  : dispatch_mode<256, 2>(a->mode, tmA, tmB, p, grid, so, st);
 }

@@ -47,6 +47,9 @@ struct ConvTcParams {
   int w_bytes;         // HALO: bytes of the resident weight region (9 * kchunks * BN * 128)
   int halo_bytes;      // HALO: bytes of one activation stage ((TH + 2 dil) * TW * 128)
   int out_stage_bytes; // > 0: the epilogue stages the bf16 tile in shared memory (BN * 256 B) and writes it with TMA (tmO)
+  int cluster;         // 1: launched as clusters of two CTAs that share every weight tile through TMA multicast (tmT = half-tile map)
+  int pix_tiles;       // tiles_x * tiles_y * N
+  int num_pair_tiles;  // cluster mode: ceil(pix_tiles / 2) * n_tiles work items per CTA pair
   int out_bufs;        // MODE_STORE staged epilogue: 1 or 2 staging buffers of BN * 256 B (out_stage_bytes = their sum)
   int mask_bufs;       // staged epilogue: 0 = mask read from global memory, 1|2 = mask tiles (BN * 256 B each) brought in by TMA (tmM)
   int relu;
@@ -253,6 +256,23 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   constexpr int ACC_COLS = AccLayout<BN, GS>::cols(MODE);
   constexpr int ACC_STAGES = AccLayout<BN, GS>::acc_stages(MODE);
   const int base_kb = p.taps * p.kchunks;
+  // Work items.  Plain: CTA b takes tiles b, b + grid, ...  Cluster mode: the two CTAs of a pair walk the same list of
+  // (pixel-tile pair, n-tile) items in lockstep, rank r taking pixel tile 2*pair + r, so both need the same weight tile
+  // at the same time (a missing odd partner recomputes the last pixel tile and drops the result).
+  const bool cl = p.cluster != 0;
+  const int cta_rank = cl ? static_cast<int>(cluster_ctarank()) : 0;
+  const int T0 = cl ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int TS = cl ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  const int TN = cl ? p.num_pair_tiles : p.num_tiles;
+  auto tile_of = [&](int q, bool& live) {
+    live = true;
+    if (!cl) return q;
+    const int nt = q % p.n_tiles;
+    int pix = 2 * (q / p.n_tiles) + cta_rank;
+    live = pix < p.pix_tiles;
+    pix = min(pix, p.pix_tiles - 1);
+    return pix * p.n_tiles + nt;
+  };
   // MODE_CTX2: two extra k-blocks whose A operand is the interpolation matrix Wint[pixel][64 positions]
   // and whose B operands are the per-image tables (-U-side of z, then s) -- see the epilogue.
   constexpr bool kCtx2 = (MODE == MODE_CTX2 || MODE == MODE_CTX2_BWD);
@@ -283,7 +303,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (lane == 0) {
       for (int s = 0; s < stages; ++s) {
         mbar_init(&full_bar[s], 1);
-        mbar_init(&empty_bar[s], 1);
+        mbar_init(&empty_bar[s], p.cluster ? 2 : 1);   // cluster mode: the MMAs of both CTAs release a stage
       }
       for (int a = 0; a < 4; ++a) {
         mbar_init(&tmem_full_bar[a], 1);
@@ -307,6 +327,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  if (cl) cluster_sync_all();   // the partner's barriers exist before anything is multicast to them
   const uint32_t tmem_base = *tmem_ptr_smem;
 
   if (warp == 0) {
@@ -335,7 +356,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
       } else
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      for (int q_ = T0; q_ < TN; q_ += TS) {
+        bool live_;
+        const int tile = tile_of(q_, live_);
         CAN_TILE_DECODE(tile)
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -356,7 +379,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
             for (int pl = 0; pl < GS; ++pl) {
               tma_load_5d(sa + pl * L::kABytes, &tmA, &full_bar[stage], chunk * 64, x0 + dx, y0 + dy, n_img, pl);
-              tma_load_3d(sb + pl * L::kBBytes, &tmB, &full_bar[stage], kb * 64, n0, pl);
+              if (cl)   // my half of the weight tile, delivered to both CTAs of the pair (tmT: box of BN / 2 rows)
+                tma_load_3d_multicast(sb + pl * L::kBBytes + cta_rank * (L::kBBytes / 2), &tmT, &full_bar[stage], kb * 64,
+                                      n0 + cta_rank * (BN / 2), pl, static_cast<uint16_t>(3));
+              else
+                tma_load_3d(sb + pl * L::kBBytes, &tmB, &full_bar[stage], kb * 64, n0, pl);
             }
           }
           if (++stage == stages) {
@@ -374,7 +401,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t phase = 0;
       constexpr int NACC = AccLayout<BN, GS>::kNacc;
       int it = 0;  // tiles processed by this CTA
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      for (int q_ = T0; q_ < TN; q_ += TS, ++it) {
         const int as = it % ACC_STAGES;
         const uint32_t aphase = static_cast<uint32_t>(it / ACC_STAGES) & 1u;
         mbar_wait(&tmem_empty_bar[as], aphase ^ 1);  // epilogue drained this accumulator stage
@@ -437,7 +464,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               }
             }
           }
-          umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+          // frees the smem slot when these MMAs retire (cluster mode: in both CTAs, whose producers write both slots)
+          if (cl) umma_commit_multicast(&empty_bar[stage], static_cast<uint16_t>(3));
+          else umma_commit(&empty_bar[stage]);
           if (++stage == stages) {
             stage = 0;
             phase ^= 1;
@@ -575,7 +604,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
     for (int i = 0; i < (kDbRegMode ? 32 : 1); ++i) dbacc[i] = 0.f;
     int it = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+    for (int q_ = T0; q_ < TN; q_ += TS, ++it) {
+    bool live_;
+    const int tile = tile_of(q_, live_);
     CAN_TILE_DECODE(tile)
     const int as = it % ACC_STAGES;
     const uint32_t aphase = static_cast<uint32_t>(it / ACC_STAGES) & 1u;
@@ -621,7 +652,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (!bias_once || it == 0) asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
 
     const int y = y0 + ty, x = x0 + tx;
-    const bool valid = (y < p.H) && (x < p.W);
+    const bool valid = live_ && (y < p.H) && (x < p.W);
     const uint32_t taddr = tmem_base + as * ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
 
     // Operands of the epilogue that do not depend on the accumulator (ReLU mask / arg-max codes /
@@ -673,6 +704,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int c0 = cbeg; c0 < cend; c0 += 32) {
         float r[32];
         load_acc<BN, GS, 32>(taddr, c0, nact, r);
+        if ((p.dbg & 64) || ((p.dbg & 128) && (warp & 3) == 1)) continue;   // bring-up experiments: accumulator reads only (all warps / the warp sharing the MMA issuer's scheduler)
         float v[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
@@ -737,7 +769,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               const int chunk = ((c0 & 63) + i) >> 3;
               *reinterpret_cast<uint4*>(row + ((chunk ^ (m & 7)) << 4)) = q;
             }
-          } else if (p.out) {
+          } else if (p.out && !(p.dbg & 256)) {   // (bit 256: bring-up experiment, all the arithmetic but no store)
             store_bf16_planes<NSPLIT, 32>(obase + c0, p.out_plane, v);
           }
           if (fbase) {
@@ -1371,6 +1403,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   tc_fence_before();
   __syncthreads();
+  if (cl) cluster_sync_all();   // neither CTA leaves while the other may still signal its barriers
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, ACC_COLS * ACC_STAGES);

@@ -70,6 +70,8 @@ CONV_CASES = [
     (1, 24, 32, 1024, 512, 2, 256),
     (1, 13, 17, 256, 128, 2, 0),   # ragged tile (H, W not multiples of the 8x16 patch)
     (1, 16, 8, 64, 64, 1, 0),      # W < 16 -> 16x8 patch
+    (1, 24, 16, 256, 512, 1, 256), # three pixel tiles: the odd CTA of a cluster pair recomputes and drops a tile
+    (3, 8, 16, 512, 256, 2, 256),  # one n-tile, three pixel tiles (cluster pairs with a single n-tile)
 ]
 
 
