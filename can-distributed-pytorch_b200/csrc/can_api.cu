@@ -114,7 +114,7 @@ int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p,
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.x = p.cluster;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
@@ -568,16 +568,17 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     const uint64_t K = static_cast<uint64_t>(a->taps) * a->Cin;
     const uint64_t dimsB[3] = {K, static_cast<uint64_t>(a->Cout), 1};
     const uint64_t strB[2] = {K * 2, K * 2 * a->Cout};
-    const uint32_t boxB[3] = {64, 128, 1};
+    const int cs = env_int("CAN_B200_CLUSTER", 1) == 4 && ctas >= 4 ? 4 : 2;
+    const uint32_t boxB[3] = {64, static_cast<uint32_t>(256 / cs), 1};
     int rc = make_tmap(&tmBh, a->w, 3, dimsB, strB, boxB);
     if (rc) return rc;
     g_tmT = &tmBh;
-    p.cluster = 1;
+    p.cluster = cs;
     p.pix_tiles = p.tiles_x * p.tiles_y * a->N;
-    p.num_pair_tiles = ((p.pix_tiles + 1) / 2) * p.n_tiles;
-    int pairs = ctas / 2;
+    p.num_pair_tiles = ((p.pix_tiles + cs - 1) / cs) * p.n_tiles;
+    int pairs = ctas / cs;
     if (pairs > p.num_pair_tiles) pairs = p.num_pair_tiles;
-    grid = dim3(2 * pairs);
+    grid = dim3(cs * pairs);
     rc = dispatch_mode<256, 1>(a->mode, tmA, tmB, p, grid, so, st);
     g_tmT = nullptr;
     return rc;

@@ -47,9 +47,9 @@ struct ConvTcParams {
   int w_bytes;         // HALO: bytes of the resident weight region (9 * kchunks * BN * 128)
   int halo_bytes;      // HALO: bytes of one activation stage ((TH + 2 dil) * TW * 128)
   int out_stage_bytes; // > 0: the epilogue stages the bf16 tile in shared memory (BN * 256 B) and writes it with TMA (tmO)
-  int cluster;         // 1: launched as clusters of two CTAs that share every weight tile through TMA multicast (tmT = half-tile map)
+  int cluster;         // 0, or the cluster size (2 | 4): CTAs of a cluster share every weight tile through TMA multicast (tmT = 1/size-tile map)
   int pix_tiles;       // tiles_x * tiles_y * N
-  int num_pair_tiles;  // cluster mode: ceil(pix_tiles / 2) * n_tiles work items per CTA pair
+  int num_pair_tiles;  // cluster mode: ceil(pix_tiles / size) * n_tiles work items per cluster
   int out_bufs;        // MODE_STORE staged epilogue: 1 or 2 staging buffers of BN * 256 B (out_stage_bytes = their sum)
   int mask_bufs;       // staged epilogue: 0 = mask read from global memory, 1|2 = mask tiles (BN * 256 B each) brought in by TMA (tmM)
   int relu;
@@ -261,14 +261,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   // at the same time (a missing odd partner recomputes the last pixel tile and drops the result).
   const bool cl = p.cluster != 0;
   const int cta_rank = cl ? static_cast<int>(cluster_ctarank()) : 0;
-  const int T0 = cl ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
-  const int TS = cl ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  const int csz = cl ? p.cluster : 1;
+  const uint16_t cmask = static_cast<uint16_t>((1u << csz) - 1u);
+  const int T0 = static_cast<int>(blockIdx.x) / csz;
+  const int TS = static_cast<int>(gridDim.x) / csz;
   const int TN = cl ? p.num_pair_tiles : p.num_tiles;
   auto tile_of = [&](int q, bool& live) {
     live = true;
     if (!cl) return q;
     const int nt = q % p.n_tiles;
-    int pix = 2 * (q / p.n_tiles) + cta_rank;
+    int pix = csz * (q / p.n_tiles) + cta_rank;
     live = pix < p.pix_tiles;
     pix = min(pix, p.pix_tiles - 1);
     return pix * p.n_tiles + nt;
@@ -303,7 +305,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (lane == 0) {
       for (int s = 0; s < stages; ++s) {
         mbar_init(&full_bar[s], 1);
-        mbar_init(&empty_bar[s], p.cluster ? 2 : 1);   // cluster mode: the MMAs of both CTAs release a stage
+        mbar_init(&empty_bar[s], p.cluster ? p.cluster : 1);   // cluster mode: the MMAs of every CTA release a stage
       }
       for (int a = 0; a < 4; ++a) {
         mbar_init(&tmem_full_bar[a], 1);
@@ -379,9 +381,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
             for (int pl = 0; pl < GS; ++pl) {
               tma_load_5d(sa + pl * L::kABytes, &tmA, &full_bar[stage], chunk * 64, x0 + dx, y0 + dy, n_img, pl);
-              if (cl)   // my half of the weight tile, delivered to both CTAs of the pair (tmT: box of BN / 2 rows)
-                tma_load_3d_multicast(sb + pl * L::kBBytes + cta_rank * (L::kBBytes / 2), &tmT, &full_bar[stage], kb * 64,
-                                      n0 + cta_rank * (BN / 2), pl, static_cast<uint16_t>(3));
+              if (cl)   // my share of the weight tile, delivered to every CTA of the cluster (tmT: box of BN / size rows)
+                tma_load_3d_multicast(sb + pl * L::kBBytes + cta_rank * (L::kBBytes / csz), &tmT, &full_bar[stage], kb * 64,
+                                      n0 + cta_rank * (BN / csz), pl, cmask);
               else
                 tma_load_3d(sb + pl * L::kBBytes, &tmB, &full_bar[stage], kb * 64, n0, pl);
             }
@@ -465,7 +467,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
           }
           // frees the smem slot when these MMAs retire (cluster mode: in both CTAs, whose producers write both slots)
-          if (cl) umma_commit_multicast(&empty_bar[stage], static_cast<uint16_t>(3));
+          if (cl) umma_commit_multicast(&empty_bar[stage], cmask);
           else umma_commit(&empty_bar[stage]);
           if (++stage == stages) {
             stage = 0;
