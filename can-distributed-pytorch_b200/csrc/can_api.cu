@@ -67,6 +67,20 @@ int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, 
   return 0;
 }
 
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+// memory hung the GPU: the cluster variant is taken only when the weight buffer is plain device memory of the
+// current device (anything else -- peer, managed, host-mapped, unknown -- gets the per-CTA loads).
+bool weights_on_current_device(const void* ptr) {
+  int dev = -1;
+  cudaPointerAttributes at;
+  if (cudaGetDevice(&dev) != cudaSuccess) return false;
+  if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeDevice && at.device == dev;
+}
+
 int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
   return v ? atoi(v) : dflt;
@@ -564,7 +578,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   // working on the same n-tile fetch each weight tile once and multicast it
   CUtensorMap tmBh;
   if (ns == 1 && a->mode == CAN_MODE_STORE && !p.out_stage_bytes && !p.mask_bufs && ctas >= 2 &&
-      env_int("CAN_B200_CLUSTER", 1) != 0) {
+      env_int("CAN_B200_CLUSTER", 1) != 0 && weights_on_current_device(a->w)) {
     const uint64_t K = static_cast<uint64_t>(a->taps) * a->Cin;
     const uint64_t dimsB[3] = {K, static_cast<uint64_t>(a->Cout), 1};
     const uint64_t strB[2] = {K * 2, K * 2 * a->Cout};
