@@ -578,11 +578,11 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   // working on the same n-tile fetch each weight tile once and multicast it
   CUtensorMap tmBh;
   if (ns == 1 && a->mode == CAN_MODE_STORE && !p.out_stage_bytes && !p.mask_bufs && ctas >= 2 &&
-      env_int("CAN_B200_CLUSTER", 1) != 0 && weights_on_current_device(a->w)) {
+      env_int("CAN_B200_CLUSTER", 0) != 0 && weights_on_current_device(a->w)) {
     const uint64_t K = static_cast<uint64_t>(a->taps) * a->Cin;
     const uint64_t dimsB[3] = {K, static_cast<uint64_t>(a->Cout), 1};
     const uint64_t strB[2] = {K * 2, K * 2 * a->Cout};
-    const int cs = env_int("CAN_B200_CLUSTER", 1) == 4 && ctas >= 4 ? 4 : 2;
+    const int cs = env_int("CAN_B200_CLUSTER", 0) == 4 && ctas >= 4 ? 4 : 2;
     const uint32_t boxB[3] = {64, static_cast<uint32_t>(256 / cs), 1};
     int rc = make_tmap(&tmBh, a->w, 3, dimsB, strB, boxB);
     if (rc) return rc;

@@ -75,6 +75,13 @@ CONV_CASES = [
 ]
 
 
+@pytest.mark.parametrize("case", [c for c in CONV_CASES if c[6] == 256])
+def test_conv_store_cluster_variant_matches_oracle(dev, case, monkeypatch):
+    """The opt-in 2-CTA cluster variant (weight tiles shared by TMA multicast) gives the same tiles."""
+    monkeypatch.setenv("CAN_B200_CLUSTER", "1")
+    test_conv_store_matches_oracle(dev, case, 1)
+
+
 @pytest.mark.parametrize("case", CONV_CASES)
 @pytest.mark.parametrize("nsplit", [1, 2])
 def test_conv_store_matches_oracle(dev, case, nsplit):
