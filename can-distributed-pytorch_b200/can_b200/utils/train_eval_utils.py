@@ -219,33 +219,56 @@ class DevicePrefetcher:
     (the reference copies synchronously from pageable memory, utils/train_eval_utils.py:30-31).
 
     ``for img, gt in DevicePrefetcher(loader, device): ...`` yields device tensors whose copies have
-    completed with respect to the current stream."""
+    completed with respect to the current stream.  The copies land in two resident sets of device buffers
+    used in turn (re-made only when a batch changes shape), so the steady state allocates nothing: a
+    yielded batch is valid until the iteration after the next one starts."""
+
+    _streams: dict = {}   # one copy stream per device for the life of the process
 
     def __init__(self, loader, device):
-        self.loader, self.device = loader, device
-        self.stream = torch.cuda.Stream(device=device)
+        self.loader, self.device = loader, torch.device(device)
+        key = (self.device.type, self.device.index if self.device.index is not None else torch.cuda.current_device())
+        if key not in DevicePrefetcher._streams:
+            DevicePrefetcher._streams[key] = torch.cuda.Stream(device=self.device)
+        self.stream = DevicePrefetcher._streams[key]
+        self._bufs = [None, None]
+        self._copied = [torch.cuda.Event(), torch.cuda.Event()]
+        self._freed = [None, None]
 
-    def _issue(self, batch):
+    def _issue(self, batch, slot):
+        bufs = self._bufs[slot]
         with torch.cuda.stream(self.stream):
-            dev = tuple(t.to(self.device, non_blocking=True) for t in batch)
-            ev = torch.cuda.Event()
-            ev.record(self.stream)
-        return dev, ev
+            if bufs is None or len(bufs) != len(batch) or any(b.shape != t.shape or b.dtype != t.dtype
+                                                              for b, t in zip(bufs, batch)):
+                bufs = tuple(torch.empty(t.shape, dtype=t.dtype, device=self.device) for t in batch)
+                self._bufs[slot] = bufs
+            if self._freed[slot] is not None:
+                self.stream.wait_event(self._freed[slot])   # the step that read this slot two batches ago
+            for b, t in zip(bufs, batch):
+                b.copy_(t, non_blocking=True)
+            self._copied[slot].record(self.stream)
+        return bufs
 
     def __iter__(self):
         it = iter(self.loader)
         try:
-            pending = self._issue(next(it))
+            pending = self._issue(next(it), 0)
         except StopIteration:
             return
+        slot = 0
         while pending is not None:
-            dev, ev = pending
+            dev = pending
             try:
-                pending = self._issue(next(it))   # next batch's H2D overlaps this batch's step
+                pending = self._issue(next(it), slot ^ 1)   # next batch's H2D overlaps this batch's step
             except StopIteration:
                 pending = None
             cur = torch.cuda.current_stream(self.device)
-            cur.wait_event(ev)
+            cur.wait_event(self._copied[slot])
             for t in dev:
                 t.record_stream(cur)
             yield dev
+            # the consumer has enqueued its step: the slot may be overwritten once that work is done
+            if self._freed[slot] is None:
+                self._freed[slot] = torch.cuda.Event()
+            self._freed[slot].record(torch.cuda.current_stream(self.device))
+            slot ^= 1
