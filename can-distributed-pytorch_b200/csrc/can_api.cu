@@ -151,11 +151,11 @@ int launch_conv_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUten
   using L = ConvTcSmem<BN, 1>;
   const int tail = L::kTailBytes;
   const int staged_bytes = p.out_stage_bytes + p.mask_bufs * BN * 256;
-  int stages = (kMaxSmem - 1024 - staged_bytes - p.w_bytes - tail) / p.halo_bytes;
+  int stages = (kMaxSmem - 1024 - staged_bytes - p.w_bytes - tail) / p.halo_stride;
   if (stages > 8) stages = 8;
   if (stages < 2) return fail(-20, "conv_tc(halo): BN=%d does not fit shared memory", BN);
   p.stages = stages;
-  const int smem = 1024 + staged_bytes + p.w_bytes + stages * p.halo_bytes + tail;
+  const int smem = 1024 + staged_bytes + p.w_bytes + stages * p.halo_stride + tail;
   auto kern = conv_tc_kernel<BN, 1, MODE, 1, 8>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -378,6 +378,18 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   p.taps = a->taps;
   p.dil = a->dil;
   p.TW = (a->W >= 16) ? 16 : 8;
+  // small-Cin layers on the bf16 path: resident weights + halo stages
+  const bool halo = a->nsplit == 1 && a->taps == 9 && a->Cout == bn && (bn == 64 || bn == 128) &&
+                    (a->mode == CAN_MODE_STORE || a->mode == CAN_MODE_POOL || a->mode == CAN_MODE_UNPOOL) &&
+                    9 * p.kchunks * bn * 128 <= 147456 && env_int("CAN_B200_HALO", 1) != 0;
+  // ... with ONE halo tile per (pixel tile, channel chunk): the patch is 8 pixels wide so that the 8-row groups of the
+  // MMA's A operand are whole patch rows, one halo pitch apart (see the kernel).  Opt-in: CAN_B200_HALO1=1 for 64
+  // output channels, 2 for every halo layer; the default stays one tile per x shift (measured
+  // 1-2 % faster per 64-wide kernel, 12 % slower at 128 wide, nothing on the whole step: these layers are bound by the
+  // MMA reading its operands from shared memory, not by L2->SM traffic)
+  const int halo1_env = env_int("CAN_B200_HALO1", 0);
+  p.halo1 = halo && (halo1_env == 2 || (halo1_env == 1 && bn == 64));
+  if (p.halo1) p.TW = 8;
   p.TH = 128 / p.TW;
   p.tiles_x = (a->W + p.TW - 1) / p.TW;
   p.tiles_y = (a->H + p.TH - 1) / p.TH;
@@ -494,29 +506,29 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
       p.mask_bufs = env_int("CAN_B200_MASKBUFS", bn == 64 ? 2 : 1);
     }
   }
-  // small-Cin layers on the bf16 path: resident weights + halo stages (L2->SM traffic / 3.6)
-  if (ns == 1 && a->taps == 9 && p.n_tiles == 1 && (bn == 64 || bn == 128) &&
-      (a->mode == CAN_MODE_STORE || a->mode == CAN_MODE_POOL || a->mode == CAN_MODE_UNPOOL) &&
-      9 * p.kchunks * bn * 128 <= 147456 && env_int("CAN_B200_HALO", 1) != 0) {
+  // small-Cin layers on the bf16 path: resident weights + halo stages (L2->SM traffic / 3.6, / 9 with one halo tile)
+  if (halo) {
     p.w_bytes = 9 * p.kchunks * bn * 128;
-    p.halo_bytes = (p.TH + 2 * a->dil) * p.TW * 128;
+    const int halo_w = p.halo1 ? p.TW + 2 * a->dil : p.TW;
+    p.halo_bytes = (p.TH + 2 * a->dil) * halo_w * 128;
+    p.halo_stride = (p.halo_bytes + 1023) & ~1023;   // every stage starts on a swizzle-pattern boundary
     // staged output only while at least two halo stages still fit beside the resident weights
     while (p.mask_bufs > 0 &&
-           1024 + p.out_stage_bytes + p.mask_bufs * bn * 256 + p.w_bytes + 2 * p.halo_bytes + 8192 > kMaxSmem)
+           1024 + p.out_stage_bytes + p.mask_bufs * bn * 256 + p.w_bytes + 2 * p.halo_stride + 8192 > kMaxSmem)
       --p.mask_bufs;
     if (!p.mask_bufs) g_tmM = nullptr;
     if (a->mode == CAN_MODE_STORE && p.out_bufs == 2 &&
-        1024 + p.out_stage_bytes + p.mask_bufs * bn * 256 + p.w_bytes + 3 * p.halo_bytes + 8192 > kMaxSmem) {
+        1024 + p.out_stage_bytes + p.mask_bufs * bn * 256 + p.w_bytes + 3 * p.halo_stride + 8192 > kMaxSmem) {
       p.out_bufs = 1;   // keep at least three halo stages
       p.out_stage_bytes = bn * 256;
     }
-    if (p.out_stage_bytes && 1024 + p.out_stage_bytes + p.w_bytes + 2 * p.halo_bytes + 8192 > kMaxSmem) {
+    if (p.out_stage_bytes && 1024 + p.out_stage_bytes + p.w_bytes + 2 * p.halo_stride + 8192 > kMaxSmem) {
       p.out_stage_bytes = 0;
       p.out_bufs = 0;
       g_tmO = nullptr;
     }
     CUtensorMap tmH;
-    int rc = make_act_tmap(&tmH, a->x, a->x_coff, a->Cin, a->x_cs, a->x_plane, 1, a->N, a->H, a->W, p.TW,
+    int rc = make_act_tmap(&tmH, a->x, a->x_coff, a->Cin, a->x_cs, a->x_plane, 1, a->N, a->H, a->W, halo_w,
                            p.TH + 2 * a->dil);
     if (rc) return rc;
     return bn == 64 ? dispatch_halo<64>(a->mode, tmA, tmB, tmH, p, grid, st)

@@ -45,7 +45,9 @@ struct ConvTcParams {
   int stages;
   int dbg;             // CAN_B200_DBG bit flags (bring-up experiments only; 0 in production)
   int w_bytes;         // HALO: bytes of the resident weight region (9 * kchunks * BN * 128)
-  int halo_bytes;      // HALO: bytes of one activation stage ((TH + 2 dil) * TW * 128)
+  int halo_bytes;      // HALO: bytes of one activation stage ((TH + 2 dil) * TW * 128; halo1: (TH + 2 dil) * (TW + 2 dil) * 128)
+  int halo_stride;     // HALO: distance between stages (halo_bytes rounded up to 1024)
+  int halo1;           // HALO: one halo tile per (pixel tile, channel chunk) serves all nine taps
   int out_stage_bytes; // > 0: the epilogue stages the bf16 tile in shared memory (BN * 256 B) and writes it with TMA (tmO)
   int cluster;         // 0, or the cluster size (2 | 4): CTAs of a cluster share every weight tile through TMA multicast (tmT = 1/size-tile map)
   int pix_tiles;       // tiles_x * tiles_y * N
@@ -234,7 +236,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint8_t* s_mask = smem + p.out_stage_bytes;                       // staged mask tiles (p.mask_bufs x BN * 256 B)
   uint8_t* wbase = s_mask + p.mask_bufs * (BN * 256);               // HALO: resident weights
   uint8_t* ring = HALO ? wbase + p.w_bytes : wbase;                // stage ring
-  const int stage_bytes = HALO ? p.halo_bytes : L::kStageBytes;
+  const int stage_bytes = HALO ? p.halo_stride : L::kStageBytes;
   uint8_t* tail = ring + stages * stage_bytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
   uint64_t* empty_bar = full_bar + 8;
@@ -345,11 +347,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           CAN_TILE_DECODE(tile)
           (void)n0;
           for (int chunk = 0; chunk < p.kchunks; ++chunk) {
-            for (int dxi = 0; dxi < 3; ++dxi) {
+            for (int dxi = p.halo1 ? 2 : 0; dxi < 3; ++dxi) {   // halo1: a single tile, x halo included
               mbar_wait(&empty_bar[stage], phase ^ 1);
               mbar_expect_tx(&full_bar[stage], static_cast<uint32_t>(p.halo_bytes));
-              tma_load_5d(ring + stage * stage_bytes, &tmW, &full_bar[stage], chunk * 64, x0 + (dxi - 1) * p.dil,
-                          y0 - p.dil, n_img, 0);
+              tma_load_5d(ring + stage * stage_bytes, &tmW, &full_bar[stage], chunk * 64,
+                          x0 + (p.halo1 ? -p.dil : (dxi - 1) * p.dil), y0 - p.dil, n_img, 0);
               if (++stage == stages) {
                 stage = 0;
                 phase ^= 1;
@@ -416,6 +418,40 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint32_t dy_bytes = static_cast<uint32_t>(p.dil * p.TW * 128);
           const uint32_t tap_row_units = static_cast<uint32_t>((3 * p.kchunks * L::kBBytes) >> 4);  // dy -> dy+1
           uint32_t accum = 0;
+          if (p.halo1) {
+            // One (TH + 2 dil) x (TW + 2 dil) halo tile per channel chunk, TW = 8: the 8-row groups of A are the patch
+            // rows, one halo pitch apart (SBO = pitch), and tap (dy, dx) starts (dy * pitch + dx) * dil pixels into
+            // the tile.  Neither is a multiple of the 1024-byte swizzle pattern: the MMA applies the 128B swizzle to
+            // the absolute shared-memory address, as the TMA write did (measured, tools/probe_umma_halo.cu), so any
+            // 128-byte-aligned start reads the right rows.
+            const uint32_t pitch = static_cast<uint32_t>(p.TW + 2 * p.dil);
+            for (int chunk = 0; chunk < p.kchunks; ++chunk) {
+              mbar_wait(&full_bar[stage], phase);
+              tc_fence_after();
+              const uint64_t da0 = umma_smem_desc(smem_u32(ring + stage * stage_bytes), 16, pitch * 128);
+              const uint64_t db0 = wdesc0 + static_cast<uint32_t>((chunk * L::kBBytes) >> 4);
+              const uint32_t tap_units = static_cast<uint32_t>((p.kchunks * L::kBBytes) >> 4);   // tap -> tap + 1
+              const uint32_t dx_units = static_cast<uint32_t>(p.dil) * 8, dy_units = dx_units * pitch;
+#pragma unroll
+              for (int dyi = 0; dyi < 3; ++dyi) {
+#pragma unroll
+                for (int dxi = 0; dxi < 3; ++dxi) {
+                  const uint64_t da = da0 + (dyi * dy_units + dxi * dx_units);
+                  const uint64_t db = db0 + (dyi * 3 + dxi) * tap_units;
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) {
+                    umma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, accum);
+                    accum = 1;
+                  }
+                }
+              }
+              umma_commit(&empty_bar[stage]);
+              if (++stage == stages) {
+                stage = 0;
+                phase ^= 1;
+              }
+            }
+          } else
           for (int chunk = 0; chunk < p.kchunks; ++chunk) {
             for (int dxi = 0; dxi < 3; ++dxi) {
               mbar_wait(&full_bar[stage], phase);

@@ -104,6 +104,14 @@ def test_conv_store_matches_oracle(dev, case, nsplit):
     assert rel < (3e-3 if nsplit == 1 else 3e-5), rel
 
 
+def test_single_halo_tile_variant_forward(dev, monkeypatch):
+    """CAN_B200_HALO1=2 (one halo tile for all nine taps): store and max-pool epilogues on 8-pixel-wide patches."""
+    monkeypatch.setenv("CAN_B200_HALO1", "2")
+    for case in [(1, 16, 16, 64, 64, 1, 0), (1, 16, 8, 64, 64, 1, 0), (2, 24, 40, 64, 128, 1, 0), (1, 13, 17, 128, 64, 2, 0)]:
+        test_conv_store_matches_oracle(dev, case, 1)
+    test_conv_pool_and_argmax(dev, 1)
+
+
 @pytest.mark.parametrize("nsplit", [1, 2])
 def test_conv_pool_and_argmax(dev, nsplit):
     from can_b200 import ops
