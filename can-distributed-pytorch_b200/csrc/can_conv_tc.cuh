@@ -214,6 +214,18 @@ __device__ __forceinline__ float rcp_fast(float x) {
   return r;
 }
 
+// 32 consecutive bias values of the tile from shared memory as eight 16-byte reads.  Every lane reads the same address
+// (a broadcast: one wavefront per instruction whatever its width), and the shared-memory port is what the narrow
+// layers run out of (the MMA's operand reads take 61 % of its cycles at N = 64, `profiles/r01_conv64_ncu_full.txt`),
+// so 32 scalar reads per warp and column group cost four times the wavefronts of these.  `s` is 16-byte aligned.
+__device__ __forceinline__ void load_bias32(const float* s, float* b) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float4 t = reinterpret_cast<const float4*>(s)[i];
+    b[4 * i] = t.x; b[4 * i + 1] = t.y; b[4 * i + 2] = t.z; b[4 * i + 3] = t.w;
+  }
+}
+
 // HALO = 1 (small Cin, bf16 path): all weights of the CTA's output channels stay resident in shared
 // memory and the activation patch is loaded with a (TH + 2 dil)-row halo once per (dx, channel chunk);
 // the three dy taps are row-shifted views of that stage (row shifts are multiples of 1024 B, so the
@@ -744,9 +756,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         load_acc<BN, GS, 32>(taddr, c0, nact, r);
         if ((p.dbg & 64) || ((p.dbg & 128) && (warp & 3) == 1)) continue;   // bring-up experiments: accumulator reads only (all warps / the warp sharing the MMA issuer's scheduler)
         float v[32];
+        load_bias32(s_bias + c0, v);
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          v[i] = r[i] + s_bias[c0 + i];
+          v[i] += r[i];
           if (p.relu) v[i] = fmaxf(v[i], 0.f);
         }
         // Staging-buffer waits are taken by EVERY thread (also those of out-of-image rows, which write nothing): a
@@ -843,6 +856,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         float r[32];
         load_acc<BN, GS, 32>(taddr, c0, nact, r);
         float v[32];
+        load_bias32(s_bias + c0, v);
         uint32_t codes[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) codes[i] = 0;
@@ -850,7 +864,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int i = 0; i < 32; ++i) {
           // floor-mode pooling only writes windows that lie fully inside the image, so the
           // garbage computed for out-of-image tile pixels never reaches a written window.
-          float a = fmaxf(r[i] + s_bias[c0 + i], 0.f);
+          float a = fmaxf(r[i] + v[i], 0.f);
           if (NSPLIT == 1) a = bf16_round(a);  // ties are decided on the stored precision
           float mx = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, 1));
           mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, p.TW));
@@ -877,9 +891,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         float r[32];
         load_acc<BN, GS, 32>(taddr, c0, nact, r);
         float v[32];
+        load_bias32(s_bias + c0, v);
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          v[i] = fmaxf(r[i] + s_bias[c0 + i], 0.f);
+          v[i] = fmaxf(r[i] + v[i], 0.f);
           dot = fmaf(v[i], __ldg(p.head_w + c0 + i), dot);
         }
         if (valid && obase) store_bf16_planes<NSPLIT, 32>(obase + c0, p.out_plane, v);
