@@ -388,7 +388,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   // 1-2 % faster per 64-wide kernel, 12 % slower at 128 wide, nothing on the whole step: these layers are bound by the
   // MMA reading its operands from shared memory, not by L2->SM traffic)
   const int halo1_env = env_int("CAN_B200_HALO1", 0);
-  p.halo1 = halo && (halo1_env == 2 || (halo1_env == 1 && bn == 64));
+  p.halo1 = halo && a->mode != CAN_MODE_UNPOOL && (halo1_env == 2 || (halo1_env == 1 && bn == 64));
   if (p.halo1) p.TW = 8;
   p.TH = 128 / p.TW;
   p.tiles_x = (a->W + p.TW - 1) / p.TW;

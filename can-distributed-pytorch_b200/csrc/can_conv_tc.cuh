@@ -249,6 +249,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint8_t* wbase = s_mask + p.mask_bufs * (BN * 256);               // HALO: resident weights
   uint8_t* ring = HALO ? wbase + p.w_bytes : wbase;                // stage ring
   const int stage_bytes = HALO ? p.halo_stride : L::kStageBytes;
+  // single-halo-tile variant: not compiled into the max-unpool kernels (their epilogue sits on the register limit)
+  const bool halo1 = HALO && MODE != MODE_UNPOOL && p.halo1;
   uint8_t* tail = ring + stages * stage_bytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
   uint64_t* empty_bar = full_bar + 8;
@@ -359,11 +361,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           CAN_TILE_DECODE(tile)
           (void)n0;
           for (int chunk = 0; chunk < p.kchunks; ++chunk) {
-            for (int dxi = p.halo1 ? 2 : 0; dxi < 3; ++dxi) {   // halo1: a single tile, x halo included
+            for (int dxi = halo1 ? 2 : 0; dxi < 3; ++dxi) {   // halo1: a single tile, x halo included
               mbar_wait(&empty_bar[stage], phase ^ 1);
               mbar_expect_tx(&full_bar[stage], static_cast<uint32_t>(p.halo_bytes));
               tma_load_5d(ring + stage * stage_bytes, &tmW, &full_bar[stage], chunk * 64,
-                          x0 + (p.halo1 ? -p.dil : (dxi - 1) * p.dil), y0 - p.dil, n_img, 0);
+                          x0 + (halo1 ? -p.dil : (dxi - 1) * p.dil), y0 - p.dil, n_img, 0);
               if (++stage == stages) {
                 stage = 0;
                 phase ^= 1;
@@ -430,7 +432,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint32_t dy_bytes = static_cast<uint32_t>(p.dil * p.TW * 128);
           const uint32_t tap_row_units = static_cast<uint32_t>((3 * p.kchunks * L::kBBytes) >> 4);  // dy -> dy+1
           uint32_t accum = 0;
-          if (p.halo1) {
+          if (halo1) {
             // One (TH + 2 dil) x (TW + 2 dil) halo tile per channel chunk, TW = 8: the 8-row groups of A are the patch
             // rows, one halo pitch apart (SBO = pitch), and tap (dy, dx) starts (dy * pitch + dx) * dil pixels into
             // the tile.  Neither is a multiple of the 1024-byte swizzle pattern: the MMA applies the 128B swizzle to
@@ -860,6 +862,45 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint32_t codes[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) codes[i] = 0;
+        if constexpr (NSPLIT == 1) {
+          // bf16 path: warp shuffles go through the shared-memory port these layers are bound by, so the window
+          // maximum is taken on channel PAIRS (the values are compared at their stored precision anyway) and the
+          // argmax comes from one 32-bit "I hold the maximum" word per lane: 35 shuffles per 32 channels, not 128
+          // (measured against the per-channel exchange below: 64->64 271 -> 245 us, 128->128 277 -> 265 us, 256->256 171 -> 167 us).
+          uint32_t pk[16], eq = 0;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            // (sign bits cleared: a -0 from the ReLU would compare unequal to +0 bitwise below)
+            const uint32_t mine = pack_bf16x2(fmaxf(r[2 * i] + v[2 * i], 0.f), fmaxf(r[2 * i + 1] + v[2 * i + 1], 0.f)) & 0x7fff7fffu;
+            uint32_t m = bf16x2_max(mine, __shfl_xor_sync(0xffffffffu, mine, 1));
+            m = bf16x2_max(m, __shfl_xor_sync(0xffffffffu, m, p.TW));
+            const uint32_t x = mine ^ m;   // the maximum is one of the four bit patterns: equal value <=> equal bits
+            eq |= ((x & 0xffffu) == 0u ? 1u : 0u) << (2 * i);
+            eq |= ((x >> 16) == 0u ? 1u : 0u) << (2 * i + 1);
+            pk[i] = m;
+          }
+          // eq words of the window in scan order (this lane is position `pos`; the writer is position 0)
+          const uint32_t e1 = __shfl_xor_sync(0xffffffffu, eq, 1), e2 = __shfl_xor_sync(0xffffffffu, eq, p.TW),
+                         e3 = __shfl_xor_sync(0xffffffffu, eq, p.TW | 1);
+          if (writer) {
+            // first position holding the maximum, for 32 channels at once: bit planes of the 2-bit code ...
+            const uint32_t c1 = e1 & ~eq, c2 = e2 & ~(eq | e1), c3 = e3 & ~(eq | e1 | e2);
+            const uint32_t lo = c1 | c3, hi = c2 | c3;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {   // ... spread to one byte per channel (bit k of a nibble -> bit 8 k)
+              const uint32_t nl = (lo >> (4 * j)) & 0xFu, nh = (hi >> (4 * j)) & 0xFu;
+              codes[j] = ((nl * 0x00204081u) & 0x01010101u) | (((nh * 0x00204081u) & 0x01010101u) << 1);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              *reinterpret_cast<uint4*>(obase + c0 + 8 * i) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+            if (abase) {
+              *reinterpret_cast<uint4*>(abase + c0) = make_uint4(codes[0], codes[1], codes[2], codes[3]);
+              *reinterpret_cast<uint4*>(abase + c0 + 16) = make_uint4(codes[4], codes[5], codes[6], codes[7]);
+            }
+          }
+          continue;
+        }
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           // floor-mode pooling only writes windows that lie fully inside the image, so the
