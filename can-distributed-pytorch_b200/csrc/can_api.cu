@@ -555,12 +555,27 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
       g_tmO = &tmO;
       p.out_stage_bytes = 65536;
     }
+    if (a->mode == CAN_MODE_CTX2 && a->out_cs % 8 == 0 && a->out_coff % 8 == 0 && env_int("CAN_B200_TMASTORE", 1) != 0 &&
+        env_int("CAN_B200_CTX2STAGE", 1) != 0) {
+      // the tile's 64 fused channels leave through one TMA store of a swizzled [pixel][64 ch] staging tile (16 KB, fits
+      // beside the four operand stages) instead of per-lane 32-byte stores
+      const uint64_t cs = static_cast<uint64_t>(a->out_cs) * 2;
+      const uint64_t dimsF[4] = {512, static_cast<uint64_t>(a->W), static_cast<uint64_t>(a->H), static_cast<uint64_t>(a->N)};
+      const uint64_t strF[3] = {cs, cs * a->W, cs * a->W * a->H};
+      const uint32_t boxF[4] = {64, static_cast<uint32_t>(p.TW), static_cast<uint32_t>(p.TH), 1};
+      rc = make_tmap(&tmO, static_cast<__nv_bfloat16*>(a->out) + a->out_coff, 4, dimsF, strF, boxF);
+      if (rc) return rc;
+      g_tmO = &tmO;
+      p.out_bufs = 1;
+      p.out_stage_bytes = 16384;
+    }
     g_tmW = &tmW;
     g_tmT = &tmT;
     rc = a->mode == CAN_MODE_CTX2 ? launch_conv<256, 1, MODE_CTX2>(tmA, tmB, p, grid, so, st)
                                   : launch_conv<256, 1, MODE_CTX2_BWD>(tmA, tmB, p, grid, so, st);
     g_tmW = nullptr;
     g_tmT = nullptr;
+    g_tmO = nullptr;
     return rc;
   }
   if (ctx) {

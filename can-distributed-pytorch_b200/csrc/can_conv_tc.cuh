@@ -571,6 +571,20 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       bulk_wait_group_read0();
       if (R > 0) mbar_arrive(&out_free_bar[(R - 1) & 1]);
+    } else if (MODE == MODE_CTX2 && out_lane) {
+      // one 64-channel tile of the fused features per GEMM tile
+      const int nb = p.out_bufs;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        CAN_TILE_DECODE(tile)
+        (void)n0;
+        const int b = it % nb;
+        mbar_wait(&out_full_bar[b], static_cast<uint32_t>(it / nb) & 1u);
+        tma_store_4d(&tmO, s_out + b * 16384, n_tile * 64, x0, y0, n_img);
+        bulk_commit_group();
+        bulk_wait_group_read0();
+        mbar_arrive(&out_free_bar[b]);
+      }
     } else if (MODE == MODE_STORE && BN == 256 && out_lane) {
       // BN = 256: four 64-channel blocks per tile, two 16 KB staging tiles (round = block)
       int R = 0;
@@ -737,7 +751,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     mbar_wait(&tmem_full_bar[as], aphase);
     tc_fence_after();
 
-    const bool kStaged = (MODE == MODE_STORE) && NSPLIT == 1 && BN <= 128 && p.out_stage_bytes > 0;
+    const bool kStaged = ((MODE == MODE_STORE && BN <= 128) || MODE == MODE_CTX2) && NSPLIT == 1 && p.out_stage_bytes > 0;
     const bool kBlockStaged = (MODE == MODE_STORE) && NSPLIT == 1 && BN == 256 && EW == 4 && p.out_stage_bytes > 0;
     const int ob_i = kStaged ? it % p.out_bufs : 0;     // staging buffer of this tile
     bool out_buf_ready = false;                         // (waited for as late as possible: just before the first write)
@@ -1163,7 +1177,23 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
           fi[c] = num * rcp_fast(den + 1e-12f);
         }
-        if (valid) store_bf16_planes<NSPLIT, 16>(obase + c0, p.out_plane, fi);
+        if (kStaged) {
+          // two 16-byte chunks into the 128B-swizzled [pixel][64 ch] staging tile; the waits are taken by every thread
+          if (!out_buf_ready) {
+            mbar_wait(&out_free_bar[ob_i], (static_cast<uint32_t>(it / p.out_bufs) & 1u) ^ 1u);
+            out_buf_ready = true;
+          }
+          if (valid) {
+            uint8_t* row = s_out + ob_i * 16384 + m * 128;
+#pragma unroll
+            for (int i = 0; i < 16; i += 8)
+              *reinterpret_cast<uint4*>(row + ((((c0 + i) >> 3) ^ (m & 7)) << 4)) =
+                  make_uint4(pack_bf16x2(fi[i], fi[i + 1]), pack_bf16x2(fi[i + 2], fi[i + 3]), pack_bf16x2(fi[i + 4], fi[i + 5]),
+                             pack_bf16x2(fi[i + 6], fi[i + 7]));
+          }
+        } else if (valid) {
+          store_bf16_planes<NSPLIT, 16>(obase + c0, p.out_plane, fi);
+        }
       }
     } else if (MODE == MODE_CTX2_BWD && NSPLIT == 1 && EW == 8 && p.out_stage_bytes > 0) {
       // Staged variant of the branch below: four rounds per tile, round s covers channels 16 s .. 16 s + 15 of

@@ -213,6 +213,14 @@ def test_forward_matches_reference_golden(dev, golden, name, precision):
     assert harness.rel_count(out.cpu(), ref) < tol["count"]
 
 
+def test_ctx2_direct_store_variant_matches_reference(dev, golden, monkeypatch):
+    """CAN_B200_CTX2STAGE=0: the contextual-module GEMM writes its fused features with per-lane stores instead of the
+    staged TMA store; same golden outputs."""
+    monkeypatch.setenv("CAN_B200_CTX2STAGE", "0")
+    for name in [n for n in CASES if CASES[n][0] != "ref"]:   # ("ref" is skipped for bf16, see above)
+        test_forward_matches_reference_golden(dev, golden, name, "bf16")
+
+
 def test_fv_and_fi_match_reference(dev, golden):
     from can_b200 import engine
     name = "he_1x64x96"
