@@ -93,3 +93,59 @@ def test_buckets_must_tile_the_arena():
         GradBuckets(a, {"x": (0, 4), "y": (5, 10)})
     with pytest.raises(AssertionError):
         GradBuckets(a, {"x": (0, 4), "y": (4, 9)})
+
+
+# ---------------------------------------------------------------- init_distributed_mode (distributed_utils.py:7-28)
+def _init_worker(rank, world, port, q):
+    import argparse
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    os.environ.pop("SLURM_PROCID", None)
+    from can_b200.utils import distributed_utils as du
+    args = argparse.Namespace(world_size=99, dist_url="env://")   # the launcher's WORLD_SIZE wins over the CLI default
+    du.init_distributed_mode(args)
+    ok = (args.distributed and args.rank == rank and args.world_size == world and args.gpu == rank and
+          args.dist_backend == ("nccl" if torch.cuda.is_available() else "gloo") and
+          du.is_dist_avail_and_initialized() and du.get_rank() == rank and du.get_world_size() == world)
+    v = torch.tensor([float(10 * (rank + 1))])
+    ok = ok and float(du.reduce_value(v, average=True)) == 15.0 and float(v) == 15.0   # in place, like the reference
+    du.cleanup()
+    ok = ok and not du.is_dist_avail_and_initialized() and du.get_world_size() == 1 and du.get_rank() == 0
+    q.put((rank, bool(ok)))
+
+
+def test_init_distributed_mode_under_a_launcher_environment():
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_init_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=300) for _ in range(world))
+    for p in procs:
+        p.join(timeout=300)
+        assert p.exitcode == 0
+    assert got == {0: True, 1: True}
+
+
+def test_init_distributed_mode_without_a_launcher(monkeypatch, capsys):
+    import argparse
+    from can_b200.utils import distributed_utils as du
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "SLURM_PROCID"):
+        monkeypatch.delenv(k, raising=False)
+    args = argparse.Namespace(world_size=4, dist_url="env://")
+    du.init_distributed_mode(args)
+    assert args.distributed is False and "Not using distributed mode" in capsys.readouterr().out
+    assert du.get_world_size() == 1 and du.get_rank() == 0 and du.is_main_process()
+    t = torch.tensor([3.0])
+    assert du.reduce_value(t) is t and float(t) == 3.0
+
+
+def test_slurm_placement_keeps_the_command_line_world_size(monkeypatch):
+    import argparse
+    from can_b200.utils import distributed_utils as du
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        monkeypatch.delenv(k, raising=False)
+    monkeypatch.setenv("SLURM_PROCID", "5")
+    rank, world, local = du._placement(argparse.Namespace(world_size=8))
+    assert (rank, world) == (5, 8) and local == 5 % max(torch.cuda.device_count(), 1)
