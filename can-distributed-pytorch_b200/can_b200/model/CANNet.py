@@ -18,6 +18,7 @@ import torch
 import torch.nn as nn
 
 from .. import engine, ops
+from ..utils.graph_cache import GraphCache
 
 FRONTEND_FEAT = [64, 64, "M", 128, 128, "M", 256, 256, 256, "M", 512, 512, 512]
 BACKEND_FEAT = [512, 512, 512, 256, 128, 64]
@@ -134,17 +135,17 @@ class CANNet(nn.Module):
 
     def _forward_no_grad(self, x, params):
         """Inference calls of a fixed shape replay a CUDA graph of the forward pass after two eager calls (23 launches,
-        ~0.5 ms of host time per call).  The graph is dropped as soon as any parameter changes (version counter, storage,
-        or an in-place arena update announced through the weight cache)."""
+        ~0.5 ms of host time per call).  Graphs are dropped as soon as any parameter changes (version counter, storage,
+        or an in-place arena update announced through the weight cache); `GraphCache` bounds how many shapes keep one."""
         sig = (self._wcache.epoch, self.nsplit) + tuple((p.data_ptr(), p._version) for p in params)
         key = tuple(x.shape)
-        graphs = self.__dict__.setdefault("_infer_graphs", {})
-        ent = graphs.get(key)
-        if ent is None or ent[0] != sig:
-            ent = graphs[key] = [sig, 0, None, None, None, 0]   # signature, eager calls, graph, static x, static out, kernels
-        if ent[2] is None:
-            if ent[1] < 2 or torch.cuda.is_current_stream_capturing():
-                ent[1] += 1
+        cache = self.__dict__.get("_infer_graphs")
+        if cache is None:
+            cache = self.__dict__["_infer_graphs"] = GraphCache()
+        ent = cache.lookup(key, sig)
+        if ent is None:
+            # (two eager calls of the same shape in a row first; a stream of changing image sizes never captures)
+            if not cache.should_capture() or torch.cuda.is_current_stream_capturing():
                 return engine.forward(self, x, self.nsplit, save=False)[0]
             try:
                 xs = x.clone()
@@ -153,14 +154,15 @@ class CANNet(nn.Module):
                 launches0 = ops.LAUNCHES
                 with torch.cuda.graph(graph):
                     out = engine.forward(self, xs, self.nsplit, save=False)[0]
-                ent[2:] = [graph, xs, out, ops.LAUNCHES - launches0]
+                ent = [graph, xs, out, ops.LAUNCHES - launches0]
+                cache.insert(key, ent)
             except Exception as exc:  # noqa: BLE001 -- the graph is an optimisation only
                 import sys
                 print(f"can_b200: CUDA graph capture of the forward pass failed ({exc}); staying eager", file=sys.stderr)
                 os.environ["CAN_B200_GRAPH_INFER"] = "0"
                 torch.cuda.synchronize()
                 return engine.forward(self, x, self.nsplit, save=False)[0]
-        _, _, graph, xs, out, nk = ent
+        graph, xs, out, nk = ent
         xs.copy_(x, non_blocking=True)
         graph.replay()
         ops.LAUNCHES += nk    # kernels of one forward pass (what the replay launches)

@@ -18,6 +18,7 @@ import torch
 import torch.distributed as dist
 
 from .. import engine, ops
+from .graph_cache import GraphCache
 from .distributed_utils import get_world_size, is_dist_avail_and_initialized, is_main_process, reduce_value
 from .dp import GradBuckets
 
@@ -71,17 +72,16 @@ class FusedTrainer:
         # and the bucketed all-reduces are issued eagerly between the replays.
         self.use_graph = os.environ.get("CAN_B200_GRAPH", "1") != "0" and (
             self.world == 1 or (dist.get_backend(self.pg) == "nccl" and os.environ.get("CAN_B200_GRAPH_DP", "1") != "0"))
-        self._graphs = {}       # (img shape, gt shape) -> [eager steps seen, graph(s), static img, static gt, static loss]
+        self._graphs = GraphCache()   # (img shape, gt shape) -> [graph(s), static img, static gt, static loss]
 
     def step(self, img: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
         """One training step; returns the rank-mean of the local sum-losses as a device tensor [1]."""
         if not self.use_graph or img.dtype != torch.float32 or gt.dtype != torch.float32:
             return self._step_eager(img, gt)
         key = (tuple(img.shape), tuple(gt.shape))
-        ent = self._graphs.setdefault(key, [0, None, None, None, None])
-        if ent[1] is None:
-            if ent[0] < 2 or self.first:
-                ent[0] += 1
+        ent = self._graphs.lookup(key)
+        if ent is None:
+            if not self._graphs.should_capture() or self.first:
                 return self._step_eager(img, gt)
             try:
                 xs, gs = img.clone(), gt.clone()
@@ -92,13 +92,14 @@ class FusedTrainer:
                         loss = self._step_eager(xs, gs)
                 else:
                     graph, loss = self._capture_dp(xs, gs)
-                ent[1:] = [graph, xs, gs, loss]
+                ent = [graph, xs, gs, loss]
+                self._graphs.insert(key, ent)
             except Exception as exc:  # noqa: BLE001 -- capture is an optimisation; eager stays correct
                 print(f"can_b200: CUDA graph capture of the training step failed ({exc}); staying eager", file=sys.stderr)
                 self.use_graph = False
                 torch.cuda.synchronize()
                 return self._step_eager(img, gt)
-        _, graph, xs, gs, loss = ent
+        graph, xs, gs, loss = ent
         xs.copy_(img, non_blocking=True)
         gs.copy_(gt, non_blocking=True)
         if self.world == 1:
