@@ -252,6 +252,7 @@ def sgd_momentum_step(p, g, buf, lr, momentum=0.95, grad_scale=1.0, first=False)
 
 # ------------------------------------------------------------------------------ backward
 _wgrad_ws = {}
+_wgrad_ws_retired = []
 
 
 def conv_wgrad(dz: Act, x: Act, grad: torch.Tensor, *, taps=9, dil=1, accumulate=False, alpha=1.0):
@@ -261,6 +262,8 @@ def conv_wgrad(dz: Act, x: Act, grad: torch.Tensor, *, taps=9, dil=1, accumulate
     dev = dz.buf.device
     ws = _wgrad_ws.get(dev)
     if ws is None or ws.numel() < need:
+        if ws is not None:
+            _wgrad_ws_retired.append(ws)   # a captured step of a smaller shape may still replay into it: never freed
         ws = torch.empty(max(need, 64 << 20), device=dev, dtype=torch.uint8)
         _wgrad_ws[dev] = ws
     assert grad.is_contiguous() and grad.dtype == torch.float32 and grad.numel() == dz.C * x.C * taps
