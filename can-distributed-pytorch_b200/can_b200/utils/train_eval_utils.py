@@ -267,9 +267,12 @@ class DevicePrefetcher:
             cur.wait_event(self._copied[slot])
             for t in dev:
                 t.record_stream(cur)
-            yield dev
-            # the consumer has enqueued its step: the slot may be overwritten once that work is done
-            if self._freed[slot] is None:
-                self._freed[slot] = torch.cuda.Event()
-            self._freed[slot].record(torch.cuda.current_stream(self.device))
+            try:
+                yield dev
+            finally:
+                # the consumer has enqueued its step (or left the loop early): the slot may be overwritten once the
+                # work enqueued so far is done
+                if self._freed[slot] is None:
+                    self._freed[slot] = torch.cuda.Event()
+                self._freed[slot].record(torch.cuda.current_stream(self.device))
             slot ^= 1
