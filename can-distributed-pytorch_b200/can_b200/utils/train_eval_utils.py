@@ -190,7 +190,7 @@ def train_one_epoch(model, optimizer, train_loader, device, epoch):
     if not torch.isfinite(mean_loss).all():  # checked once per epoch instead of a host sync per step
         print("WARNING: non-finite loss, ending training ", mean_loss)
         sys.exit(1)
-    if device != torch.device("cpu"):
+    if torch.device(device).type == "cuda":   # (`device` may be a string, as in the reference's CLI)
         torch.cuda.synchronize(device)
     return mean_loss.item()
 
@@ -209,7 +209,7 @@ def evaluate(model, test_loader, device, epoch=0, show_images=False, use_wandb=F
         et = model(img)
         _, ce, cg, _ = ops.mse_count(et, gt_dmap, want_grad=False)
         mae += (ce.sum() - cg.sum()).abs()
-    if device != torch.device("cpu"):
+    if torch.device(device).type == "cuda":   # (`device` may be a string, as in the reference's CLI)
         torch.cuda.synchronize(device)
     mae = reduce_value(mae, average=False)
     return mae.item()
