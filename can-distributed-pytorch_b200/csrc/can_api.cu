@@ -67,20 +67,6 @@ int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, 
   return 0;
 }
 
-// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
-// memory hung the GPU: the cluster variant is taken only when the weight buffer is plain device memory of the
-// current device (anything else -- peer, managed, host-mapped, unknown -- gets the per-CTA loads).
-bool weights_on_current_device(const void* ptr) {
-  int dev = -1;
-  cudaPointerAttributes at;
-  if (cudaGetDevice(&dev) != cudaSuccess) return false;
-  if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) {
-    cudaGetLastError();
-    return false;
-  }
-  return at.type == cudaMemoryTypeDevice && at.device == dev;
-}
-
 int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
   return v ? atoi(v) : dflt;
@@ -118,25 +104,6 @@ int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p,
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tc)");
     attr_done = true;
     attr_smem = kMaxSmem;
-  }
-  if (p.cluster) {
-    // clusters of two CTAs (weight tiles shared through TMA multicast): extended launch with the cluster dimension
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = grid;
-    cfg.blockDim = dim3(128 + 32 * EW);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = p.cluster;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA,
-                                       g_tmO ? *g_tmO : tmA, g_tmM ? *g_tmM : tmA, p);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(conv_tc, cluster 2)");
-    return 0;
   }
   kern<<<grid, 128 + 32 * EW, smem, st>>>(tmA, tmB, g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA, g_tmO ? *g_tmO : tmA,
                                          g_tmM ? *g_tmM : tmA, p);
@@ -601,29 +568,6 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
            : ns == 2 ? dispatch_mode<128, 2>(a->mode, tmA, tmB, p, grid, so, st)
                      : dispatch_mode<128, 3>(a->mode, tmA, tmB, p, grid, so, st);
   if (ns == 3) return fail(-13, "conv_tc: bn=256 does not fit with 3 planes");
-  // widest tiles, bf16 path: the kernel is bound by L2 -> SM operand traffic (2/3 of it weights); pairs of CTAs
-  // working on the same n-tile fetch each weight tile once and multicast it
-  CUtensorMap tmBh;
-  if (ns == 1 && a->mode == CAN_MODE_STORE && !p.out_stage_bytes && !p.mask_bufs && ctas >= 2 &&
-      env_int("CAN_B200_CLUSTER", 0) != 0 && weights_on_current_device(a->w)) {
-    const uint64_t K = static_cast<uint64_t>(a->taps) * a->Cin;
-    const uint64_t dimsB[3] = {K, static_cast<uint64_t>(a->Cout), 1};
-    const uint64_t strB[2] = {K * 2, K * 2 * a->Cout};
-    const int cs = env_int("CAN_B200_CLUSTER", 0) == 4 && ctas >= 4 ? 4 : 2;
-    const uint32_t boxB[3] = {64, static_cast<uint32_t>(256 / cs), 1};
-    int rc = make_tmap(&tmBh, a->w, 3, dimsB, strB, boxB);
-    if (rc) return rc;
-    g_tmT = &tmBh;
-    p.cluster = cs;
-    p.pix_tiles = p.tiles_x * p.tiles_y * a->N;
-    p.num_pair_tiles = ((p.pix_tiles + cs - 1) / cs) * p.n_tiles;
-    int pairs = ctas / cs;
-    if (pairs > p.num_pair_tiles) pairs = p.num_pair_tiles;
-    grid = dim3(cs * pairs);
-    rc = dispatch_mode<256, 1>(a->mode, tmA, tmB, p, grid, so, st);
-    g_tmT = nullptr;
-    return rc;
-  }
   return ns == 1 ? dispatch_mode<256, 1>(a->mode, tmA, tmB, p, grid, so, st)
                  : dispatch_mode<256, 2>(a->mode, tmA, tmB, p, grid, so, st);
 }

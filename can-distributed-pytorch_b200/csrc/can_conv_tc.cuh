@@ -49,9 +49,6 @@ struct ConvTcParams {
   int halo_stride;     // HALO: distance between stages (halo_bytes rounded up to 1024)
   int halo1;           // HALO: one halo tile per (pixel tile, channel chunk) serves all nine taps
   int out_stage_bytes; // > 0: the epilogue stages the bf16 tile in shared memory (BN * 256 B) and writes it with TMA (tmO)
-  int cluster;         // 0, or the cluster size (2 | 4): CTAs of a cluster share every weight tile through TMA multicast (tmT = 1/size-tile map)
-  int pix_tiles;       // tiles_x * tiles_y * N
-  int num_pair_tiles;  // cluster mode: ceil(pix_tiles / size) * n_tiles work items per cluster
   int out_bufs;        // MODE_STORE staged epilogue: 1 or 2 staging buffers of BN * 256 B (out_stage_bytes = their sum)
   int mask_bufs;       // staged epilogue: 0 = mask read from global memory, 1|2 = mask tiles (BN * 256 B each) brought in by TMA (tmM)
   int relu;
@@ -272,25 +269,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   constexpr int ACC_COLS = AccLayout<BN, GS>::cols(MODE);
   constexpr int ACC_STAGES = AccLayout<BN, GS>::acc_stages(MODE);
   const int base_kb = p.taps * p.kchunks;
-  // Work items.  Plain: CTA b takes tiles b, b + grid, ...  Cluster mode: the two CTAs of a pair walk the same list of
-  // (pixel-tile pair, n-tile) items in lockstep, rank r taking pixel tile 2*pair + r, so both need the same weight tile
-  // at the same time (a missing odd partner recomputes the last pixel tile and drops the result).
-  const bool cl = p.cluster != 0;
-  const int cta_rank = cl ? static_cast<int>(cluster_ctarank()) : 0;
-  const int csz = cl ? p.cluster : 1;
-  const uint16_t cmask = static_cast<uint16_t>((1u << csz) - 1u);
-  const int T0 = static_cast<int>(blockIdx.x) / csz;
-  const int TS = static_cast<int>(gridDim.x) / csz;
-  const int TN = cl ? p.num_pair_tiles : p.num_tiles;
-  auto tile_of = [&](int q, bool& live) {
-    live = true;
-    if (!cl) return q;
-    const int nt = q % p.n_tiles;
-    int pix = csz * (q / p.n_tiles) + cta_rank;
-    live = pix < p.pix_tiles;
-    pix = min(pix, p.pix_tiles - 1);
-    return pix * p.n_tiles + nt;
-  };
   // MODE_CTX2: two extra k-blocks whose A operand is the interpolation matrix Wint[pixel][64 positions]
   // and whose B operands are the per-image tables (-U-side of z, then s) -- see the epilogue.
   constexpr bool kCtx2 = (MODE == MODE_CTX2 || MODE == MODE_CTX2_BWD);
@@ -321,7 +299,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (lane == 0) {
       for (int s = 0; s < stages; ++s) {
         mbar_init(&full_bar[s], 1);
-        mbar_init(&empty_bar[s], p.cluster ? p.cluster : 1);   // cluster mode: the MMAs of every CTA release a stage
+        mbar_init(&empty_bar[s], 1);
       }
       for (int a = 0; a < 4; ++a) {
         mbar_init(&tmem_full_bar[a], 1);
@@ -345,7 +323,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if (cl) cluster_sync_all();   // the partner's barriers exist before anything is multicast to them
   const uint32_t tmem_base = *tmem_ptr_smem;
 
   if (warp == 0) {
@@ -374,9 +351,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
       } else
-      for (int q_ = T0; q_ < TN; q_ += TS) {
-        bool live_;
-        const int tile = tile_of(q_, live_);
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
         CAN_TILE_DECODE(tile)
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -397,11 +372,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
             for (int pl = 0; pl < GS; ++pl) {
               tma_load_5d(sa + pl * L::kABytes, &tmA, &full_bar[stage], chunk * 64, x0 + dx, y0 + dy, n_img, pl);
-              if (cl)   // my share of the weight tile, delivered to every CTA of the cluster (tmT: box of BN / size rows)
-                tma_load_3d_multicast(sb + pl * L::kBBytes + cta_rank * (L::kBBytes / csz), &tmT, &full_bar[stage], kb * 64,
-                                      n0 + cta_rank * (BN / csz), pl, cmask);
-              else
-                tma_load_3d(sb + pl * L::kBBytes, &tmB, &full_bar[stage], kb * 64, n0, pl);
+              tma_load_3d(sb + pl * L::kBBytes, &tmB, &full_bar[stage], kb * 64, n0, pl);
             }
           }
           if (++stage == stages) {
@@ -419,7 +390,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t phase = 0;
       constexpr int NACC = AccLayout<BN, GS>::kNacc;
       int it = 0;  // tiles processed by this CTA
-      for (int q_ = T0; q_ < TN; q_ += TS, ++it) {
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
         const int as = it % ACC_STAGES;
         const uint32_t aphase = static_cast<uint32_t>(it / ACC_STAGES) & 1u;
         mbar_wait(&tmem_empty_bar[as], aphase ^ 1);  // epilogue drained this accumulator stage
@@ -516,9 +487,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               }
             }
           }
-          // frees the smem slot when these MMAs retire (cluster mode: in both CTAs, whose producers write both slots)
-          if (cl) umma_commit_multicast(&empty_bar[stage], cmask);
-          else umma_commit(&empty_bar[stage]);
+          umma_commit(&empty_bar[stage]);   // frees the smem slot when these MMAs retire
           if (++stage == stages) {
             stage = 0;
             phase ^= 1;
@@ -670,9 +639,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
     for (int i = 0; i < (kDbRegMode ? 32 : 1); ++i) dbacc[i] = 0.f;
     int it = 0;
-    for (int q_ = T0; q_ < TN; q_ += TS, ++it) {
-    bool live_;
-    const int tile = tile_of(q_, live_);
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
     CAN_TILE_DECODE(tile)
     const int as = it % ACC_STAGES;
     const uint32_t aphase = static_cast<uint32_t>(it / ACC_STAGES) & 1u;
@@ -718,7 +685,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (!bias_once || it == 0) asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
 
     const int y = y0 + ty, x = x0 + tx;
-    const bool valid = live_ && (y < p.H) && (x < p.W);
+    const bool valid = (y < p.H) && (x < p.W);
     const uint32_t taddr = tmem_base + as * ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
 
     // Operands of the epilogue that do not depend on the accumulator (ReLU mask / arg-max codes /
@@ -1527,7 +1494,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   tc_fence_before();
   __syncthreads();
-  if (cl) cluster_sync_all();   // neither CTA leaves while the other may still signal its barriers
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, ACC_COLS * ACC_STAGES);
