@@ -234,7 +234,7 @@ def mse_count(et: torch.Tensor, gt: torch.Tensor, want_grad: bool, grad_scale: f
     ce = torch.empty(N, device=dev, dtype=torch.float32)
     cg = torch.empty(N, device=dev, dtype=torch.float32)
     grad = torch.empty_like(et) if want_grad else None
-    key = (dev, N)
+    key = (dev, N, torch.cuda.current_stream(dev).cuda_stream)   # (the kernel's counter must not be shared by two streams)
     if key not in _mse_ws:
         _mse_ws[key] = torch.zeros(lib().can_mse_count_workspace_bytes(N), device=dev, dtype=torch.uint8)
     check(lib().can_mse_count_fwd_bwd(et.data_ptr(), gt.data_ptr(), N, HW, loss.data_ptr(), ce.data_ptr(),
@@ -255,17 +255,24 @@ _wgrad_ws = {}
 _wgrad_ws_retired = []
 
 
+def _wgrad_workspace(dev, need):
+    """Split-K workspace shared by conv_wgrad and ctx_ut (kernels of one stream run in order).  A regrown buffer keeps
+    its predecessor alive: a captured step of a smaller shape may still replay into it."""
+    ws = _wgrad_ws.get(dev)
+    if ws is None or ws.numel() < need:
+        if ws is not None:
+            _wgrad_ws_retired.append(ws)
+        ws = torch.empty(max(need, 64 << 20), device=dev, dtype=torch.uint8)
+        _wgrad_ws[dev] = ws
+    return ws
+
+
 def conv_wgrad(dz: Act, x: Act, grad: torch.Tensor, *, taps=9, dil=1, accumulate=False, alpha=1.0):
     """grad[co][ci][kh][kw] (+)= alpha * sum_pixels dz[pix][co] * x[pix + tap][ci]   (fp32, parameter layout)."""
     N, H, W = dz.N, dz.H, dz.W
     need = lib().can_conv_wgrad_workspace_bytes(N, H, W, x.C, dz.C, taps, dz.nsplit)
     dev = dz.buf.device
-    ws = _wgrad_ws.get(dev)
-    if ws is None or ws.numel() < need:
-        if ws is not None:
-            _wgrad_ws_retired.append(ws)   # a captured step of a smaller shape may still replay into it: never freed
-        ws = torch.empty(max(need, 64 << 20), device=dev, dtype=torch.uint8)
-        _wgrad_ws[dev] = ws
+    ws = _wgrad_workspace(dev, need)
     assert grad.is_contiguous() and grad.dtype == torch.float32 and grad.numel() == dz.C * x.C * taps
     _count(2)
     with _Prof(2.0 * taps * x.C * dz.C * N * H * W, f"wgrad {x.C}->{dz.C} t{taps} d{dil} {H}x{W}"):
@@ -384,10 +391,7 @@ def ctx_ut(wint: Act, x: Act) -> torch.Tensor:
     B, H, W, Cc = x.N, x.H, x.W, x.C
     dev = x.buf.device
     need = lib().can_ctx_ut_workspace_bytes(B, H, W, Cc)
-    ws = _wgrad_ws.get(dev)
-    if ws is None or ws.numel() < need:
-        ws = torch.empty(max(need, 64 << 20), device=dev, dtype=torch.uint8)
-        _wgrad_ws[dev] = ws
+    ws = _wgrad_workspace(dev, need)
     out = torch.empty(64, B, Cc, device=dev, dtype=torch.float32)
     _count(2)
     with _Prof(2.0 * 64 * Cc * B * H * W, f"wgrad ut {Cc}->64 x{B} {H}x{W}"):

@@ -73,9 +73,15 @@ class FusedTrainer:
         self.use_graph = os.environ.get("CAN_B200_GRAPH", "1") != "0" and (
             self.world == 1 or (dist.get_backend(self.pg) == "nccl" and os.environ.get("CAN_B200_GRAPH_DP", "1") != "0"))
         self._graphs = GraphCache()   # (img shape, gt shape) -> [graph(s), static img, static gt, static loss]
+        self._captured_hyper = (self.lr, self.momentum)
 
     def step(self, img: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
-        """One training step; returns the rank-mean of the local sum-losses as a device tensor [1]."""
+        """One training step; returns the rank-mean of the local sum-losses as a device tensor [1] (a fresh tensor every
+        call: it stays valid after later steps).  ``lr`` / ``momentum`` may be changed between steps (a captured step
+        has them baked in as kernel arguments, so a change drops the captured graphs)."""
+        if (self.lr, self.momentum) != self._captured_hyper:
+            self._graphs = GraphCache()
+            self._captured_hyper = (self.lr, self.momentum)
         if not self.use_graph or img.dtype != torch.float32 or gt.dtype != torch.float32:
             return self._step_eager(img, gt)
         key = (tuple(img.shape), tuple(gt.shape))
@@ -104,6 +110,7 @@ class FusedTrainer:
         gs.copy_(gt, non_blocking=True)
         if self.world == 1:
             graph.replay()
+            loss = loss.clone()   # the static tensor is rewritten by the next replay
         else:
             for g, tag in zip(graph[:3], ("backend", "ctx", "frontend")):
                 g.replay()
@@ -174,9 +181,26 @@ def train_one_epoch(model, optimizer, train_loader, device, epoch):
     fused = isinstance(optimizer, FusedTrainer)
     # the next batch's host->device copies run on a side stream while this step computes (pinned loaders overlap fully)
     batches = DevicePrefetcher(train_loader, device) if torch.device(device).type == "cuda" else train_loader
+    # Non-finite guard (train_eval_utils.py:48-50): the reference reads the loss back on every rank before
+    # optimizer.step, a host sync per step.  Here step k's finite flag is copied to pinned host memory asynchronously and
+    # looked at while step k+1 is being enqueued, so a diverged run stops one step late instead of one epoch late and no
+    # step waits for the device.  (The late step's update is applied; the reference's exit leaves no usable state either.)
+    on_cuda = torch.device(device).type == "cuda"
+    flags = [None, None]   # (pinned bool [1], event) of the two steps in flight
+
+    def check_late(slot):
+        ent = flags[slot]
+        if ent is not None:
+            ent[1].synchronize()
+            if not bool(ent[0][0]):
+                print("WARNING: non-finite loss, ending training ", mean_loss)
+                sys.exit(1)
+
     for step, (img, gt_dmap) in enumerate(batches):
         img = img.to(device, non_blocking=True)
         gt_dmap = gt_dmap.to(device, non_blocking=True)
+        if on_cuda:
+            check_late((step + 1) & 1)   # the flag of step - 1 (its kernels finished while this batch was fetched)
         if fused:
             loss = optimizer.step(img, gt_dmap)
         else:
@@ -187,7 +211,15 @@ def train_one_epoch(model, optimizer, train_loader, device, epoch):
             loss = reduce_value(loss.detach().reshape(1), average=True)
             optimizer.step()
         mean_loss = (mean_loss * step + loss.detach()) / (step + 1)
-    if not torch.isfinite(mean_loss).all():  # checked once per epoch instead of a host sync per step
+        if on_cuda:
+            ent = flags[step & 1]
+            if ent is None:
+                ent = flags[step & 1] = (torch.empty(1, dtype=torch.bool).pin_memory(), torch.cuda.Event())
+            ent[0].copy_(torch.isfinite(loss.detach()).reshape(-1)[:1], non_blocking=True)
+            ent[1].record()
+        if is_main_process() and hasattr(train_loader, "desc"):
+            train_loader.desc = "[epoch {}]".format(epoch)   # (the running mean stays on the device: no per-step read-back)
+    if not torch.isfinite(mean_loss).all():  # covers the last step (and CPU runs)
         print("WARNING: non-finite loss, ending training ", mean_loss)
         sys.exit(1)
     if torch.device(device).type == "cuda":   # (`device` may be a string, as in the reference's CLI)
@@ -221,8 +253,9 @@ class DevicePrefetcher:
 
     ``for img, gt in DevicePrefetcher(loader, device): ...`` yields device tensors whose copies have
     completed with respect to the current stream.  The copies land in two resident sets of device buffers
-    used in turn (re-made only when a batch changes shape), so the steady state allocates nothing: a
-    yielded batch is valid until the iteration after the next one starts."""
+    used in turn (re-made only when a batch changes shape), so the steady state allocates nothing.  A
+    yielded batch is valid until the NEXT batch is requested (its slot is refilled at the start of the iteration after
+    that, ordered only after the work enqueued before that request): clone what must outlive the loop body."""
 
     _streams: dict = {}   # one copy stream per device for the life of the process
 

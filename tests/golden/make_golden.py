@@ -2,7 +2,8 @@
 
 Run in the build container only (``/root/reference`` does not exist on the GPU box):
 
-    python tests/golden/make_golden.py
+    python tests/golden/make_golden.py          # small cases  -> cannet_golden.npz
+    python tests/golden/make_golden.py --big    # BASELINE.json's own shapes -> cannet_golden_big.npz
 
 The reference is path-loaded (``model/__init__.py`` imports matplotlib, absent here)
 and built with ``CANNet(load_weights=True)`` (the default constructor downloads
@@ -31,6 +32,16 @@ CASES = [
 ]
 
 
+# BASELINE.json configs at their own image sizes (one image each; batches are checked image by image).
+# Stored: the fp64 and fp32 density maps, the loss and the per-parameter gradient summaries -- no features.
+BIG_CASES = [
+    # name, regime, N, H, W, backward?
+    ("he_1x512x512", "he", 1, 512, 512, True),       # configs[2]
+    ("he_1x768x1024", "he", 1, 768, 1024, True),     # configs[1], configs[3]
+    ("he_1x2048x2048", "he", 1, 2048, 2048, False),  # configs[4] (inference only: forward, fp64)
+]
+
+
 def load_reference():
     spec = importlib.util.spec_from_file_location("ref_cannet", "/root/reference/model/CANNet.py")
     mod = importlib.util.module_from_spec(spec)
@@ -41,6 +52,34 @@ def load_reference():
 def summarize(t):
     t = t.detach().double().flatten()
     return np.array([t.sum().item(), t.norm().item(), t.abs().max().item()] + t[:5].tolist())
+
+
+def main_big():
+    torch.set_num_threads(os.cpu_count())
+    ref = load_reference()
+    out = {}
+    for name, regime, n, h, w, bwd in BIG_CASES:
+        sd = harness.make_state_dict(regime, seed=0)
+        x = harness.make_input(n, h, w)
+        gt = harness.make_gt(n, h, w)
+        for dt, tag in ((torch.float64, "f64"), (torch.float32, "f32")):
+            if not bwd and tag == "f32":
+                continue
+            m = ref.CANNet(load_weights=True).to(dt)
+            m.load_state_dict({k: v.to(dt) for k, v in sd.items()}, strict=True)
+            with torch.set_grad_enabled(bwd):
+                et = m(x.to(dt))
+                loss = torch.nn.MSELoss(reduction="sum")(et, gt.to(dt))  # train_eval_utils.py:20,37
+            if bwd:
+                loss.backward()
+            out[f"{name}/{tag}/out"] = et.detach().numpy()
+            out[f"{name}/{tag}/loss"] = np.array(loss.item())
+            if bwd and tag == "f64":
+                for k, p in m.state_dict(keep_vars=True).items():
+                    out[f"{name}/grad/{k}"] = summarize(p.grad)
+            del m, et, loss
+        print(name, "ok", out[f"{name}/f64/out"].shape, float(out[f"{name}/f64/loss"]), flush=True)
+    np.savez_compressed(os.path.join(os.path.dirname(__file__), "cannet_golden_big.npz"), **out)
 
 
 def main():
@@ -76,4 +115,4 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    main_big() if "--big" in sys.argv[1:] else main()

@@ -92,6 +92,25 @@ def test_torch_port_matches_reference(golden, name):
         assert np.allclose(g.flatten()[:5].numpy(), s[3:], rtol=1e-7, atol=1e-12 * max(1.0, s[2])), k
 
 
+def test_torch_port_matches_reference_at_baseline_size():
+    """The port at BASELINE.json configs[2]'s image size (3x512x512) against the live reference's committed fp64 output,
+    loss and gradient summaries (tests/golden/cannet_golden_big.npz); the fp32 self-noise of the reference at all three
+    big sizes stays ~100x below the 1e-4 tolerance."""
+    import os
+    big = np.load(os.path.join(os.path.dirname(__file__), "golden", "cannet_golden_big.npz"))
+    name, h, w = "he_1x512x512", 512, 512
+    sd = harness.make_state_dict("he")
+    loss, out, grads = T.loss_and_grads(harness.make_input(1, h, w), harness.make_gt(1, h, w), sd, dtype=torch.float64)
+    assert harness.rel_l2(out, torch.from_numpy(big[f"{name}/f64/out"])) < 1e-10
+    assert float(loss) == pytest.approx(float(big[f"{name}/f64/loss"]), rel=1e-10)
+    for k, g in grads.items():
+        s = big[f"{name}/grad/{k}"]
+        assert float(g.norm()) == pytest.approx(s[1], rel=1e-8), k
+    for n in ("he_1x512x512", "he_1x768x1024"):
+        assert harness.rel_l2(torch.from_numpy(big[f"{n}/f32/out"]), torch.from_numpy(big[f"{n}/f64/out"])) < 2e-5
+    assert big["he_1x2048x2048/f64/out"].shape == (1, 1, 256, 256)
+
+
 def test_fp32_reference_self_noise(golden):
     # the tolerance budget: reference fp32 vs fp64 (SURVEY.md section 8c)
     for name in CASES:
