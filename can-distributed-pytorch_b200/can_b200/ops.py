@@ -223,14 +223,15 @@ def ctx_pool(fv: Act, w1: torch.Tensor, w2: torch.Tensor):
 _mse_ws = {}
 
 
-def mse_count(et: torch.Tensor, gt: torch.Tensor, want_grad: bool, grad_scale: float = 1.0):
-    """Returns (loss[1], cnt_et[N], cnt_gt[N], grad or None); et/gt are [N,1,h,w] fp32."""
+def mse_count(et: torch.Tensor, gt: torch.Tensor, want_grad: bool, grad_scale: float = 1.0, loss_out: torch.Tensor = None):
+    """Returns (loss[1], cnt_et[N], cnt_gt[N], grad or None); et/gt are [N,1,h,w] fp32.  ``loss_out`` (fp32 [1] on the
+    same device) receives the loss instead of a fresh tensor."""
     N = et.shape[0]
     HW = et[0].numel()
     dev = et.device
     et = et.contiguous()
     gt = gt.contiguous().float()
-    loss = torch.empty(1, device=dev, dtype=torch.float32)
+    loss = loss_out if loss_out is not None else torch.empty(1, device=dev, dtype=torch.float32)
     ce = torch.empty(N, device=dev, dtype=torch.float32)
     cg = torch.empty(N, device=dev, dtype=torch.float32)
     grad = torch.empty_like(et) if want_grad else None

@@ -37,29 +37,40 @@ class FusedTrainer:
         self.world = get_world_size()
         params = list(model.parameters())
         dev = params[0].device
-        total = sum(p.numel() for p in params)
-        self.arena = torch.empty(total, device=dev, dtype=torch.float32)
+        # Arena layout (the state_dict is untouched; only where each parameter's storage lives is chosen here):
+        #   [ header: 64 floats, slot 0 = this rank's loss ][ frontend, parameter order ][ backend + head ]
+        #   [ conv{1,2,3,6}_1 ][ conv{1,2,3,6}_2 ]
+        # every parameter starts on a 256-byte boundary, so the kernels' 16-byte stores can write gradients in place and
+        # the four conv{S}_1 / conv{S}_2 gradients are each one [4,512,512] block (engine._stacked_view).  The header
+        # rides in the last gradient bucket: the loss needs no all-reduce of its own (distributed_utils.py:60-70).
+        HDR, ALIGN = 64, 64
+        order = list(range(engine.IDX_CTX)) + [engine.IDX_CTX + 2 * j for j in range(4)] + \
+                [engine.IDX_CTX + 2 * j + 1 for j in range(4)]
+        offs, off = {}, HDR
+        for i in order:
+            offs[i] = off
+            off += (params[i].numel() + ALIGN - 1) // ALIGN * ALIGN
+        total = off
+        self.arena = torch.zeros(total, device=dev, dtype=torch.float32)
         self.garena = torch.zeros(total, device=dev, dtype=torch.float32)
         self.buf = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.loss_slot = self.garena[0:1]
+        self.hdr = HDR          # the update skips the header
         self.gviews = []
-        self.zero_ranges = []  # bias / head slices that the backward accumulates into
-        off = 0
         with torch.no_grad():
-            for p in params:
+            for i, p in enumerate(params):
                 n = p.numel()
-                view = self.arena[off:off + n].view_as(p)
+                view = self.arena[offs[i]:offs[i] + n].view_as(p)
                 view.copy_(p)
                 p.data = view           # parameters now live in the arena (state_dict unchanged)
-                self.gviews.append(self.garena[off:off + n].view_as(p))
-                if p.dim() == 1 or p.shape[0] == 1:
-                    self.zero_ranges.append((off, off + n))
-                off += n
+                self.gviews.append(self.garena[offs[i]:offs[i] + n].view_as(p))
         self.total = total
-        # buckets in the order backward produces them: backend+head, ctx, frontend
-        n_front = sum(p.numel() for p in params[:engine.IDX_BACKEND])
-        n_back = sum(p.numel() for p in params[engine.IDX_BACKEND:engine.IDX_CTX])
-        self.buckets = GradBuckets(self.garena, {"backend": (n_front, n_front + n_back), "ctx": (n_front + n_back, total),
-                                                 "frontend": (0, n_front)}, group=process_group)
+        # buckets in the order backward produces them: backend+head, ctx, conv4_x, the rest of the frontend
+        # (1.7 M floats + the loss slot: all that is left to exchange when backward ends)
+        o_hi, o_back, o_ctx = offs[2 * 7], offs[engine.IDX_BACKEND], offs[engine.IDX_CTX]
+        self.buckets = GradBuckets(self.garena, {"backend": (o_back, o_ctx), "ctx": (o_ctx, total),
+                                                 "frontend_hi": (o_hi, o_back), "frontend": (0, o_hi)},
+                                   group=process_group)
         self.first = True
         model._wcache.invalidate()
         if self.world > 1:  # identical initial weights on every rank (train.py:104-114 / DDP broadcast)
@@ -112,55 +123,58 @@ class FusedTrainer:
             graph.replay()
             loss = loss.clone()   # the static tensor is rewritten by the next replay
         else:
-            for g, tag in zip(graph[:3], ("backend", "ctx", "frontend")):
+            for g, tag in zip(graph[:-1], self.DP_TAGS):
                 g.replay()
                 self.buckets.ready(tag)
-            self.buckets.reduce_scalar(loss)   # (the static loss tensor; rewritten by the next replay)
             self.buckets.wait()
-            graph[3].replay()
-            loss = loss / self.world
+            loss = self.loss_slot / self.world   # rank-mean of the local sum-losses (came with the last bucket)
+            graph[-1].replay()
         ops.LAUNCHES += self._graph_launches
         self.model._wcache.invalidate()   # the replay updated the arena: packed weights are stale for eager callers
         return loss
 
+    DP_TAGS = ("backend", "ctx", "frontend_hi", "frontend")   # the order engine.backward_steps yields them
+
     def _capture_dp(self, xs, gs):
-        """Four graphs of one data-parallel step (no NCCL inside); nothing executes during capture."""
+        """One graph per gradient bucket + one for the SGD update (no NCCL inside); nothing executes during capture."""
         m = self.model
         launches0 = ops.LAUNCHES
-        graphs = [torch.cuda.CUDAGraph() for _ in range(4)]
-        with torch.cuda.graph(graphs[0]):
-            self.garena.zero_()
-            out, saved = engine.forward(m, xs, m.nsplit, save=True)
-            loss, _, _, grad = ops.mse_count(out, gs, want_grad=True)
-            gen = engine.backward_steps(m, saved, grad, grads=self.gviews)
-            assert next(gen) == "backend"
-        pool = graphs[0].pool()
-        with torch.cuda.graph(graphs[1], pool=pool):
-            assert next(gen) == "ctx"
-        with torch.cuda.graph(graphs[2], pool=pool):
-            assert next(gen) == "frontend"
-            for _ in gen:   # runs the generator to its end (nothing left to enqueue)
-                pass
-        with torch.cuda.graph(graphs[3], pool=pool):
-            ops.sgd_momentum_step(self.arena, self.garena, self.buf, self.lr, self.momentum, self.buckets.grad_scale,
-                                  first=False)
+        graphs = [torch.cuda.CUDAGraph() for _ in range(len(self.DP_TAGS) + 1)]
+        pool = None
+        gen = None
+        for i, tag in enumerate(self.DP_TAGS):
+            with torch.cuda.graph(graphs[i], pool=pool):
+                if i == 0:
+                    self.garena.zero_()
+                    out, saved = engine.forward(m, xs, m.nsplit, save=True)
+                    loss, _, _, grad = ops.mse_count(out, gs, want_grad=True, loss_out=self.loss_slot)
+                    gen = engine.backward_steps(m, saved, grad, grads=self.gviews)
+                assert next(gen) == tag
+                if i == len(self.DP_TAGS) - 1:
+                    for _ in gen:   # runs the generator to its end (nothing left to enqueue)
+                        pass
+            pool = graphs[0].pool()
+        with torch.cuda.graph(graphs[-1], pool=pool):
+            ops.sgd_momentum_step(self.arena[self.hdr:], self.garena[self.hdr:], self.buf[self.hdr:], self.lr,
+                                  self.momentum, self.buckets.grad_scale, first=False)
         self._graph_launches = ops.LAUNCHES - launches0
         m._wcache.invalidate()
-        return graphs, loss
+        return graphs, self.loss_slot
 
     def _step_eager(self, img: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
         m = self.model
         launches0 = ops.LAUNCHES
         self.garena.zero_()  # bias / head gradients are accumulated with atomics (one 83 MB memset, ~13 us)
         out, saved = engine.forward(m, img, m.nsplit, save=True)
-        loss, _, _, grad = ops.mse_count(out, gt, want_grad=True)
+        # data parallel: the loss goes into the header slot of the gradient arena and is summed over ranks with the last
+        # bucket (logged loss = rank-mean of the local sum-losses, reduce_value)
+        loss, _, _, grad = ops.mse_count(out, gt, want_grad=True, loss_out=self.loss_slot if self.world > 1 else None)
         engine.backward(m, saved, grad, grads=self.gviews, on_ready=self.buckets.ready)
         if self.world > 1:
-            self.buckets.reduce_scalar(loss)   # logged loss = rank-mean of the local sum-losses (reduce_value)
             self.buckets.wait()
-            loss = loss / self.world
-        ops.sgd_momentum_step(self.arena, self.garena, self.buf, self.lr, self.momentum, self.buckets.grad_scale,
-                              first=self.first)
+            loss = self.loss_slot / self.world
+        ops.sgd_momentum_step(self.arena[self.hdr:], self.garena[self.hdr:], self.buf[self.hdr:], self.lr, self.momentum,
+                              self.buckets.grad_scale, first=self.first)
         self.first = False
         m._wcache.invalidate()  # the arena changed in place: packed weights must be rebuilt
         self._graph_launches = ops.LAUNCHES - launches0   # kernels of one step (what a graph replay launches)

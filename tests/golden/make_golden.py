@@ -4,6 +4,7 @@ Run in the build container only (``/root/reference`` does not exist on the GPU b
 
     python tests/golden/make_golden.py          # small cases  -> cannet_golden.npz
     python tests/golden/make_golden.py --big    # BASELINE.json's own shapes -> cannet_golden_big.npz
+    python tests/golden/make_golden.py --yard   # bf16 yardstick of the reference itself -> cannet_bf16_yardstick.npz
 
 The reference is path-loaded (``model/__init__.py`` imports matplotlib, absent here)
 and built with ``CANNet(load_weights=True)`` (the default constructor downloads
@@ -82,6 +83,67 @@ def main_big():
     np.savez_compressed(os.path.join(os.path.dirname(__file__), "cannet_golden_big.npz"), **out)
 
 
+YARD_CASES = [("he_1x64x96", "he", 1, 64, 96), ("he_2x48x80", "he", 2, 48, 80), ("default_1x104x136", "default", 1, 104, 136),
+              ("he_1x256x256", "he", 1, 256, 256)]
+TRAJ = dict(regime="he", n=2, h=48, w=80, steps=20, lr=1e-7, momentum=0.95)
+
+
+def main_yard():
+    """How far the REFERENCE ITSELF moves when its convolutions run in bf16 (torch.autocast on the CPU: bf16 weights and
+    activations, fp32 accumulation -- the arithmetic of this repo's bf16 path): per-parameter gradient error against its
+    own fp64 run, and the loss trajectory of 20 SGD steps (train_eval_utils.py:28-52, train.py:63,125-126) against fp32.
+    The GPU tests hold the CUDA bf16 path to a small multiple of these figures instead of a flat tolerance."""
+    torch.set_num_threads(os.cpu_count())
+    ref = load_reference()
+    out = {}
+    crit = torch.nn.MSELoss(reduction="sum")
+    for name, regime, n, h, w in YARD_CASES:
+        sd = harness.make_state_dict(regime, seed=0)
+        x, gt = harness.make_input(n, h, w), harness.make_gt(n, h, w)
+        m64 = ref.CANNet(load_weights=True).double()
+        m64.load_state_dict({k: v.double() for k, v in sd.items()})
+        crit(m64(x.double()), gt.double()).backward()
+        m = ref.CANNet(load_weights=True)
+        m.load_state_dict(sd)
+        with torch.autocast("cpu", dtype=torch.bfloat16):
+            et = m(x)
+        loss = crit(et.float(), gt)
+        loss.backward()
+        out[f"{name}/fwd_rel_l2"] = np.array(harness.rel_l2(et.float().detach(), m64(x.double()).detach()))
+        for (k, p), (_, p64) in zip(m.named_parameters(), m64.named_parameters()):
+            out[f"{name}/grad_rel_l2/{k}"] = np.array(harness.rel_l2(p.grad, p64.grad))
+        worst = max(float(v) for kk, v in out.items() if kk.startswith(f"{name}/grad_rel_l2/"))
+        print(name, "fwd", float(out[f"{name}/fwd_rel_l2"]), "worst grad", worst, flush=True)
+    # loss trajectories: fp32 and bf16-autocast runs of the reference module under torch.optim.SGD
+    t = TRAJ
+    sd = harness.make_state_dict(t["regime"], seed=0)
+    traj = {}
+    for tag in ("f32", "bf16"):
+        m = ref.CANNet(load_weights=True)
+        m.load_state_dict(sd)
+        opt = torch.optim.SGD(m.parameters(), lr=t["lr"], momentum=t["momentum"], weight_decay=0)   # train.py:63,125-126
+        losses = []
+        for step in range(t["steps"]):
+            x = harness.make_input(t["n"], t["h"], t["w"], seed=100 + step)
+            gt = harness.make_gt(t["n"], t["h"], t["w"], seed=200 + step)
+            opt.zero_grad()
+            if tag == "bf16":
+                with torch.autocast("cpu", dtype=torch.bfloat16):
+                    et = m(x)
+                et = et.float()
+            else:
+                et = m(x)
+            loss = crit(et, gt)
+            loss.backward()
+            opt.step()
+            losses.append(loss.item())
+        traj[tag] = np.array(losses)
+    out["traj/f32"], out["traj/bf16"] = traj["f32"], traj["bf16"]
+    print("trajectory f32 ", traj["f32"])
+    print("trajectory bf16 rel diff", np.abs(traj["bf16"] - traj["f32"]) / traj["f32"])
+    np.savez_compressed(os.path.join(os.path.dirname(__file__), "cannet_bf16_yardstick.npz"), **out)
+
+
 def main():
     torch.set_num_threads(os.cpu_count())
     ref = load_reference()
@@ -115,4 +177,4 @@ def main():
 
 
 if __name__ == "__main__":
-    main_big() if "--big" in sys.argv[1:] else main()
+    main_big() if "--big" in sys.argv[1:] else main_yard() if "--yard" in sys.argv[1:] else main()

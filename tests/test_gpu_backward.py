@@ -2,9 +2,12 @@
 
 Gradient tolerances: a ReLU / max-pool mask is a discontinuity, so a forward error eps flips a
 fraction ~eps of the masks and moves the gradient by ~sqrt(eps) in relative L2 (measured: the
-fp32 path, forward rel-L2 1.5e-5, gives 1e-5 .. 1.3e-2 per parameter; bf16, forward 6e-3, gives
-1e-3 .. 0.22).  BASELINE.json states tolerances for the forward outputs only; the bounds below are
-this repo's own and are checked per parameter together with the cosine similarity."""
+fp32 path, forward rel-L2 1.5e-5, gives 1e-5 .. 1.3e-2 per parameter).  BASELINE.json states tolerances for
+the forward outputs only.  The bf16 path is held to a yardstick instead of a flat bound: the reference module
+ITSELF under CPU bf16 autocast against its own fp64 run, per parameter (tests/golden/make_golden.py --yard:
+0.24 on conv1_1's weight falling to 5e-3 at the head) -- the CUDA gradients must stay within 2x of it."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -106,6 +109,12 @@ def test_unpool_routes_gradient_to_first_max(dev, shape):
 # ---------------------------------------------------------------- whole backward
 CASES = [("he", 1, 64, 96), ("he", 2, 48, 80), ("default", 1, 104, 136)]
 GRAD_TOL = {"fp32": dict(worst=5e-2, median=1e-2, cos=0.999), "bf16": dict(worst=0.35, median=0.12, cos=0.93)}
+YARD_FACTOR, YARD_FLOOR = 2.0, 1.5e-2
+
+
+@pytest.fixture(scope="module")
+def yard():
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "cannet_bf16_yardstick.npz"))
 
 
 def test_single_halo_tile_variant_backward(dev, monkeypatch):
@@ -119,8 +128,10 @@ def test_single_halo_tile_variant_backward(dev, monkeypatch):
 
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
 @pytest.mark.parametrize("case", CASES)
-def test_parameter_gradients_match_oracle(dev, case, precision):
+def test_parameter_gradients_match_oracle(dev, case, precision, yard=None):
     regime, n, h, w = case
+    if yard is None:
+        yard = np.load(os.path.join(os.path.dirname(__file__), "golden", "cannet_bf16_yardstick.npz"))
     sd = harness.make_state_dict(regime)
     x, gt = harness.make_input(n, h, w), harness.make_gt(n, h, w)
     loss_ref, _, gref = T.loss_and_grads(x, gt, sd, dtype=torch.float64)
@@ -135,6 +146,10 @@ def test_parameter_gradients_match_oracle(dev, case, precision):
         assert p.grad is not None and p.grad.shape == p.shape and torch.isfinite(p.grad).all(), k
         rels[k] = harness.rel_l2(p.grad.cpu(), gref[k])
         assert _cos(p.grad.cpu(), gref[k]) > tol["cos"], (k, rels[k])
+        if precision == "bf16":
+            # per parameter: within 2x of what bf16 arithmetic does to the reference's own gradient
+            y = float(yard[f"{regime}_{n}x{h}x{w}/grad_rel_l2/{k}"])
+            assert rels[k] < max(YARD_FACTOR * y, YARD_FLOOR), (k, rels[k], y)
     assert max(rels.values()) < tol["worst"], max(rels.items(), key=lambda kv: kv[1])
     assert float(np.median(list(rels.values()))) < tol["median"]
 
@@ -180,6 +195,26 @@ def test_fused_train_steps_match_oracle(dev, precision):
         d_got = (cur[k].cpu().double() - sd[k].double())
         assert harness.rel_l2(d_got, d_ref) < utol, k
     assert list(cur.keys()) == list(sd.keys())      # state_dict layout unchanged by the arena
+
+
+def test_twenty_step_loss_trajectory_follows_the_fp32_reference(dev, yard):
+    """20 SGD steps (lr 1e-7, momentum 0.95, a new batch every step) of the CUDA bf16 path against the live reference's
+    committed fp32 trajectory (tests/golden/make_golden.py --yard), step by step.  Yardstick: the reference under CPU
+    bf16 autocast drifts by up to 1.3 % over the same steps; the CUDA path must stay within 3 % at every step and within
+    2x the yardstick on average.  The first two steps are eager, the third is captured, the rest are graph replays."""
+    from can_b200.utils.train_eval_utils import FusedTrainer
+    ref, ref_bf16 = yard["traj/f32"], yard["traj/bf16"]
+    m = _model(harness.make_state_dict("he"), "bf16", dev)
+    tr = FusedTrainer(m, lr=1e-7, momentum=0.95)
+    got = []
+    for step in range(len(ref)):
+        x, gt = harness.make_input(2, 48, 80, seed=100 + step), harness.make_gt(2, 48, 80, seed=200 + step)
+        got.append(float(tr.step(x.to(dev), gt.to(dev))))
+    rel = np.abs(np.array(got) - ref) / ref
+    rel_y = np.abs(ref_bf16 - ref) / ref
+    print("trajectory rel diff: cuda bf16", np.round(rel, 4), "cpu bf16 yardstick", np.round(rel_y, 4))
+    assert rel.max() < 3e-2, (rel, got)
+    assert rel.mean() < 2.0 * rel_y.mean() + 2e-3, (rel.mean(), rel_y.mean())
 
 
 def test_stock_sgd_and_fused_sgd_agree(dev):
