@@ -37,6 +37,12 @@ class ConvArgs(C.Structure):
     ]
 
 
+class PackItem(C.Structure):
+    """can_pack_item of include/can_b200.h"""
+    _fields_ = [("w", C.c_void_p), ("dst_fwd", C.c_void_p), ("dst_dgrad", C.c_void_p), ("cout", C.c_int), ("cin", C.c_int),
+                ("taps", C.c_int)]
+
+
 _SIGNATURES = {
     "can_last_error_string": (C.c_char_p, []),
     "can_version": (C.c_int, []),
@@ -44,6 +50,7 @@ _SIGNATURES = {
     "can_pack_conv_weight": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "can_pack_conv_weight_both": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                             C.c_void_p]),
+    "can_pack_conv_weights_multi": (C.c_int, [C.POINTER(PackItem), C.c_int, C.c_int, C.c_void_p]),
     "can_pack_ctx_w2": (C.c_int, [C.c_void_p] * 5 + [C.c_int, C.c_void_p]),
     "can_transpose_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "can_conv_first_fwd": (C.c_int, [C.c_void_p] * 4 + [C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),

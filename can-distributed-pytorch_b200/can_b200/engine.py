@@ -45,6 +45,14 @@ class WeightCache:
             self._store[key] = hit
         return hit[1]
 
+    def put(self, key, params, value):
+        """Store a value built elsewhere (a multi-tensor pack) under the tag `get` would compute."""
+        self._store[key] = (tuple((p.data_ptr(), p._version, p.device) for p in params), value)
+
+    def fresh(self, key, params):
+        hit = self._store.get(key)
+        return hit is not None and hit[0] == tuple((p.data_ptr(), p._version, p.device) for p in params)
+
     def invalidate(self):
         """Drop every entry derived from parameters (after an in-place arena update, which does
         not bump version counters); shape-only entries (empty tag) are kept."""
@@ -57,6 +65,22 @@ def _packed(cache, tag, li, wt, nsplit, both):
     if both:
         return cache.get((tag, li, nsplit, "both"), (wt,), lambda: ops.pack_conv_weight_both(wt, nsplit))
     return (cache.get((tag, li, nsplit), (wt,), lambda: ops.pack_conv_weight(wt, nsplit)),)
+
+
+def prepack(model, nsplit):
+    """Training step: the forward and data-gradient packings of all fifteen 3x3 conv weights in ONE launch (they are
+    all stale after an optimizer update; fifteen small launches otherwise)."""
+    cache: WeightCache = model._wcache
+    fr, bk = _conv_params(model)
+    todo = [(("f", li, nsplit, "both"), fr[li][0]) for li in range(1, 10)] + \
+           [(("b", li, nsplit, "both"), bk[li][0]) for li in range(6)]
+    todo = [(k, w) for k, w in todo if not cache.fresh(k, (w,)) and w.is_contiguous() and w.dtype == torch.float32]
+    if len(todo) < 2:
+        return
+    with torch.no_grad():
+        packs = ops.pack_conv_weights_multi([w for _, w in todo], nsplit)
+    for (k, w), pk in zip(todo, packs):
+        cache.put(k, (w,), pk)
 
 
 def _conv_params(model):
@@ -79,6 +103,8 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
     x = x.contiguous().float()
     fr, bk = _conv_params(model)
     saved = {"x": x} if save else None
+    if save:
+        prepack(model, nsplit)
 
     # ---- frontend (CANNet.py:40) -------------------------------------------------
     w0, b0 = fr[0]

@@ -10,7 +10,7 @@ from dataclasses import dataclass
 
 import torch
 
-from ._lib import ConvArgs, check, lib
+from ._lib import ConvArgs, PackItem, check, lib
 
 MODE_STORE, MODE_POOL, MODE_HEAD, MODE_UNPOOL, MODE_CTX, MODE_CTX_BWD, MODE_DFV, MODE_CTX2, MODE_CTX2_BWD = range(9)
 
@@ -141,6 +141,24 @@ def pack_conv_weight_both(w: torch.Tensor, nsplit: int):
           "pack_conv_weight_both")
     _count()
     return fwd, dg
+
+
+def pack_conv_weights_multi(ws, nsplit: int):
+    """[(fwd pack, dgrad pack)] of up to 24 OIHW fp32 conv weights (3x3 or 1x1) in one launch."""
+    items = (PackItem * len(ws))()
+    out = []
+    for it, w in zip(items, ws):
+        co, ci, kh, kw = w.shape
+        taps = kh * kw
+        w = w.detach()
+        assert w.is_contiguous() and w.dtype == torch.float32
+        fwd = torch.empty(nsplit, co, taps * ci, device=w.device, dtype=torch.bfloat16)
+        dg = torch.empty(nsplit, ci, taps * co, device=w.device, dtype=torch.bfloat16)
+        it.w, it.dst_fwd, it.dst_dgrad, it.cout, it.cin, it.taps = w.data_ptr(), fwd.data_ptr(), dg.data_ptr(), co, ci, taps
+        out.append((fwd, dg))
+    check(lib().can_pack_conv_weights_multi(items, len(ws), nsplit, _stream()), "pack_conv_weights_multi")
+    _count()
+    return out
 
 
 def pack_ctx_w2(ws, nsplit: int) -> torch.Tensor:

@@ -81,22 +81,43 @@ thread_local const CUtensorMap* g_tmT = nullptr;
 thread_local const CUtensorMap* g_tmO = nullptr;
 thread_local const CUtensorMap* g_tmM = nullptr;   // mask map of the staged epilogue
 
-template <int BN, int NSPLIT, int MODE>
+// cta_group::2 launches: a cluster of two CTAs per pair
+template <typename K, typename... Args>
+int launch_pair(K kern, dim3 grid, int threads, int smem, cudaStream_t st, const char* what, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(threads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, args...);
+  if (e != cudaSuccess) return cuda_fail(e, what);
+  return 0;
+}
+
+template <int BN, int NSPLIT, int MODE, int PAIR = 0>
 int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p, dim3 grid, int stages_override,
                 cudaStream_t st) {
   using L = ConvTcSmem<BN, gemm_planes(NSPLIT, MODE)>;
   constexpr int ctx = MODE;   // (ConvTcSmem::bytes sizes the table region from the mode)
   const int staged_bytes = p.out_stage_bytes + p.mask_bufs * BN * 256;
-  int stages = (kMaxSmem - L::bytes(0, ctx) - staged_bytes) / L::kStageBytes;
+  constexpr int kStage = PAIR ? L::kABytes + L::kBBytes / 2 : L::kStageBytes;   // pair: each CTA holds half of B
+  int stages = (kMaxSmem - L::bytes(0, ctx) - staged_bytes) / kStage;
   if (stages > 8) stages = 8;
   if (stages_override > 0 && stages_override < stages) stages = stages_override;
   if (stages < 2) return fail(-20, "conv_tc: tile BN=%d nsplit=%d does not fit shared memory", BN, NSPLIT);
   p.stages = stages;
-  const int smem = L::bytes(stages, ctx) + staged_bytes;
+  const int smem = L::bytes(0, ctx) + stages * kStage + staged_bytes;
   // eight epilogue warps for the narrow, epilogue-bound tiles of the bf16 path
   constexpr int EW = ((NSPLIT == 1 && BN <= 128 && (MODE == MODE_STORE || MODE == MODE_POOL || MODE == MODE_UNPOOL)) ||
                       MODE == MODE_CTX2 || MODE == MODE_CTX2_BWD) ? 8 : 4;   // (MODE_DFV with 8: measured slower)
-  auto kern = conv_tc_kernel<BN, NSPLIT, MODE, 0, EW>;
+  auto kern = conv_tc_kernel<BN, NSPLIT, MODE, 0, EW, PAIR>;
   static bool attr_done = false;  // per template instantiation
   static int attr_smem = 0;
   if (!attr_done || smem > attr_smem) {
@@ -105,6 +126,9 @@ int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p,
     attr_done = true;
     attr_smem = kMaxSmem;
   }
+  if (PAIR)
+    return launch_pair(kern, grid, 128 + 32 * EW, smem, st, "cudaLaunchKernelEx(conv_tc, CTA pairs)", tmA, tmB,
+                       g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA, g_tmO ? *g_tmO : tmA, g_tmM ? *g_tmM : tmA, p);
   kern<<<grid, 128 + 32 * EW, smem, st>>>(tmA, tmB, g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA, g_tmO ? *g_tmO : tmA,
                                          g_tmM ? *g_tmM : tmA, p);
   CAN_CHECK_LAUNCH("conv_tc launch");
@@ -269,6 +293,17 @@ int launch_ctx_gemv(const float* Wm, const float* in, long long in_ns, long long
     cudaError_t e = cudaFuncSetAttribute(ctx_pos_gemv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 36 * 512 * 4);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(ctx_pos_gemv)");
     attr = true;
+  }
+  if (env_int("CAN_B200_CTXGEMM", 1) != 0) {
+    // all images of a scale as one GEMM (a weight slab is read once per 32 positions, not once per image)
+    const int pt = N >= 8 ? 64 : 32;   // positions per tile
+    int tiles = 0;
+    const int SS[4] = {1, 2, 3, 6};
+    for (int j = 0; j < 4; ++j) tiles += ((N * SS[j] * SS[j] + pt - 1) / pt) * 8;
+    if (pt == 64) ctx_pos_gemm_kernel<64><<<tiles, 256, 0, st>>>(Wm, in, in_ns, in_ps, in_js, add, out, N);
+    else ctx_pos_gemm_kernel<32><<<tiles, 256, 0, st>>>(Wm, in, in_ns, in_ps, in_js, add, out, N);
+    CAN_CHECK_LAUNCH("ctx_pos_gemm");
+    return 0;
   }
   ctx_pos_gemv_kernel<<<dim3(32, 4, N), 256, 9 * 512 * 4, st>>>(Wm, in, in_ns, in_ps, in_js, add, out);
   CAN_CHECK_LAUNCH("ctx_pos_gemv");
@@ -558,6 +593,41 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     return ns == 1   ? launch_conv<64, 1, MODE_HEAD>(tmA, tmB, p, grid, so, st)
            : ns == 2 ? launch_conv<64, 2, MODE_HEAD>(tmA, tmB, p, grid, so, st)
                      : launch_conv<64, 3, MODE_HEAD>(tmA, tmB, p, grid, so, st);
+  }
+  // bf16 path, 128- and 256-wide tiles: CTA pairs (cta_group::2).  Each CTA loads its own pixel tile and half of the
+  // n-tile's weight rows: a third less shared-memory operand traffic per MMA at BN = 256 and every weight tile fetched
+  // from L2 once per pair.  Measured (profiles/r02_pair_ab.txt): 512->512 169 -> 158 us, its data gradient 180 -> 164 us,
+  // 256->256 179 -> 159 us, the training step 7.82 -> 7.46 ms.  CAN_B200_PAIR=0 switches them off.  The narrow HALO
+  // layers and the weight-gradient kernels were built as pairs too and measured slower (same file): not kept.
+  const int pix_tiles = p.tiles_x * p.tiles_y * a->N;
+  const int m = a->mode;
+  if (ns == 1 && (bn == 128 || bn == 256) && pix_tiles >= 2 && ctas >= 2 && env_int("CAN_B200_PAIR", 1) != 0 &&
+      (m == CAN_MODE_STORE || m == CAN_MODE_POOL || m == CAN_MODE_UNPOOL || m == CAN_MODE_DFV)) {
+    CUtensorMap tmBh;   // weight map with a box of half the n-tile (rank r loads rows [n0 + r bn/2, n0 + (r + 1) bn/2))
+    const uint64_t K = static_cast<uint64_t>(a->taps) * a->Cin;
+    const uint64_t dimsB[3] = {K, static_cast<uint64_t>(a->Cout), 1};
+    const uint64_t strB[2] = {K * 2, K * 2 * a->Cout};
+    const uint32_t boxB[3] = {64, static_cast<uint32_t>(bn / 2), 1};
+    int rc = make_tmap(&tmBh, a->w, 3, dimsB, strB, boxB);
+    if (rc) return rc;
+    const int items = ((pix_tiles + 1) / 2) * p.n_tiles;
+    int pairs = ctas / 2;
+    if (pairs > items) pairs = items;
+    const dim3 pg(2 * pairs);
+    if (bn == 256) {
+      switch (m) {
+        case CAN_MODE_STORE: return launch_conv<256, 1, MODE_STORE, 1>(tmA, tmBh, p, pg, so, st);
+        case CAN_MODE_POOL: return launch_conv<256, 1, MODE_POOL, 1>(tmA, tmBh, p, pg, so, st);
+        case CAN_MODE_UNPOOL: return launch_conv<256, 1, MODE_UNPOOL, 1>(tmA, tmBh, p, pg, so, st);
+        default: return launch_conv<256, 1, MODE_DFV, 1>(tmA, tmBh, p, pg, so, st);
+      }
+    }
+    switch (m) {
+      case CAN_MODE_STORE: return launch_conv<128, 1, MODE_STORE, 1>(tmA, tmBh, p, pg, so, st);
+      case CAN_MODE_POOL: return launch_conv<128, 1, MODE_POOL, 1>(tmA, tmBh, p, pg, so, st);
+      case CAN_MODE_UNPOOL: return launch_conv<128, 1, MODE_UNPOOL, 1>(tmA, tmBh, p, pg, so, st);
+      default: return launch_conv<128, 1, MODE_DFV, 1>(tmA, tmBh, p, pg, so, st);
+    }
   }
   if (bn == 64)
     return ns == 1   ? dispatch_mode<64, 1>(a->mode, tmA, tmB, p, grid, so, st)
@@ -1162,6 +1232,34 @@ int can_pack_conv_weight_both(const float* w, void* dst_fwd, void* dst_dgrad, in
   launch_pack(w, static_cast<__nv_bfloat16*>(dst_fwd), static_cast<__nv_bfloat16*>(dst_dgrad), cout, cin, taps, nsplit,
               static_cast<cudaStream_t>(stream));
   CAN_CHECK_LAUNCH("pack_conv_weight_both");
+  return 0;
+}
+
+int can_pack_conv_weights_multi(const can_pack_item* items, int n, int nsplit, void* stream) {
+  if (!items || n <= 0 || n > PackItems::kMax || nsplit < 1 || nsplit > 3)
+    return fail(-1, "pack_conv_weights_multi: bad arguments (at most %d items)", PackItems::kMax);
+  PackItems it;
+  memset(&it, 0, sizeof(it));
+  it.n = n;
+  int blocks = 0;
+  for (int i = 0; i < n; ++i) {
+    const can_pack_item& a = items[i];
+    if (!a.w || (!a.dst_fwd && !a.dst_dgrad) || a.cout <= 0 || a.cin <= 0 || a.cout % 32 || a.cin % 32 ||
+        (a.taps != 9 && a.taps != 1))
+      return fail(-2, "pack_conv_weights_multi: item %d: cout/cin must be positive multiples of 32, taps 9 or 1", i);
+    it.first[i] = blocks;
+    it.w[i] = a.w;
+    it.fwd[i] = static_cast<__nv_bfloat16*>(a.dst_fwd);
+    it.dgrad[i] = static_cast<__nv_bfloat16*>(a.dst_dgrad);
+    it.cout[i] = a.cout;
+    it.cin[i] = a.cin;
+    it.taps[i] = a.taps;
+    blocks += (a.cin / 32) * (a.cout / 32);
+  }
+  it.first[n] = blocks;
+  const size_t smem = 32 * (32 * 9 + 1) * sizeof(float);
+  pack_conv_weights_multi_kernel<<<blocks, 256, smem, static_cast<cudaStream_t>(stream)>>>(it, nsplit);
+  CAN_CHECK_LAUNCH("pack_conv_weights_multi");
   return 0;
 }
 

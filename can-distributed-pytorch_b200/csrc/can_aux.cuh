@@ -205,12 +205,10 @@ __global__ void wgrad_reduce_kernel_v3(const float* __restrict__ ws, float* __re
 // Third-generation weight packing (same contract as pack_conv_weight_kernel_v2): all loads of a thread are
 // issued before the first dependent shared-memory store (the v2 loop paid the memory latency nine times).
 template <int TAPS>
-__global__ void __launch_bounds__(256)
-pack_conv_weight_kernel_v3(const float* __restrict__ w, __nv_bfloat16* __restrict__ fwd,
-                           __nv_bfloat16* __restrict__ dgrad, int cout, int cin, int nsplit) {
-  extern __shared__ float s_w[];  // [32 co][32*TAPS + 1]
+__device__ __forceinline__ void pack_conv_weight_tile(const float* __restrict__ w, __nv_bfloat16* __restrict__ fwd,
+                                                      __nv_bfloat16* __restrict__ dgrad, int cout, int cin, int nsplit,
+                                                      int ci0, int co0, float* s_w) {
   constexpr int taps = TAPS;
-  const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 32;
   constexpr int row = 32 * TAPS + 1;
   constexpr int per_row = 32 * TAPS, tot = 32 * per_row;
   constexpr int NL = (tot + 255) / 256;   // 36 (3x3) or 4 (1x1)
@@ -263,6 +261,38 @@ pack_conv_weight_kernel_v3(const float* __restrict__ w, __nv_bfloat16* __restric
       }
     }
   }
+}
+
+template <int TAPS>
+__global__ void __launch_bounds__(256)
+pack_conv_weight_kernel_v3(const float* __restrict__ w, __nv_bfloat16* __restrict__ fwd,
+                           __nv_bfloat16* __restrict__ dgrad, int cout, int cin, int nsplit) {
+  extern __shared__ float s_w[];  // [32 co][32*TAPS + 1]
+  pack_conv_weight_tile<TAPS>(w, fwd, dgrad, cout, cin, nsplit, blockIdx.x * 32, blockIdx.y * 32, s_w);
+}
+
+// Every conv weight of the network in ONE launch (a training step re-packs all of them after the optimizer update:
+// sixteen launches of 2-10 us each otherwise, most of them too small to fill the GPU).  Item i owns the blocks
+// [first[i], first[i + 1]) = its (cin/32) x (cout/32) tiles; taps is 9 or 1.
+struct PackItems {
+  static constexpr int kMax = 24;
+  int n;
+  int first[kMax + 1];
+  const float* w[kMax];
+  __nv_bfloat16* fwd[kMax];
+  __nv_bfloat16* dgrad[kMax];
+  int cout[kMax], cin[kMax], taps[kMax];
+};
+__global__ void __launch_bounds__(256)
+pack_conv_weights_multi_kernel(const __grid_constant__ PackItems it, int nsplit) {
+  extern __shared__ float s_w[];  // [32 co][32*9 + 1]
+  int i = 0;
+  while (i + 1 < it.n && static_cast<int>(blockIdx.x) >= it.first[i + 1]) ++i;
+  const int t = blockIdx.x - it.first[i];
+  const int tiles_x = it.cin[i] / 32;
+  const int ci0 = (t % tiles_x) * 32, co0 = (t / tiles_x) * 32;
+  if (it.taps[i] == 9) pack_conv_weight_tile<9>(it.w[i], it.fwd[i], it.dgrad[i], it.cout[i], it.cin[i], nsplit, ci0, co0, s_w);
+  else pack_conv_weight_tile<1>(it.w[i], it.fwd[i], it.dgrad[i], it.cout[i], it.cin[i], nsplit, ci0, co0, s_w);
 }
 
 // im2col of the 3-channel image (second generation): out[pl][n][y][x][k], k = ci*9 + r*3 + s for

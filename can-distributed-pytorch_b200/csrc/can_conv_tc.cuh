@@ -230,7 +230,14 @@ __device__ __forceinline__ void load_bias32(const float* s, float* b) {
 // EW = number of epilogue warps (4 or 8).  The epilogue runs one warp per scheduler, i.e. latency
 // bound; for narrow tiles (small K) it is the critical path, so EW = 8 lets two warps share each TMEM
 // lane quarter, each taking half of the BN columns.
-template <int BN, int NSPLIT, int MODE, int HALO = 0, int EW = 4>
+// PAIR = 1 (bf16 path): two CTAs of a cluster on the two SMs of a TPC work as a cta_group::2 pair.  One MMA covers two
+// pixel tiles of the same n-tile (M = 256: each CTA's own 128-pixel A tile is its half of A) and each CTA holds only
+// HALF of the n-tile's weight rows (rows [rank * BN/2, (rank + 1) * BN/2) of B): the tensor core of each SM reads
+// A + B/2 instead of A + B from its shared memory, and the pair fetches every weight tile from L2 once instead of twice
+// (wide tiles: 32 KB instead of 48 KB per CTA and k-block).  The even CTA issues every MMA; both CTAs load (their TMA
+// completions are counted on the leader's barriers), run the epilogue of their own tile out of their own TMEM, and the
+// MMA warp's commits arrive on the barriers of both.  No TMA multicast is involved.
+template <int BN, int NSPLIT, int MODE, int HALO = 0, int EW = 4, int PAIR = 0>
 __global__ void __launch_bounds__(128 + 32 * EW, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmT,
@@ -245,7 +252,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint8_t* s_mask = smem + p.out_stage_bytes;                       // staged mask tiles (p.mask_bufs x BN * 256 B)
   uint8_t* wbase = s_mask + p.mask_bufs * (BN * 256);               // HALO: resident weights
   uint8_t* ring = HALO ? wbase + p.w_bytes : wbase;                // stage ring
-  const int stage_bytes = HALO ? p.halo_stride : L::kStageBytes;
+  const int stage_bytes = HALO ? p.halo_stride : GS * (L::kABytes + (PAIR ? L::kBBytes / 2 : L::kBBytes));
   // single-halo-tile variant: not compiled into the max-unpool kernels (their epilogue sits on the register limit)
   const bool halo1 = HALO && MODE != MODE_UNPOOL && p.halo1;
   uint8_t* tail = ring + stages * stage_bytes;
@@ -269,6 +276,24 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   constexpr int ACC_COLS = AccLayout<BN, GS>::cols(MODE);
   constexpr int ACC_STAGES = AccLayout<BN, GS>::acc_stages(MODE);
   const int base_kb = p.taps * p.kchunks;
+  static_assert(!PAIR || (!HALO && NSPLIT == 1 && (MODE == MODE_STORE || MODE == MODE_POOL || MODE == MODE_UNPOOL || MODE == MODE_DFV)),
+                "CTA pairs exist for the streamed (non-HALO) tiles of the bf16 path");
+  // Work items.  Plain: CTA b takes tiles b, b + grid, ...  Pair: the two CTAs walk the same list of tile PAIRS in
+  // lockstep, rank r taking tile 2 q + r (an odd tile count leaves the last item's odd CTA a dead tile: it recomputes the
+  // last tile and drops the result).
+  const int rank = PAIR ? static_cast<int>(cluster_ctarank()) : 0;
+  const bool leader = rank == 0;
+  const int W0 = PAIR ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int WS = PAIR ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  const int pix_tiles = p.num_tiles / p.n_tiles;
+  const int WN = PAIR ? ((pix_tiles + 1) >> 1) * p.n_tiles : p.num_tiles;
+  // (n-tile fastest, as in the plain tile order: CTAs working at the same time share the activation patch in L2)
+  auto tile_of = [&](int q) {
+    return PAIR ? min(2 * (q / p.n_tiles) + rank, pix_tiles - 1) * p.n_tiles + q % p.n_tiles : q;
+  };
+  auto live_of = [&](int q) { return !PAIR || (2 * (q / p.n_tiles) + rank < pix_tiles); };
+  constexpr int kBt = PAIR ? L::kBBytes / 2 : L::kBBytes;   // bytes of one weight tile in this CTA
+  constexpr int kStageSz = GS * (L::kABytes + kBt);         // non-HALO stage: A tile(s) + this CTA's part of B
   // MODE_CTX2: two extra k-blocks whose A operand is the interpolation matrix Wint[pixel][64 positions]
   // and whose B operands are the per-image tables (-U-side of z, then s) -- see the epilogue.
   constexpr bool kCtx2 = (MODE == MODE_CTX2 || MODE == MODE_CTX2_BWD);
@@ -303,7 +328,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       for (int a = 0; a < 4; ++a) {
         mbar_init(&tmem_full_bar[a], 1);
-        mbar_init(&tmem_empty_bar[a], 32 * EW);  // every epilogue thread arrives
+        // every epilogue thread arrives (pair: plus one arrival per epilogue warp of the odd CTA, on the leader's barrier)
+        mbar_init(&tmem_empty_bar[a], 32 * EW + (PAIR ? EW : 0));
       }
       mbar_init(w_bar, 1);
       for (int a = 0; a < 2; ++a) {
@@ -317,11 +343,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       fence_mbar_init();
     }
     __syncwarp();
-    tmem_alloc(tmem_ptr_smem, ACC_COLS * ACC_STAGES);
-    tmem_relinquish();
+    if (PAIR) {
+      tmem_alloc_pair(tmem_ptr_smem, ACC_COLS * ACC_STAGES);
+      tmem_relinquish_pair();
+    } else {
+      tmem_alloc(tmem_ptr_smem, ACC_COLS * ACC_STAGES);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();   // the partner's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
@@ -334,7 +366,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // resident weights: every (tap, chunk) tile of this CTA's BN output channels, once
         mbar_expect_tx(w_bar, static_cast<uint32_t>(p.w_bytes));
         for (int kb = 0; kb < base_kb; ++kb) tma_load_3d(wbase + kb * L::kBBytes, &tmB, w_bar, kb * 64, 0, 0);
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        for (int q_ = W0; q_ < WN; q_ += WS) {
+        const int tile = tile_of(q_);
           CAN_TILE_DECODE(tile)
           (void)n0;
           for (int chunk = 0; chunk < p.kchunks; ++chunk) {
@@ -351,7 +384,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
       } else
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      for (int q_ = W0; q_ < WN; q_ += WS) {
+        const int tile = tile_of(q_);
         CAN_TILE_DECODE(tile)
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -362,8 +396,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             dy = (tap / 3 - 1) * p.dil;
             dx = (tap % 3 - 1) * p.dil;
           }
-          uint8_t* sa = ring + stage * L::kStageBytes;
+          uint8_t* sa = ring + stage * kStageSz;
           uint8_t* sb = sa + GS * L::kABytes;
+          if (PAIR) {
+            // both CTAs' tiles are counted on the leader's barrier (a completion that overtakes the leader's expect_tx
+            // leaves the count transiently negative; the phase needs the leader's arrival too)
+            if (leader) mbar_expect_tx(&full_bar[stage], 2 * kStageSz);
+            const uint32_t fb = mapa_shared(&full_bar[stage], 0);
+            tma_load_5d_pair(sa, &tmA, fb, chunk * 64, x0 + dx, y0 + dy, n_img, 0);
+            tma_load_3d_pair(sb, &tmB, fb, kb * 64, n0 + rank * (BN / 2), 0);
+          } else {
           mbar_expect_tx(&full_bar[stage], L::kStageBytes);
           if (kCtx2 && kb >= base_kb) {
             tma_load_5d(sa, &tmW, &full_bar[stage], 0, x0, y0, 0, 0);
@@ -375,6 +417,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               tma_load_3d(sb + pl * L::kBBytes, &tmB, &full_bar[stage], kb * 64, n0, pl);
             }
           }
+          }
           if (++stage == stages) {
             stage = 0;
             phase ^= 1;
@@ -383,17 +426,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
+    // ===================== MMA issuer (pair: the leader CTA's only) =====================
+    if ((!PAIR || leader) && elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(PAIR ? 256 : 128, BN, 0, 0);
+      auto mma = [&](uint32_t d, uint64_t da, uint64_t db, uint32_t acc) {
+        if (PAIR) umma_bf16_pair(d, da, db, idesc, acc);
+        else umma_bf16(d, da, db, idesc, acc);
+      };
+      auto commit = [&](uint64_t* bar) {
+        if (PAIR) umma_commit_pair(bar);
+        else umma_commit(bar);
+      };
       int stage = 0;
       uint32_t phase = 0;
       constexpr int NACC = AccLayout<BN, GS>::kNacc;
       int it = 0;  // tiles processed by this CTA
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      for (int q_ = W0; q_ < WN; q_ += WS, ++it) {
         const int as = it % ACC_STAGES;
         const uint32_t aphase = static_cast<uint32_t>(it / ACC_STAGES) & 1u;
-        mbar_wait(&tmem_empty_bar[as], aphase ^ 1);  // epilogue drained this accumulator stage
+        mbar_wait(&tmem_empty_bar[as], aphase ^ 1);  // epilogue drained this accumulator stage (pair: in both CTAs)
         tc_fence_after();
         const uint32_t tacc = tmem_base + as * ACC_COLS;
         uint32_t used = 0;  // bit a: accumulator a already holds a partial sum
@@ -401,7 +452,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (it == 0) mbar_wait(w_bar, 0);
           const uint64_t wdesc0 = umma_smem_desc(smem_u32(wbase), 16, 1024);
           const uint32_t dy_bytes = static_cast<uint32_t>(p.dil * p.TW * 128);
-          const uint32_t tap_row_units = static_cast<uint32_t>((3 * p.kchunks * L::kBBytes) >> 4);  // dy -> dy+1
+          const uint32_t tap_row_units = static_cast<uint32_t>((3 * p.kchunks * kBt) >> 4);  // dy -> dy+1
           uint32_t accum = 0;
           if (halo1) {
             // One (TH + 2 dil) x (TW + 2 dil) halo tile per channel chunk, TW = 8: the 8-row groups of A are the patch
@@ -414,8 +465,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               mbar_wait(&full_bar[stage], phase);
               tc_fence_after();
               const uint64_t da0 = umma_smem_desc(smem_u32(ring + stage * stage_bytes), 16, pitch * 128);
-              const uint64_t db0 = wdesc0 + static_cast<uint32_t>((chunk * L::kBBytes) >> 4);
-              const uint32_t tap_units = static_cast<uint32_t>((p.kchunks * L::kBBytes) >> 4);   // tap -> tap + 1
+              const uint64_t db0 = wdesc0 + static_cast<uint32_t>((chunk * kBt) >> 4);
+              const uint32_t tap_units = static_cast<uint32_t>((p.kchunks * kBt) >> 4);   // tap -> tap + 1
               const uint32_t dx_units = static_cast<uint32_t>(p.dil) * 8, dy_units = dx_units * pitch;
 #pragma unroll
               for (int dyi = 0; dyi < 3; ++dyi) {
@@ -425,12 +476,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                   const uint64_t db = db0 + (dyi * 3 + dxi) * tap_units;
 #pragma unroll
                   for (int k = 0; k < 4; ++k) {
-                    umma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, accum);
+                    mma(tacc, da + 2 * k, db + 2 * k, accum);
                     accum = 1;
                   }
                 }
               }
-              umma_commit(&empty_bar[stage]);
+              commit(&empty_bar[stage]);
               if (++stage == stages) {
                 stage = 0;
                 phase ^= 1;
@@ -444,18 +495,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               // one descriptor per stage; taps and k-steps only add to its 14-bit address field (>> 4).
               // The issuing thread is alone: every ALU op it spends per MMA is exposed latency.
               const uint64_t da0 = umma_smem_desc(smem_u32(ring + stage * stage_bytes), 16, 1024);
-              const uint64_t db0 = wdesc0 + static_cast<uint32_t>(((dxi * p.kchunks + chunk) * L::kBBytes) >> 4);
+              const uint64_t db0 = wdesc0 + static_cast<uint32_t>(((dxi * p.kchunks + chunk) * kBt) >> 4);
 #pragma unroll
               for (int dyi = 0; dyi < 3; ++dyi) {
                 const uint64_t da = da0 + static_cast<uint32_t>((dyi * dy_bytes) >> 4);
                 const uint64_t db = db0 + static_cast<uint32_t>(dyi * tap_row_units);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                  umma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, accum);
+                  mma(tacc, da + 2 * k, db + 2 * k, accum);
                   accum = 1;
                 }
               }
-              umma_commit(&empty_bar[stage]);
+              commit(&empty_bar[stage]);
               if (++stage == stages) {
                 stage = 0;
                 phase ^= 1;
@@ -466,7 +517,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(ring + stage * L::kStageBytes);
+          const uint32_t sa = smem_u32(ring + stage * kStageSz);
           const uint64_t da0 = umma_smem_desc(sa, 16, 1024);                       // one descriptor pair per
           const uint64_t db0 = umma_smem_desc(sa + GS * L::kABytes, 16, 1024);     // stage (see HALO note)
 #pragma unroll
@@ -482,18 +533,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 used |= 1u << acc;
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
-                  umma_bf16(tacc + acc * BN, da0 + ((pa * L::kABytes + k * 32) >> 4), db0 + ((pb * L::kBBytes + k * 32) >> 4),
-                            idesc, k ? 1u : accf);
+                  mma(tacc + acc * BN, da0 + ((pa * L::kABytes + k * 32) >> 4), db0 + ((pb * L::kBBytes + k * 32) >> 4),
+                      k ? 1u : accf);
               }
             }
           }
-          umma_commit(&empty_bar[stage]);   // frees the smem slot when these MMAs retire
+          commit(&empty_bar[stage]);   // frees the smem slot when these MMAs retire (pair: in both CTAs)
           if (++stage == stages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(&tmem_full_bar[as]);  // accumulator of this tile complete
+        commit(&tmem_full_bar[as]);  // accumulator of this tile complete (pair: of both tiles, told to both CTAs)
       }
     }
   } else if (warp == 2 + EW) {
@@ -504,15 +555,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (MODE == MODE_UNPOOL && out_lane) {
       // four rounds per tile (one per position of the 2x2 window), two staging buffers; tmO strides by 2 in x and y
       int R = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      for (int q_ = W0; q_ < WN; q_ += WS) {
+        const int tile = tile_of(q_);
         CAN_TILE_DECODE(tile)
         for (int r = 0; r < 4; ++r, ++R) {
           const int b = R & 1;
           mbar_wait(&out_full_bar[b], static_cast<uint32_t>(R >> 1) & 1u);
+          if (live_of(q_)) {   // (a pair's dead tile goes through the hand-shakes but stores nothing)
 #pragma unroll
           for (int blk = 0; blk < BN / 64; ++blk)
             tma_store_4d(&tmO, s_out + b * (BN * 256) + blk * 16384, n0 + blk * 64, 2 * x0 + (r & 1), 2 * y0 + (r >> 1),
                          n_img);
+          }
           bulk_commit_group();
           bulk_wait_group_read1();                      // the previous round's store has read its buffer
           if (R > 0) mbar_arrive(&out_free_bar[b ^ 1]);
@@ -523,7 +577,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else if (MODE == MODE_CTX2_BWD && out_lane) {
       // four rounds per tile, eight segment stores per round (tmO: box (16 ch, TW, TH), no swizzle)
       int R = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      for (int q_ = W0; q_ < WN; q_ += WS) {
+        const int tile = tile_of(q_);
         CAN_TILE_DECODE(tile)
         (void)n0;
         for (int r = 0; r < 4; ++r, ++R) {
@@ -544,7 +599,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // one 64-channel tile of the fused features per GEMM tile
       const int nb = p.out_bufs;
       int it = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      for (int q_ = W0; q_ < WN; q_ += WS, ++it) {
+        const int tile = tile_of(q_);
         CAN_TILE_DECODE(tile)
         (void)n0;
         const int b = it % nb;
@@ -557,7 +613,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else if (MODE == MODE_STORE && BN == 256 && out_lane) {
       // BN = 256: four 64-channel blocks per tile, two 16 KB staging tiles (round = block)
       int R = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      for (int q_ = W0; q_ < WN; q_ += WS) {
+        const int tile = tile_of(q_);
         CAN_TILE_DECODE(tile)
         for (int blk = 0; blk < BN / 64; ++blk, ++R) {
           const int nb = p.out_bufs, b = R % nb;
@@ -580,13 +637,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else if (out_lane) {
       const int nb = p.out_bufs;   // 1 or 2
       int it = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      for (int q_ = W0; q_ < WN; q_ += WS, ++it) {
+        const int tile = tile_of(q_);
         CAN_TILE_DECODE(tile)
         const int b = it % nb;
         mbar_wait(&out_full_bar[b], static_cast<uint32_t>(it / nb) & 1u);
+        if (live_of(q_)) {
 #pragma unroll
         for (int blk = 0; blk < BN / 64; ++blk)
           tma_store_4d(&tmO, s_out + b * (BN * 256) + blk * 16384, n0 + blk * 64, x0, y0, n_img);
+        }
         bulk_commit_group();
         if (nb == 1) {
           bulk_wait_group_read0();
@@ -606,7 +666,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // brings the ReLU-mask tile of each output tile into shared memory, as far ahead as the buffers allow
     if (p.mask_bufs && elect_one()) {
       int it = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      for (int q_ = W0; q_ < WN; q_ += WS, ++it) {
+        const int tile = tile_of(q_);
         CAN_TILE_DECODE(tile)
         const int b = it % p.mask_bufs;
         const uint32_t ph = static_cast<uint32_t>(it / p.mask_bufs) & 1u;
@@ -627,6 +688,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // columns of the tile handled by this warp (EW == 8: the two warps of a lane quarter split them)
     constexpr int CW = BN / (EW / 4);
     const int cbeg = ((warp - 2) >> 2) * CW, cend = cbeg + CW;
+    // "this CTA's epilogue is done with accumulator stage a": the MMA issuer waits for it.  Pair: the issuer lives in the
+    // leader CTA, so the odd CTA's warps arrive on the leader's barrier (one arrival per warp).
+    auto release_acc = [&](int a) {
+      if (PAIR && !leader) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(mapa_shared(&tmem_empty_bar[a], 0));
+      } else {
+        mbar_arrive(&tmem_empty_bar[a]);
+      }
+    };
     if (p.db) {
       for (int i = etid; i < 1024; i += 32 * EW) s_db[i] = 0.f;
       asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
@@ -639,7 +710,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
     for (int i = 0; i < (kDbRegMode ? 32 : 1); ++i) dbacc[i] = 0.f;
     int it = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+    for (int q_ = W0; q_ < WN; q_ += WS, ++it) {
+        const int tile = tile_of(q_);
     CAN_TILE_DECODE(tile)
     const int as = it % ACC_STAGES;
     const uint32_t aphase = static_cast<uint32_t>(it / ACC_STAGES) & 1u;
@@ -685,7 +757,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (!bias_once || it == 0) asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
 
     const int y = y0 + ty, x = x0 + tx;
-    const bool valid = (y < p.H) && (x < p.W);
+    const bool valid = live_of(q_) && (y < p.H) && (x < p.W);
     const uint32_t taddr = tmem_base + as * ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
 
     // Operands of the epilogue that do not depend on the accumulator (ReLU mask / arg-max codes /
@@ -829,7 +901,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // 2x2 window = lanes {l, l^1, l^TW, l^TW^1}; the lane at the even/even corner writes.
       const int PH = p.H >> 1, PW = p.W >> 1;
       const int py = y >> 1, px = x >> 1;
-      const bool writer = ((tx & 1) == 0) && ((ty & 1) == 0) && (py < PH) && (px < PW);
+      const bool writer = ((tx & 1) == 0) && ((ty & 1) == 0) && (py < PH) && (px < PW) && live_of(q_);
       const int pos = ((ty & 1) << 1) | (tx & 1);  // scan order inside the window
       const long long ppix = (static_cast<long long>(n_img) * PH + py) * PW + px;
       __nv_bfloat16* obase = p.out + ppix * p.out_cs + p.out_coff + n0;
@@ -971,7 +1043,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
       tc_fence_before();
-      mbar_arrive(&tmem_empty_bar[as]);   // the accumulator is in registers now
+      release_acc(as);   // the accumulator is in registers now
 #pragma unroll 1
       for (int wpos = 0; wpos < 4; ++wpos) {
         const int R = it * 4 + wpos, b = R & 1;
@@ -1474,7 +1546,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     // this accumulator stage may be overwritten by the MMAs of the tile after next
     tc_fence_before();
-    mbar_arrive(&tmem_empty_bar[as]);
+    release_acc(as);
     if (kStaged) {
       // generic-proxy writes of s_out -> visible to the async proxy, then tell the output warp
       // (out-of-image pixels of edge tiles are clipped by the tensor map)
@@ -1494,9 +1566,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();   // neither CTA leaves (or frees TMEM) while the other may still signal its barriers
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, ACC_COLS * ACC_STAGES);
+    if (PAIR) tmem_dealloc_pair(tmem_base, ACC_COLS * ACC_STAGES);
+    else tmem_dealloc(tmem_base, ACC_COLS * ACC_STAGES);
   }
 }
 

@@ -101,6 +101,15 @@ int can_pack_conv_weight(const float* w, void* dst, int cout, int cin, int taps,
  * step re-packs every weight after each optimizer update.                                        */
 int can_pack_conv_weight_both(const float* w, void* dst_fwd, void* dst_dgrad, int cout, int cin, int taps,
                               int nsplit, void* stream);
+/* The same for up to 24 weights in one launch (all 3x3 / 1x1 conv weights of the network; cout and cin multiples of
+ * 32, taps 9 or 1).  A training step calls it once after the optimizer update (utils/train_eval_utils.py:52).      */
+typedef struct can_pack_item {
+  const float* w;    /* [cout][cin][taps] fp32 */
+  void* dst_fwd;     /* [plane][cout][taps][cin] bf16, or NULL */
+  void* dst_dgrad;   /* [plane][cin][taps][cout] bf16 (taps flipped), or NULL */
+  int cout, cin, taps;
+} can_pack_item;
+int can_pack_conv_weights_multi(const can_pack_item* items, int n, int nsplit, void* stream);
 /* conv{1,2,3,6}_2.weight -> stacked [plane][2048][512] in (channel-chunk, scale, channel) row
  * order for CAN_MODE_CTX (model/CANNet.py:19,21,23,25).                                      */
 int can_pack_ctx_w2(const float* w1_2, const float* w2_2, const float* w3_2, const float* w6_2, void* dst,

@@ -48,7 +48,7 @@ def main():
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 10
     tag = " ".join(f"{k[9:]}={os.environ[k]}" for k in ("CAN_B200_DBG", "CAN_B200_HALO", "CAN_B200_CTAS", "CAN_B200_STAGES",
-                                                       "CAN_B200_BN", "CAN_B200_TMASTORE") if k in os.environ)
+                                                       "CAN_B200_BN", "CAN_B200_TMASTORE", "CAN_B200_PAIR") if k in os.environ)
     print(f"{Cin}->{Cout} {H}x{W} N={N} {mode} [{tag}]: {ms * 1e3:.1f} us  ({2 * 9 * Cin * Cout * N * H * W / ms / 1e9:.0f} TF)")
 
 

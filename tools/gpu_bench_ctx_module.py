@@ -13,14 +13,21 @@ sys.path.insert(0, os.path.join(ROOT, "can-distributed-pytorch_b200"))
 from can_b200 import ops  # noqa: E402
 
 
-def timeit(fn, iters=10):
+def timeit(fn, iters=20):
+    """Device time of fn(): captured once into a CUDA graph and replayed (the real step runs inside a graph; eager
+    timing of a 5-launch chain of ~10 us kernels would measure the Python / ctypes launch path instead)."""
     for _ in range(3):
         fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        fn()
+    g.replay()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(iters):
-        fn()
+        g.replay()
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / iters * 1e-3
