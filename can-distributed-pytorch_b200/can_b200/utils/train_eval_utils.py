@@ -75,6 +75,15 @@ class FusedTrainer:
         model._wcache.invalidate()
         if self.world > 1:  # identical initial weights on every rank (train.py:104-114 / DDP broadcast)
             dist.broadcast(self.arena, src=0, group=self.pg)
+            # NCCL's all-reduce kernels run next to backward.  They cannot share an SM with this library's one-CTA-per-SM
+            # kernels, so CAN_B200_DP_RESERVE_SMS = k makes those kernels launch on SMs - k.  Default 0: measured at 2 GPUs
+            # (three interleaved 40-step runs each) 8.53 ms per step with k = 0, 8.56 ms with k = 4 -- NCCL takes more than
+            # a handful of SMs, and giving up enough of them costs more than the interference.
+            if dev.type == "cuda" and "CAN_B200_CTAS" not in os.environ:
+                reserve = int(os.environ.get("CAN_B200_DP_RESERVE_SMS", "0"))
+                sms = torch.cuda.get_device_properties(dev).multi_processor_count
+                if 0 < reserve < sms:
+                    os.environ["CAN_B200_CTAS"] = str(sms - reserve)
         # Single-GPU steps of a fixed input shape are replayed from a CUDA graph after two eager steps: a step is
         # ~120 kernel launches (~2.4 ms of host time), which a loop that reads the loss back every step would
         # otherwise pay on the critical path.  CAN_B200_GRAPH=0 keeps every step eager.

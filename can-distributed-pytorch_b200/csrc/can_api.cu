@@ -74,6 +74,19 @@ int env_int(const char* name, int dflt) {
 
 constexpr int kMaxSmem = 232448;  // 227 KB opt-in limit per CTA on sm_100
 
+// SMs the one-CTA-per-SM kernels may fill: all of them, or CAN_B200_CTAS when set (the data-parallel trainer can leave a
+// few to NCCL's all-reduce kernels, CAN_B200_DP_RESERVE_SMS; measured neutral to slightly negative at 2 GPUs, default off).
+int avail_sms() {
+  static int sm_count = 0;
+  if (!sm_count) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0) sm_count = 148;
+  }
+  const int e = env_int("CAN_B200_CTAS", 0);
+  return e > 0 && e < sm_count ? e : sm_count;
+}
+
 // extra tensor maps of MODE_CTX2 (interpolation matrix, per-image tables); other modes pass copies of tmA
 thread_local const CUtensorMap* g_tmW = nullptr;
 thread_local const CUtensorMap* g_tmT = nullptr;
@@ -212,23 +225,25 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   pl.swap64 = (nsplit == 1 && taps == 9 && Cin == 64 && Cout == 64 && env_int("CAN_B200_WGSWAP", 1) != 0) ? 1 : 0;
   if (pl.swap64) {
     pl.tap_groups = 1;
-    int ks = pl.total_patches < 148 ? pl.total_patches : 148;
+    const int sms = avail_sms();
+    int ks = pl.total_patches < sms ? pl.total_patches : sms;
     pl.per = (pl.total_patches + ks - 1) / ks;
     pl.ksplit = (pl.total_patches + pl.per - 1) / pl.per;
     return pl;
   }
   const int tiles = pl.m_tiles * pl.n_tiles * pl.tap_groups;
   // split-K factor from a two-term cost model: MMA time at the wave efficiency of tiles*c CTAs on
-  // 148 SMs (one CTA per SM) + the fp32 partial tiles every split writes and the reduction re-reads
+  // the available SMs (one CTA per SM) + the fp32 partial tiles every split writes and the reduction re-reads
   // (measured: 11 splits of the 1024->512 layer wrote 155 MB = a third of that kernel's time).
   int ks = 1;
   double best = 1e30;
   const double flops = 2.0 * taps * static_cast<double>(Cin) * Cout * N * H * W;
   const double wbytes = 8.0 * taps * static_cast<double>(Cin) * Cout;  // 4 B written + 4 B read per split
+  const int sms = avail_sms();
   for (int c = 1; c <= 160 && c <= pl.total_patches; ++c) {
     const int ctas = tiles * c;
-    const int waves = (ctas + 147) / 148;
-    const double eff = static_cast<double>(ctas) / (148.0 * waves);
+    const int waves = (ctas + sms - 1) / sms;
+    const double eff = static_cast<double>(ctas) / (static_cast<double>(sms) * waves);
     const double cost = flops / (1.1e15 * eff) + c * wbytes / 4.5e12 + 1.5e-6 * waves;
     if (cost < best - 1e-12) {
       best = cost;
@@ -288,25 +303,14 @@ int make_act_tmap_groups(CUtensorMap* m, const void* base, int coff, int C, int 
 
 int launch_ctx_gemv(const float* Wm, const float* in, long long in_ns, long long in_ps, long long in_js,
                     const float* add, float* out, int N, cudaStream_t st) {
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(ctx_pos_gemv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 36 * 512 * 4);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(ctx_pos_gemv)");
-    attr = true;
-  }
-  if (env_int("CAN_B200_CTXGEMM", 1) != 0) {
-    // all images of a scale as one GEMM (a weight slab is read once per 32 positions, not once per image)
-    const int pt = N >= 8 ? 64 : 32;   // positions per tile
-    int tiles = 0;
-    const int SS[4] = {1, 2, 3, 6};
-    for (int j = 0; j < 4; ++j) tiles += ((N * SS[j] * SS[j] + pt - 1) / pt) * 8;
-    if (pt == 64) ctx_pos_gemm_kernel<64><<<tiles, 256, 0, st>>>(Wm, in, in_ns, in_ps, in_js, add, out, N);
-    else ctx_pos_gemm_kernel<32><<<tiles, 256, 0, st>>>(Wm, in, in_ns, in_ps, in_js, add, out, N);
-    CAN_CHECK_LAUNCH("ctx_pos_gemm");
-    return 0;
-  }
-  ctx_pos_gemv_kernel<<<dim3(32, 4, N), 256, 9 * 512 * 4, st>>>(Wm, in, in_ns, in_ps, in_js, add, out);
-  CAN_CHECK_LAUNCH("ctx_pos_gemv");
+  // all images of a scale as one GEMM (a weight slab is read once per tile of positions, not once per image)
+  const int pt = N >= 8 ? 64 : 32;   // positions per tile
+  int tiles = 0;
+  const int SS[4] = {1, 2, 3, 6};
+  for (int j = 0; j < 4; ++j) tiles += ((N * SS[j] * SS[j] + pt - 1) / pt) * 8;
+  if (pt == 64) ctx_pos_gemm_kernel<64><<<tiles, 256, 0, st>>>(Wm, in, in_ns, in_ps, in_js, add, out, N);
+  else ctx_pos_gemm_kernel<32><<<tiles, 256, 0, st>>>(Wm, in, in_ns, in_ps, in_js, add, out, N);
+  CAN_CHECK_LAUNCH("ctx_pos_gemm");
   return 0;
 }
 
@@ -316,8 +320,7 @@ void launch_pack(const float* w, __nv_bfloat16* fwd, __nv_bfloat16* dgrad, int c
   const dim3 grid(cin / 32, cout / 32);
   const size_t smem = 32 * (32 * taps + 1) * sizeof(float);
   if (taps == 9) pack_conv_weight_kernel_v3<9><<<grid, 256, smem, st>>>(w, fwd, dgrad, cout, cin, nsplit);
-  else if (taps == 1) pack_conv_weight_kernel_v3<1><<<grid, 256, smem, st>>>(w, fwd, dgrad, cout, cin, nsplit);
-  else pack_conv_weight_kernel_v2<<<grid, 256, smem, st>>>(w, fwd, dgrad, cout, cin, taps, nsplit);
+  else pack_conv_weight_kernel_v3<1><<<grid, 256, smem, st>>>(w, fwd, dgrad, cout, cin, nsplit);
 }
 
 }  // namespace
@@ -436,15 +439,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   // persistent CTAs: one per SM (or fewer when there are fewer tiles), striding over the tile list
   p.n_tiles = a->Cout / bn;
   p.num_tiles = p.tiles_x * p.tiles_y * a->N * p.n_tiles;
-  static int sm_count = 0;
-  if (!sm_count) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
-      sm_count = 148;
-  }
-  const int ctas_env = env_int("CAN_B200_CTAS", 0);
-  int ctas = ctas_env > 0 ? ctas_env : sm_count;
+  int ctas = avail_sms();
   if (ctas > p.num_tiles) ctas = p.num_tiles;
   dim3 grid(ctas);
   const int so = a->stages > 0 ? a->stages : env_int("CAN_B200_STAGES", 0);
@@ -700,7 +695,10 @@ int can_ctx_pool_fwd(const void* fv, int64_t fv_plane, int nsplit, int cs, int c
   if (cs % 2 || coff % 2) return fail(-3, "ctx_pool_fwd: cs/coff must be even");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   float* R = static_cast<float*>(ws);
-  if (cs % 4 == 0 && coff % 4 == 0 && W <= 16384 && H <= 65535) {
+  // TMA-streamed rows kernel whenever the channel window is 16-byte aligned (always, from this package); the plain
+  // per-row kernel otherwise
+  const bool aligned16 = cs % 8 == 0 && coff % 8 == 0 && fv_plane % 8 == 0 && (reinterpret_cast<uintptr_t>(fv) & 15) == 0;
+  if (aligned16 && W <= 16384 && H <= 65535) {
     // segment table of a row: window boundaries (sorted, unique) and the windows containing each segment
     PoolSegments seg;
     memset(&seg, 0, sizeof(seg));
@@ -729,11 +727,8 @@ int can_ctx_pool_fwd(const void* fv, int64_t fv_plane, int nsplit, int cs, int c
         if (seg.bound[sgi] >= ws12[w12] && seg.bound[sgi + 1] <= we12[w12]) m |= 1u << w12;
       seg.mask[sgi] = static_cast<unsigned short>(m);
     }
-    const int smem = (W + 15) & ~15;  // per-x segment ids
-    const bool aligned16 = cs % 8 == 0 && coff % 8 == 0 && fv_plane % 8 == 0 &&
-                           (reinterpret_cast<uintptr_t>(fv) & 15) == 0;
-    if (aligned16 && env_int("CAN_B200_K1", 3) == 3) {
-      // TMA-streamed version: persistent CTAs, producer warp + two sets of 8 consumer warps
+    {
+      // persistent CTAs, producer warp + two sets of 8 consumer warps
       const int smem3 = pool_rows_smem_bytes(W);
       static thread_local bool attr_done = false;
       if (!attr_done) {
@@ -742,9 +737,7 @@ int can_ctx_pool_fwd(const void* fv, int64_t fv_plane, int nsplit, int cs, int c
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(ctx_pool_rows)");
         attr_done = true;
       }
-      int dev = 0, sms = 0;
-      cudaGetDevice(&dev);
-      if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+      const int sms = avail_sms();
       const int NH = N * H;
       const int ctas = NH < sms ? NH : sms;
       CUtensorMap tm;
@@ -756,9 +749,6 @@ int can_ctx_pool_fwd(const void* fv, int64_t fv_plane, int nsplit, int cs, int c
       int rc = make_tmap(&tm, static_cast<const __nv_bfloat16*>(fv) + coff, 5, dims, str, box, false);
       if (rc) return rc;
       ctx_pool_rows_kernel_v3<<<ctas, 544, smem3, st>>>(tm, nsplit, R, NH, W, seg);
-    } else {
-      ctx_pool_rows_kernel_v2<<<dim3(H, N), 256, smem, st>>>(static_cast<const __nv_bfloat16*>(fv), fv_plane, nsplit,
-                                                             cs, coff, R, H, W, seg, env_int("CAN_B200_DBG", 0));
     }
   } else {
     ctx_pool_rows_kernel<<<dim3(H, N), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(fv), fv_plane, nsplit, cs, coff,

@@ -63,104 +63,7 @@ bias_grad_kernel_v2(const __nv_bfloat16* __restrict__ dz, long long plane, int n
   }
 }
 
-// grad[co][ci][tap] (parameter layout) = (accumulate ? grad : 0) + alpha * sum_s ws[s][tap][co][ci]
-// grid (cin/32, cout), block 32*taps: coalesced reads per tap, transposed through shared memory,
-// coalesced 32*taps-float write.
-__global__ void wgrad_reduce_kernel_v2(const float* __restrict__ ws, float* __restrict__ grad, int splits, int taps,
-                                       int cout, int cin, int accumulate, float alpha) {
-  __shared__ float s_t[32 * 9];
-  const int co = blockIdx.y, ci0 = blockIdx.x * 32;
-  const int c = threadIdx.x & 31, tap = threadIdx.x >> 5;
-  const long long slab = static_cast<long long>(taps) * cout * cin;
-  const float* src = ws + (static_cast<long long>(tap) * cout + co) * cin + ci0 + c;
-  float acc = 0.f;
-  int sp = 0;
-  for (; sp + 4 <= splits; sp += 4) {  // four independent loads in flight
-    const float a0 = src[(sp + 0) * slab], a1 = src[(sp + 1) * slab], a2 = src[(sp + 2) * slab],
-                a3 = src[(sp + 3) * slab];
-    acc += (a0 + a1) + (a2 + a3);
-  }
-  for (; sp < splits; ++sp) acc += src[sp * slab];
-  s_t[c * taps + tap] = acc;
-  __syncthreads();
-  float* g = grad + (static_cast<long long>(co) * cin + ci0) * taps + threadIdx.x;
-  *g = (accumulate ? *g : 0.f) + alpha * s_t[threadIdx.x];
-}
-
-// Pack one conv weight [cout][cin][taps] fp32 into the K-major bf16 planes of BOTH GEMM
-// orientations in one pass (either destination may be null):
-//   fwd  [pl][co][tap][ci]           dgrad [pl][ci][taps-1-tap][co]
-// grid (cin/32, cout/32); block 256.  Reads are contiguous runs of 32*taps floats per output
-// channel; writes are 64-byte runs.
-__global__ void __launch_bounds__(256)
-pack_conv_weight_kernel_v2(const float* __restrict__ w, __nv_bfloat16* __restrict__ fwd,
-                           __nv_bfloat16* __restrict__ dgrad, int cout, int cin, int taps, int nsplit) {
-  extern __shared__ float s_w[];  // [32 co][32*taps + 1]
-  const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 32;
-  const int row = 32 * taps + 1;
-  // four independent loads in flight per thread (a load-then-store loop would serialise on the
-  // memory latency: in-order issue stalls at the first dependent store)
-  const int per_row = 32 * taps, tot = 32 * per_row;
-  for (int i0 = threadIdx.x; i0 < tot; i0 += 1024) {
-    float v[4];
-    int dst[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int i = i0 + u * 256;
-      const int r = i / per_row, o = i - r * per_row;
-      dst[u] = r * row + o;
-      v[u] = (i < tot) ? __ldg(w + (static_cast<long long>(co0 + r) * cin + ci0) * taps + o) : 0.f;
-    }
-#pragma unroll
-    for (int u = 0; u < 4; ++u)
-      if (i0 + u * 256 < tot) s_w[dst[u]] = v[u];
-  }
-  __syncthreads();
-  const long long total = static_cast<long long>(cout) * cin * taps;
-  // eight consecutive K-elements per thread -> one 16-byte store per plane
-  if (fwd) {
-    for (int idx = threadIdx.x; idx < 32 * taps * 4; idx += 256) {
-      const int qd = idx & 3, rt = idx >> 2;
-      const int r = rt / taps, tap = rt - r * taps;
-      float v[8];
-#pragma unroll
-      for (int e = 0; e < 8; ++e) v[e] = s_w[r * row + (qd * 8 + e) * taps + tap];
-      __nv_bfloat16* d = fwd + (static_cast<long long>(co0 + r) * taps + tap) * cin + ci0 + qd * 8;
-      for (int pl = 0; pl < nsplit; ++pl) {
-        uint4 q;
-        q.x = pack_bf16x2(v[0], v[1]);
-        q.y = pack_bf16x2(v[2], v[3]);
-        q.z = pack_bf16x2(v[4], v[5]);
-        q.w = pack_bf16x2(v[6], v[7]);
-        *reinterpret_cast<uint4*>(d + pl * total) = q;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] -= bf16_round(v[e]);
-      }
-    }
-  }
-  if (dgrad) {
-    for (int idx = threadIdx.x; idx < 32 * taps * 4; idx += 256) {
-      const int qd = idx & 3, rt = idx >> 2;
-      const int ci = rt / taps, tap = rt - ci * taps;
-      float v[8];
-#pragma unroll
-      for (int e = 0; e < 8; ++e) v[e] = s_w[(qd * 8 + e) * row + ci * taps + tap];
-      __nv_bfloat16* d = dgrad + (static_cast<long long>(ci0 + ci) * taps + (taps - 1 - tap)) * cout + co0 + qd * 8;
-      for (int pl = 0; pl < nsplit; ++pl) {
-        uint4 q;
-        q.x = pack_bf16x2(v[0], v[1]);
-        q.y = pack_bf16x2(v[2], v[3]);
-        q.z = pack_bf16x2(v[4], v[5]);
-        q.w = pack_bf16x2(v[6], v[7]);
-        *reinterpret_cast<uint4*>(d + pl * total) = q;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] -= bf16_round(v[e]);
-      }
-    }
-  }
-}
-
-// Third-generation reduction of the split-K partials (same contract as wgrad_reduce_kernel_v2):
+// Reduction of the split-K partials into the parameter layout:
 //   grad[co][ci][tap] = (accumulate ? grad : 0) + alpha * sum_s ws[s][tap][co][ci]
 // grid (ceil(cin/128), cout), block 32*taps: every thread owns four consecutive ci of one tap (16-byte loads,
 // up to four splits in flight), the block transposes 128 ci x taps through shared memory and writes
@@ -202,8 +105,10 @@ __global__ void wgrad_reduce_kernel_v3(const float* __restrict__ ws, float* __re
   for (int j = threadIdx.x; j < n; j += blockDim.x) g[j] = (accumulate ? g[j] : 0.f) + alpha * s_t[j];
 }
 
-// Third-generation weight packing (same contract as pack_conv_weight_kernel_v2): all loads of a thread are
-// issued before the first dependent shared-memory store (the v2 loop paid the memory latency nine times).
+// Pack one conv weight [cout][cin][taps] fp32 into the K-major bf16 planes of BOTH GEMM orientations in one pass
+// (either destination may be null):   fwd [pl][co][tap][ci]     dgrad [pl][ci][taps-1-tap][co]
+// Tile = 32 cin x 32 cout (grid (cin/32, cout/32) for the single-weight kernel), block 256; all loads of a thread are
+// issued before the first dependent shared-memory store (a load-store loop paid the memory latency nine times).
 template <int TAPS>
 __device__ __forceinline__ void pack_conv_weight_tile(const float* __restrict__ w, __nv_bfloat16* __restrict__ fwd,
                                                       __nv_bfloat16* __restrict__ dgrad, int cout, int cin, int nsplit,
@@ -353,93 +258,11 @@ struct PoolSegments {
   unsigned short mask[26];
 };
 
-// K1 stage A (second generation): row sums of fv over the 12 x-windows.  One CTA per (row y, image
-// n); 256 threads = 128 channel groups (4 channels, one 8-byte load) x 2 pixel lanes (adjacent
-// threads, combined with one shuffle); eight loads in flight per thread.  A pixel adds to ONE
-// running segment sum; a finished segment is added to the windows that contain it.  No serial
-// prologue (a per-CTA sort of the boundaries by one thread cost more than streaming the row).
-// fv is read exactly once.   R[n][y][12][512] fp32
-__global__ void __launch_bounds__(256, 3)
-ctx_pool_rows_kernel_v2(const __nv_bfloat16* __restrict__ fv, long long fv_plane, int nsplit, int cs, int coff,
-                        float* __restrict__ R, int H, int W, const __grid_constant__ PoolSegments seg, int dbg) {
-  extern __shared__ unsigned char s_segid[];      // [W] segment index of every x
-  __shared__ unsigned short s_segmask[26];
-  if (threadIdx.x < 26) s_segmask[threadIdx.x] = seg.mask[threadIdx.x];
-  for (int x = threadIdx.x; x < W; x += 256) {
-    int sgi = 0;
-#pragma unroll
-    for (int b = 1; b < 25; ++b) sgi += (b < seg.nseg && x >= seg.bound[b]) ? 1 : 0;
-    s_segid[x] = static_cast<unsigned char>(sgi);
-  }
-  __syncthreads();
-  const int y = blockIdx.x, n = blockIdx.y;
-  const int cg = threadIdx.x >> 1, xl = threadIdx.x & 1;
-  const __nv_bfloat16* row = fv + (static_cast<long long>(n) * H + y) * W * cs + coff + cg * 4;
-  float acc[12][4];
-#pragma unroll
-  for (int k = 0; k < 12; ++k)
-#pragma unroll
-    for (int e = 0; e < 4; ++e) acc[k][e] = 0.f;
-  float cur0 = 0.f, cur1 = 0.f, cur2 = 0.f, cur3 = 0.f;
-  int cur_seg = (xl < W) ? s_segid[xl] : 0;
-  auto flush = [&](int sgi) {
-    const unsigned m = s_segmask[sgi];
-#pragma unroll
-    for (int k = 0; k < 12; ++k) {
-      if (m & (1u << k)) {
-        acc[k][0] += cur0;
-        acc[k][1] += cur1;
-        acc[k][2] += cur2;
-        acc[k][3] += cur3;
-      }
-    }
-    cur0 = cur1 = cur2 = cur3 = 0.f;
-  };
-  for (int pl = 0; pl < nsplit; ++pl) {
-    const __nv_bfloat16* rp = row + pl * fv_plane;
-    for (int x0 = xl; x0 < W; x0 += 16) {
-      uint2 q[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int x = x0 + 2 * u;
-        q[u] = (x < W) ? *reinterpret_cast<const uint2*>(rp + static_cast<long long>(x) * cs) : make_uint2(0, 0);
-      }
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int x = x0 + 2 * u;
-        if (x < W) {
-          const int sgi = (dbg & 1) ? cur_seg : s_segid[x];
-          if (sgi != cur_seg) {
-            flush(cur_seg);
-            cur_seg = sgi;
-          }
-          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q[u]);
-          cur0 += __low2float(h[0]);
-          cur1 += __high2float(h[0]);
-          cur2 += __low2float(h[1]);
-          cur3 += __high2float(h[1]);
-        }
-      }
-    }
-    flush(cur_seg);
-    cur_seg = (xl < W) ? s_segid[xl] : 0;
-  }
-  float* o = R + ((static_cast<long long>(n) * H + y) * 12) * 512 + cg * 4;
-#pragma unroll
-  for (int k = 0; k < 12; ++k) {
-    float4 t;
-    t.x = acc[k][0] + __shfl_xor_sync(0xffffffffu, acc[k][0], 1);
-    t.y = acc[k][1] + __shfl_xor_sync(0xffffffffu, acc[k][1], 1);
-    t.z = acc[k][2] + __shfl_xor_sync(0xffffffffu, acc[k][2], 1);
-    t.w = acc[k][3] + __shfl_xor_sync(0xffffffffu, acc[k][3], 1);
-    if (xl == 0) *reinterpret_cast<float4*>(o + k * 512) = t;
-  }
-}
-
-// K1 stage A (third generation): persistent CTAs stream image rows through shared memory with TMA
+// K1 stage A: persistent CTAs stream image rows through shared memory with TMA
 // (two 256-channel x kPoolChunk-pixel boxes per stage, kPoolStages stages), so ~160 KB per SM are in
-// flight at no register cost -- the register-staged versions above were latency-bound at 1.1 TB/s
-// (31 % warps active, long-scoreboard stalls; profiles/).
+// flight at no register cost -- register-staged versions were latency-bound at 1.1 TB/s
+// (31 % warps active, long-scoreboard stalls; profiles/r01_k1_pool_rows_v3.txt).  Rows a point of the
+// (unaligned) channel window cannot be loaded by TMA fall back to ctx_pool_rows_kernel (can_simple.cuh).
 //   warp 16      producer: runs ahead, throttled by the per-stage "empty" barriers
 //   warps 0-7    consumer set 0: even stages;   warps 8-15  consumer set 1: odd stages
 // In a consumer set thread t owns channels 2t, 2t+1: straight-line code over the 32 staged pixels

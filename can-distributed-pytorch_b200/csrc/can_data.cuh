@@ -132,7 +132,19 @@ __global__ void density_sigma_kernel(const double* __restrict__ pts, int n, int 
   hp.r = static_cast<int>(py);
   hp.c = static_cast<int>(px);
   hp.pad = 0;
-  const bool inside = hp.r < H && hp.c < W && py >= 0.0 && px >= 0.0;
+  // the reference tests int(pt) < size only (truncation toward zero): negative indices address from the far side, as
+  // numpy's `pt2d[int(pt[1]), int(pt[0])] = 1.` does; further out it raises, here the head is skipped
+  bool inside = hp.r < H && hp.c < W && hp.r >= -H && hp.c >= -W;
+  if (hp.r < 0) hp.r += H;
+  if (hp.c < 0) hp.c += W;
+  if (sigma <= 1e-15) {
+    // four or more coincident annotations: scipy's gaussian_filter leaves the impulse untouched for sigma <= 1e-15
+    hp.R = inside ? 0 : -1;
+    hp.coef = 0.0;
+    hp.sum = 1.0;
+    par[i] = hp;
+    return;
+  }
   const int R = static_cast<int>(__dadd_rn(__dmul_rn(4.0, sigma), 0.5));
   hp.R = inside ? R : -1;
   hp.coef = -0.5 / __dmul_rn(sigma, sigma);

@@ -509,87 +509,10 @@ head_bwd_kernel(const float* __restrict__ dout, const __nv_bfloat16* __restrict_
 // out[n][OFF_j + p][r] = (add ? add(n, OFF_j + p, r) : 0) + sum_k Wm[j][r][k] * in(n, OFF_j + p, k)
 //   Wm : [4][512 rows][512] row-major (conv weights as stored -> forward; their transposes -> backward)
 //   in(n, pos, k) = in[n*in_ns + pos*in_ps + j*in_js + k]   (same addressing for `add`)
-// grid (8 row slabs of 64 x 4 position groups, 4 scales, N); 256 threads = 64 rows x 4 quarter-rows of 128 k.
-// One warp per output row: lane l owns k = 4l + 128 i (i < 4) -> every weight load is one coalesced
-// 512-byte request and every shared-memory read is conflict-free; the S2 partial sums are combined
-// with shuffles.  Two rows per warp iteration for instruction-level parallelism.
-template <int S2>
-__device__ __forceinline__ void ctx_gemv_rows(const float* __restrict__ wbase, const float* s_in,
-                                              float* __restrict__ obase, const float* __restrict__ addbase,
-                                              long long in_ps, int row0, int nrows, int lane) {
-  for (int r = 0; r < nrows; r += 2) {
-    const float* w0 = wbase + static_cast<long long>(row0 + r) * 512 + lane * 4;
-    const float* w1 = w0 + 512;
-    float4 wa[4], wb[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      wa[i] = __ldg(reinterpret_cast<const float4*>(w0 + i * 128));
-      wb[i] = __ldg(reinterpret_cast<const float4*>(w1 + i * 128));
-    }
-    float acc0[S2], acc1[S2];
-#pragma unroll
-    for (int p = 0; p < S2; ++p) {
-      float a0 = 0.f, a1 = 0.f;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float4 x4 = *reinterpret_cast<const float4*>(s_in + p * 512 + i * 128 + lane * 4);
-        a0 = fmaf(wa[i].x, x4.x, a0); a0 = fmaf(wa[i].y, x4.y, a0);
-        a0 = fmaf(wa[i].z, x4.z, a0); a0 = fmaf(wa[i].w, x4.w, a0);
-        a1 = fmaf(wb[i].x, x4.x, a1); a1 = fmaf(wb[i].y, x4.y, a1);
-        a1 = fmaf(wb[i].z, x4.z, a1); a1 = fmaf(wb[i].w, x4.w, a1);
-      }
-      acc0[p] = a0;
-      acc1[p] = a1;
-    }
-#pragma unroll
-    for (int p = 0; p < S2; ++p) {
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        acc0[p] += __shfl_xor_sync(0xffffffffu, acc0[p], o);
-        acc1[p] += __shfl_xor_sync(0xffffffffu, acc1[p], o);
-      }
-    }
-    if (lane == 0) {
-#pragma unroll
-      for (int p = 0; p < S2; ++p) {
-        obase[p * 512 + row0 + r] = acc0[p] + (addbase ? addbase[p * in_ps + row0 + r] : 0.f);
-        obase[p * 512 + row0 + r + 1] = acc1[p] + (addbase ? addbase[p * in_ps + row0 + r + 1] : 0.f);
-      }
-    }
-  }
-}
-
-__global__ void __launch_bounds__(256)
-ctx_pos_gemv_kernel(const float* __restrict__ Wm, const float* __restrict__ in, long long in_ns, long long in_ps,
-                    long long in_js, const float* __restrict__ add, float* __restrict__ out) {
-  extern __shared__ float s_in[];  // [positions of this CTA][512]
-  const int SS[4] = {1, 2, 3, 6};
-  const int OFF[4] = {0, 1, 5, 14};
-  const int j = blockIdx.y, n = blockIdx.z;
-  const int slab = blockIdx.x & 7, pg = blockIdx.x >> 3;   // the 36 positions of S=6 are cut into 4 groups of 9
-  if (j < 3 && pg > 0) return;
-  const int cnt = (j == 3) ? 9 : SS[j] * SS[j];
-  const int pos0 = OFF[j] + ((j == 3) ? pg * 9 : 0);
-  const float* gin = in + n * in_ns + pos0 * in_ps + j * in_js;
-  for (int i = threadIdx.x; i < cnt * 128; i += blockDim.x) {
-    const int p = i >> 7, k4 = (i & 127) * 4;
-    *reinterpret_cast<float4*>(s_in + p * 512 + k4) = *reinterpret_cast<const float4*>(gin + p * in_ps + k4);
-  }
-  __syncthreads();
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int row0 = slab * 64 + wid * 8;  // 8 rows per warp
-  const float* wbase = Wm + static_cast<long long>(j) * 512 * 512;
-  float* obase = out + (static_cast<long long>(n) * 50 + pos0) * 512;
-  const float* addbase = add ? add + n * in_ns + pos0 * in_ps + j * in_js : nullptr;
-  if (j == 0) ctx_gemv_rows<1>(wbase, s_in, obase, addbase, in_ps, row0, 8, lane);
-  else if (j == 1) ctx_gemv_rows<4>(wbase, s_in, obase, addbase, in_ps, row0, 8, lane);
-  else ctx_gemv_rows<9>(wbase, s_in, obase, addbase, in_ps, row0, 8, lane);
-}
-
-// Batched version of ctx_pos_gemv_kernel (same operands and result): the positions of ALL images of a scale are the
-// rows of one [N * S^2 x 512] x [512 x 512]^T product, so a weight slab is read once per PT positions instead of once
-// per image (batch 16: 268 MB of L2 reads and 37 us per launch with the per-image kernel).  Used for every batch size,
-// so an image's tables do not depend on the batch it is part of (same k order for every output).  Tile = PT positions x 64 output rows, K in steps of 32 through shared
+// The positions of ALL images of a scale are the rows of one [N * S^2 x 512] x [512 x 512]^T product, so a weight slab
+// is read once per PT positions instead of once per image (batch 16: a per-image GEMV re-read 268 MB from L2 and took
+// 37 us per launch).  Every output is summed in k order whatever the batch size, so an image's tables do not depend on
+// the batch it is part of.  Tile = PT positions x 64 output rows, K in steps of 32 through shared
 // memory (k-major, padded), 256 threads x (PT/16 positions x 4 rows), fp32 FMA in k order.  PT = 64 for large batches:
 // with 2 positions per thread the kernel is bound by its own shared-memory reads (one 16-byte read per 4 FMAs).
 // grid: sum_j ceil(N S_j^2 / PT) * 8 tiles, scale-major.

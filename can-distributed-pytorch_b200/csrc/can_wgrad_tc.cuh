@@ -261,24 +261,6 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
   }
 }
 
-// grad[co][ci][tap] (OIHW) (+)= alpha * sum_s ws[s][tap][co][ci]
-__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ grad, int splits, int taps,
-                                    int cout, int cin, int accumulate, float alpha) {
-  const long long total = static_cast<long long>(cout) * cin * taps;
-  const long long slab = total;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    // i indexes ws-within-split order [tap][co][ci] so reads coalesce
-    const int ci = i % cin;
-    const int co = (i / cin) % cout;
-    const int tap = i / (static_cast<long long>(cin) * cout);
-    float acc = 0.f;
-    for (int s = 0; s < splits; ++s) acc += ws[s * slab + i];
-    float* g = grad + (static_cast<long long>(co) * cin + ci) * taps + tap;
-    *g = (accumulate ? *g : 0.f) + alpha * acc;
-  }
-}
-
 // Weight gradient of a 64 -> 64 3x3 layer (bf16 path), operand roles swapped.
 //
 // With M = Cout = 64 the kernel above spends half of every M = 128 MMA on padding and needs three

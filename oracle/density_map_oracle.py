@@ -2,7 +2,7 @@
 
 Follows ``data_preparation/k_nearest_gaussian_kernel.py:14-54``:
   :37-39  distances to the 3 nearest other heads (scipy KDTree.query(points, k=4): self + 3)
-  :43-47  a unit impulse at (int(row), int(col)); heads outside the image are skipped
+  :43-47  a unit impulse at (int(row), int(col)); heads past the far edges are skipped, negative indices wrap (numpy)
   :48-51  sigma = 0.1 * (d1 + d2 + d3)   (one head only: sigma = mean(image shape) / 4)
   :52     density += scipy.ndimage.gaussian_filter(impulse, sigma, mode='constant')   (float32 image, heads in order)
 
@@ -29,6 +29,8 @@ def knn_sigma(points, shape):
 
 
 def kernel1d(sigma):
+    if sigma <= 1e-15:   # scipy's gaussian_filter skips axes with sigma <= 1e-15: the impulse stays an impulse
+        return np.ones(1), 0
     radius = int(4.0 * float(sigma) + 0.5)
     x = np.arange(-radius, radius + 1)
     phi = np.exp(-0.5 / (sigma * sigma) * x ** 2)
@@ -44,9 +46,14 @@ def density_map(points, shape):
         return density
     sig = knn_sigma(points, shape)
     for (c, r), s in zip(points, sig):
-        ri, ci = int(r), int(c)
+        ri, ci = int(r), int(c)          # truncation toward zero, as the reference's int(pt[..])
         if not (ri < H and ci < W):
             continue
+        # negative indices address from the far side (numpy semantics of `pt2d[int(pt[1]), int(pt[0])] = 1.`, :44);
+        # beyond that the reference raises IndexError
+        if ri < -H or ci < -W:
+            raise IndexError("annotation outside the image by more than its size")
+        ri, ci = ri % H, ci % W
         w, R = kernel1d(s)
         y0, y1 = max(ri - R, 0), min(ri + R, H - 1)
         x0, x1 = max(ci - R, 0), min(ci + R, W - 1)

@@ -39,6 +39,13 @@ def main():
         pts = np.stack([rng.random(n) * (w + (4 if name == "edge" else 0)), rng.random(n) * (h + (4 if name == "edge" else 0))], 1)
         out[name + ".points"], out[name + ".shape"] = pts, np.array([h, w])
         out[name + ".density"] = gaussian_filter_density([h, w], pts)
+    # edge cases of the reference's own arithmetic: (a) slightly negative coordinates -- int() truncates toward zero, so
+    # (-0.5, .) lands on index 0 and (-3.2, .) on index -3 = the third row / column from the far side (numpy indexing);
+    # (b) four coincident annotations -- sigma = 0, for which scipy's gaussian_filter returns the impulse unchanged
+    pts = np.array([[-0.5, 10.2], [20.7, -0.3], [-3.2, 30.0], [40.0, -2.6], [25.0, 25.0], [50.5, 12.5], [50.5, 12.5],
+                    [50.5, 12.5], [50.5, 12.5], [60.0, 40.0]])
+    out["wrap.points"], out["wrap.shape"] = pts, np.array([48, 64])
+    out["wrap.density"] = gaussian_filter_density([48, 64], pts)
     np.savez_compressed(os.path.join(HERE, "density_golden.npz"), **out)
     print("wrote", {k: v.shape for k, v in out.items() if k.endswith("density")})
 

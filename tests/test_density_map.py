@@ -8,7 +8,7 @@ import torch
 from oracle import density_map_oracle as M
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-CASES = ("sparse", "dense", "edge", "one", "none")
+CASES = ("sparse", "dense", "edge", "one", "none", "wrap")
 
 
 @pytest.fixture(scope="module")

@@ -34,8 +34,8 @@ def main():
             total[op] += 1
     print(f"# {os.path.relpath(SO, ROOT)}: Blackwell opcodes per kernel (cuobjdump -sass)")
     print("# total: " + ", ".join(f"{k} {v}" for k, v in sorted(total.items())))
-    multicast = sum(v for k, v in total.items() if "MULTICAST" in k)
-    print(f"# TMA multicast loads in the library: {multicast}")
+    multicast = sum(v for k, v in total.items() if k.startswith("UTMALDG") and "MULTICAST" in k)
+    print(f"# TMA loads with multicast in the library: {multicast}  (UTCBAR...MULTICAST = tcgen05.commit arriving on both CTAs of a pair)")
     for fn, c in per.items():
         if c:
             print(f"{fn}: " + ", ".join(f"{k} {v}" for k, v in sorted(c.items())))
