@@ -352,7 +352,7 @@ def main():
             traffic = json.load(open(tpath)).get(f"batch{B}")
     all_tf = (k_flop / 1e12) / (k_ms * 1e-3) if k_ms > 0 else 0.0
     step_tf = (k_flop / npass / 1e12) / (ms / args.steps * 1e-3)   # all tensor FLOPs of a step / the timed step
-    roofline = {"bound": "tensor", "kernel": "conv_tc_kernel<256,1,STORE> 512->512 3x3 @96x128 (tcgen05 implicit GEMM)",
+    roofline = {"bound": "tensor", "kernel": "conv_tc_kernel<256,1,STORE,PAIR> 512->512 3x3 @96x128 (tcgen05 cta_group::2 implicit GEMM, M=256 per pair)",
                 "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf if peak_tf else None,
                 "peak_kind": peak_kind, "frac_burst": achieved / peak_burst, "frac_sustained": achieved / peak_sust,
                 "traffic": traffic, "peak_source": peak_src,

@@ -63,6 +63,7 @@ _SIGNATURES = {
     "can_mse_count_static_max_images": (C.c_int, []),
     "can_mse_count_fwd_bwd_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 4
                                      + [C.c_float, C.c_void_p]),
+    "can_zero_ranges": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.c_int, C.c_void_p]),
     "can_sgd_momentum_step": (C.c_int, [C.c_void_p] * 3 + [C.c_int64, C.c_float, C.c_float, C.c_float, C.c_int,
                                                           C.c_void_p]),
     "can_conv_wgrad_workspace_bytes": (C.c_int64, [C.c_int] * 7),

@@ -263,6 +263,14 @@ def mse_count(et: torch.Tensor, gt: torch.Tensor, want_grad: bool, grad_scale: f
     return loss, ce, cg, grad
 
 
+def zero_ranges(base: torch.Tensor, ranges):
+    """base[a:a + n] = 0 for up to 32 (a, n) slices of a flat fp32 tensor, one launch."""
+    offs = (C.c_int64 * len(ranges))(*[a for a, _ in ranges])
+    cnts = (C.c_int32 * len(ranges))(*[n for _, n in ranges])
+    check(lib().can_zero_ranges(base.data_ptr(), offs, cnts, len(ranges), _stream()), "zero_ranges")
+    _count()
+
+
 def sgd_momentum_step(p, g, buf, lr, momentum=0.95, grad_scale=1.0, first=False):
     check(lib().can_sgd_momentum_step(p.data_ptr(), g.data_ptr(), buf.data_ptr(), p.numel(), lr, momentum, grad_scale,
                                       int(first), _stream()), "sgd_momentum_step")

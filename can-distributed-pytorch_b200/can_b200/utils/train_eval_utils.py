@@ -57,6 +57,7 @@ class FusedTrainer:
         self.loss_slot = self.garena[0:1]
         self.hdr = HDR          # the update skips the header
         self.gviews = []
+        self.zero_slices = []   # (offset, count) of the gradients backward accumulates into: biases and the 1x1 head
         with torch.no_grad():
             for i, p in enumerate(params):
                 n = p.numel()
@@ -64,6 +65,8 @@ class FusedTrainer:
                 view.copy_(p)
                 p.data = view           # parameters now live in the arena (state_dict unchanged)
                 self.gviews.append(self.garena[offs[i]:offs[i] + n].view_as(p))
+                if p.dim() == 1 or p.shape[0] == 1:
+                    self.zero_slices.append((offs[i], n))
         self.total = total
         # buckets in the order backward produces them: backend+head, ctx, conv4_x, the rest of the frontend
         # (1.7 M floats + the loss slot: all that is left to exchange when backward ends)
@@ -154,7 +157,7 @@ class FusedTrainer:
         for i, tag in enumerate(self.DP_TAGS):
             with torch.cuda.graph(graphs[i], pool=pool):
                 if i == 0:
-                    self.garena.zero_()
+                    ops.zero_ranges(self.garena, self.zero_slices)
                     out, saved = engine.forward(m, xs, m.nsplit, save=True)
                     loss, _, _, grad = ops.mse_count(out, gs, want_grad=True, loss_out=self.loss_slot)
                     gen = engine.backward_steps(m, saved, grad, grads=self.gviews)
@@ -173,7 +176,9 @@ class FusedTrainer:
     def _step_eager(self, img: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
         m = self.model
         launches0 = ops.LAUNCHES
-        self.garena.zero_()  # bias / head gradients are accumulated with atomics (one 83 MB memset, ~13 us)
+        # bias / head gradients are accumulated with atomics: those slices start at zero; every other gradient is
+        # overwritten by its kernel (the arena was zeroed once, so the alignment padding stays zero)
+        ops.zero_ranges(self.garena, self.zero_slices)
         out, saved = engine.forward(m, img, m.nsplit, save=True)
         # data parallel: the loss goes into the header slot of the gradient arena and is summed over ranks with the last
         # bucket (logged loss = rank-mean of the local sum-losses, reduce_value)

@@ -94,21 +94,32 @@ thread_local const CUtensorMap* g_tmT = nullptr;
 thread_local const CUtensorMap* g_tmO = nullptr;
 thread_local const CUtensorMap* g_tmM = nullptr;   // mask map of the staged epilogue
 
-// cta_group::2 launches: a cluster of two CTAs per pair
+// Extended launch: clusters of `cluster` CTAs (cta_group::2 pairs), and programmatic dependent launch for the kernels
+// that call pdl_wait() before their first global read (CAN_B200_PDL=0 switches it off): inside a step ~100 dependent
+// kernels follow each other, and every one of them spends its first microseconds on barrier set-up and TMEM allocation.
 template <typename K, typename... Args>
-int launch_pair(K kern, dim3 grid, int threads, int smem, cudaStream_t st, const char* what, Args... args) {
+int launch_ex(K kern, dim3 grid, int threads, int smem, cudaStream_t st, const char* what, int cluster, Args... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = dim3(threads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (cluster > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = cluster;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (env_int("CAN_B200_PDL", 0) != 0) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = na;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, args...);
   if (e != cudaSuccess) return cuda_fail(e, what);
   return 0;
@@ -139,13 +150,8 @@ int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p,
     attr_done = true;
     attr_smem = kMaxSmem;
   }
-  if (PAIR)
-    return launch_pair(kern, grid, 128 + 32 * EW, smem, st, "cudaLaunchKernelEx(conv_tc, CTA pairs)", tmA, tmB,
-                       g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA, g_tmO ? *g_tmO : tmA, g_tmM ? *g_tmM : tmA, p);
-  kern<<<grid, 128 + 32 * EW, smem, st>>>(tmA, tmB, g_tmW ? *g_tmW : tmA, g_tmT ? *g_tmT : tmA, g_tmO ? *g_tmO : tmA,
-                                         g_tmM ? *g_tmM : tmA, p);
-  CAN_CHECK_LAUNCH("conv_tc launch");
-  return 0;
+  return launch_ex(kern, grid, 128 + 32 * EW, smem, st, "conv_tc launch", PAIR ? 2 : 1, tmA, tmB, g_tmW ? *g_tmW : tmA,
+                   g_tmT ? *g_tmT : tmA, g_tmO ? *g_tmO : tmA, g_tmM ? *g_tmM : tmA, p);
 }
 
 // HALO variant (bf16 path, small Cin): resident weights + halo activation stages.
@@ -167,9 +173,8 @@ int launch_conv_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUten
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tc halo)");
     attr_done = true;
   }
-  kern<<<grid, 128 + 32 * 8, smem, st>>>(tmA, tmB, tmHalo, tmA, g_tmO ? *g_tmO : tmA, g_tmM ? *g_tmM : tmA, p);
-  CAN_CHECK_LAUNCH("conv_tc(halo) launch");
-  return 0;
+  return launch_ex(kern, grid, 128 + 32 * 8, smem, st, "conv_tc(halo) launch", 1, tmA, tmB, tmHalo, tmA,
+                   g_tmO ? *g_tmO : tmA, g_tmM ? *g_tmM : tmA, p);
 }
 
 template <int BN>
@@ -272,9 +277,7 @@ int launch_wgrad(const CUtensorMap& tmDZ, const CUtensorMap& tmX, WgradTcParams&
     attr_done = true;
   }
   p.ws_tma = g_tmWS ? 1 : 0;
-  kern<<<grid, 192, L::bytes(stages), st>>>(tmDZ, tmX, g_tmWS ? *g_tmWS : tmDZ, p);
-  CAN_CHECK_LAUNCH("wgrad_tc launch");
-  return 0;
+  return launch_ex(kern, grid, 192, L::bytes(stages), st, "wgrad_tc launch", 1, tmDZ, tmX, g_tmWS ? *g_tmWS : tmDZ, p);
 }
 
 int make_act_tmap(CUtensorMap* m, const void* base, int coff, int C, int cs, int64_t plane, int nsplit, int N, int H,
@@ -843,6 +846,22 @@ int can_mse_count_fwd_bwd_static(const float* et, const float* gt, int N, int HW
   return 0;
 }
 
+int can_zero_ranges(float* base, const int64_t* offsets, const int32_t* counts, int n, void* stream) {
+  if (!base || !offsets || !counts || n <= 0 || n > ZeroRanges::kMax)
+    return fail(-1, "zero_ranges: bad arguments (at most %d slices)", ZeroRanges::kMax);
+  ZeroRanges r;
+  memset(&r, 0, sizeof(r));
+  r.n = n;
+  for (int i = 0; i < n; ++i) {
+    if (offsets[i] < 0 || counts[i] < 0) return fail(-2, "zero_ranges: negative offset / count in slice %d", i);
+    r.off[i] = offsets[i];
+    r.count[i] = counts[i];
+  }
+  zero_ranges_kernel<<<n, 256, 0, static_cast<cudaStream_t>(stream)>>>(base, r);
+  CAN_CHECK_LAUNCH("zero_ranges");
+  return 0;
+}
+
 int can_sgd_momentum_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float grad_scale,
                           int first_step, void* stream) {
   if (!p || !g || !buf || n <= 0) return fail(-1, "sgd_momentum_step: bad arguments");
@@ -996,12 +1015,11 @@ int conv_wgrad_impl(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, co
       if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(wgrad_tc_swap64)");
       attr_done = true;
     }
-    wgrad_tc_swap64_kernel<<<pl.ksplit, 192, 2048 + p.stages * stage_b, st>>>(tmDZ, tmX, p);
-    CAN_CHECK_LAUNCH("wgrad_tc_swap64 launch");
-    wgrad_reduce_kernel_t<<<dim3(Cout / 32, Cin), 32 * taps, 0, st>>>(p.ws, grad, pl.ksplit, taps, Cout, Cin, accumulate,
-                                                                      alpha);
-    CAN_CHECK_LAUNCH("wgrad_reduce_t");
-    return 0;
+    rc = launch_ex(wgrad_tc_swap64_kernel, dim3(pl.ksplit), 192, 2048 + p.stages * stage_b, st, "wgrad_tc_swap64 launch", 1,
+                   tmDZ, tmX, p);
+    if (rc) return rc;
+    return launch_ex(wgrad_reduce_kernel_t, dim3(Cout / 32, Cin), 32 * taps, 0, st, "wgrad_reduce_t", 1,
+                     static_cast<const float*>(p.ws), grad, pl.ksplit, taps, Cout, Cin, accumulate, alpha);
   }
   if (pl.T > 1) {  // bf16 path, several taps per CTA
     if (pl.bn == 64) rc = launch_wgrad<64, 1, 3>(tmDZ, tmX, p, grid, st);
@@ -1021,10 +1039,8 @@ int conv_wgrad_impl(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, co
     rc = launch_wgrad<256, 1, 1>(tmDZ, tmX, p, grid, st);
   }
   if (rc) return rc;
-  wgrad_reduce_kernel_v3<<<dim3((Cin + 127) / 128, Cout), 32 * taps, 0, st>>>(p.ws, grad, pl.ksplit, taps, Cout, Cin,
-                                                                              accumulate, alpha);
-  CAN_CHECK_LAUNCH("wgrad_reduce");
-  return 0;
+  return launch_ex(wgrad_reduce_kernel_v3, dim3((Cin + 127) / 128, Cout), 32 * taps, 0, st, "wgrad_reduce", 1,
+                   static_cast<const float*>(p.ws), grad, pl.ksplit, taps, Cout, Cin, accumulate, alpha);
 }
 }  // namespace
 

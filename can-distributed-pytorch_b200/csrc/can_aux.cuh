@@ -71,6 +71,8 @@ bias_grad_kernel_v2(const __nv_bfloat16* __restrict__ dz, long long plane, int n
 __global__ void wgrad_reduce_kernel_v3(const float* __restrict__ ws, float* __restrict__ grad, int splits, int taps,
                                        int cout, int cin, int accumulate, float alpha) {
   __shared__ float s_t[128 * 9];
+  pdl_launch_dependents();
+  pdl_wait();
   const int co = blockIdx.y, ci0 = blockIdx.x * 128;
   const int lane = threadIdx.x & 31, tap = threadIdx.x >> 5;
   const int c4 = lane * 4;

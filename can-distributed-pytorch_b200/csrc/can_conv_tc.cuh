@@ -356,6 +356,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (PAIR) cluster_sync_all();   // the partner's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  // everything above touched no global memory: with programmatic dependent launch it overlaps the previous kernel's tail
+  pdl_launch_dependents();
+  pdl_wait();
 
   if (warp == 0) {
     // ===================== TMA producer =====================

@@ -283,6 +283,15 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
                : "memory");
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start while its predecessor in the
+// stream still runs: its CTAs are scheduled as the predecessor's CTAs finish, run their prologue (barrier init, TMEM
+// allocation, descriptor prefetch) and block in pdl_wait() until the predecessor has completed and its writes are
+// visible.  pdl_wait() must come before the first read of anything an earlier kernel wrote (TMA loads included); it is a
+// no-op for a launch without the attribute.  pdl_launch_dependents() lets the successor be scheduled early.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---------------------------------------------------------------- UMMA descriptors
 // Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
 //   [0,14) start>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [61,64) layout (2 = SWIZZLE_128B)

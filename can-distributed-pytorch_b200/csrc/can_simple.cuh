@@ -382,6 +382,21 @@ sgd_momentum_kernel(float* __restrict__ p, const float* __restrict__ g, float* _
   }
 }
 
+// Zero up to kMax slices of one fp32 buffer in one launch (the bias / head gradient slices of the flat gradient arena:
+// they are accumulated with atomics, everything else in the arena is overwritten every step, so an 83 MB memset per
+// step would write 82.9 MB too many).  blockIdx.x = slice.
+struct ZeroRanges {
+  static constexpr int kMax = 32;
+  int n;
+  long long off[kMax];
+  int count[kMax];
+};
+__global__ void __launch_bounds__(256)
+zero_ranges_kernel(float* __restrict__ base, const __grid_constant__ ZeroRanges r) {
+  float* p = base + r.off[blockIdx.x];
+  for (int i = threadIdx.x; i < r.count[blockIdx.x]; i += blockDim.x) p[i] = 0.f;
+}
+
 // --------------------------------------------------------------------------------
 // backward helpers
 // --------------------------------------------------------------------------------

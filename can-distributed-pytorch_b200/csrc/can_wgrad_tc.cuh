@@ -96,6 +96,8 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();   // (see can_ptx.cuh: the prologue above overlaps the previous kernel's tail)
+  pdl_wait();
 
   if (warp == 0) {
     if (elect_one()) {
@@ -323,6 +325,8 @@ wgrad_tc_swap64_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_launch_dependents();   // (see can_ptx.cuh: the prologue above overlaps the previous kernel's tail)
+  pdl_wait();
 
   if (warp == 0) {
     if (elect_one()) {
@@ -422,6 +426,8 @@ wgrad_tc_swap64_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_co
 __global__ void wgrad_reduce_kernel_t(const float* __restrict__ ws, float* __restrict__ grad, int splits, int taps,
                                       int cout, int cin, int accumulate, float alpha) {
   __shared__ float s_t[32 * 9];
+  pdl_launch_dependents();
+  pdl_wait();
   const int ci = blockIdx.y, co0 = blockIdx.x * 32;
   const int c = threadIdx.x & 31, tap = threadIdx.x >> 5;
   const long long slab = static_cast<long long>(taps) * cout * cin;

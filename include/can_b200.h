@@ -157,6 +157,11 @@ int can_mse_count_static_max_images(void);
 int can_mse_count_fwd_bwd_static(const float* et, const float* gt, int N, int HW, float* loss, float* cnt_et,
                                  float* cnt_gt, float* grad, float grad_scale, void* stream);
 
+/* Zero n <= 32 slices [offsets[i], offsets[i] + counts[i]) (in floats) of one fp32 buffer in one launch: the gradient
+ * slices that backward accumulates into (biases, head) -- the part of `optimizer.zero_grad()`
+ * (utils/train_eval_utils.py:29) that the fused step still needs; `offsets` / `counts` are HOST arrays.            */
+int can_zero_ranges(float* base, const int64_t* offsets, const int32_t* counts, int n, void* stream);
+
 /* torch.optim.SGD(momentum, dampening 0, no nesterov, wd 0) over a flat fp32 arena
  * (train.py:63,125-126; utils/train_eval_utils.py:52).  g is multiplied by grad_scale first. */
 int can_sgd_momentum_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum,

@@ -51,8 +51,9 @@ def main():
     torch.cuda.synchronize()
     print(f"host enqueue time: {(t1 - t0) / 2 * 1e3:.3f} ms per step")
     ops.PROFILE = []
+    os.environ["CAN_B200_GRAPH_INFER"] = "0"   # per-launch events need the eager wrappers (inference graph off too)
     if tr is not None:
-        tr.use_graph = False   # per-launch events need the eager wrappers
+        tr.use_graph = False
     step()
     torch.cuda.synchronize()
     prof, ops.PROFILE = ops.PROFILE, None
