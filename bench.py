@@ -260,11 +260,26 @@ def main():
 
         from can_b200.utils.train_eval_utils import DevicePrefetcher
 
+        loss_host = [torch.empty(1).pin_memory(), torch.empty(1).pin_memory()]
+        loss_done = [torch.cuda.Event(), torch.cuda.Event()]
+
         def e2e_batches(n):
-            # every step: H2D of that step's pinned-host inputs (on the prefetch stream, overlapped with the
-            # previous step's compute) + D2H read of the step's loss
+            # every step: H2D of that step's pinned-host inputs (on the prefetch stream, overlapped with the previous
+            # step's compute) + D2H read of the step's loss.  The loss of step k is copied to pinned memory
+            # asynchronously and read on the host while step k + 1 is being enqueued (as train_one_epoch reads its finite
+            # flag): every step's loss is read inside the timed region, none of the reads idles the device.
+            k = 0
             for xd, gd in DevicePrefetcher(((x_host, gt_host) for _ in range(n)), dev):
-                yield trainer.step(xd, gd).cpu()
+                loss = trainer.step(xd, gd)
+                loss_host[k & 1].copy_(loss, non_blocking=True)
+                loss_done[k & 1].record()
+                if k > 0:
+                    loss_done[(k - 1) & 1].synchronize()
+                    yield float(loss_host[(k - 1) & 1])
+                k += 1
+            if k > 0:
+                loss_done[(k - 1) & 1].synchronize()
+                yield float(loss_host[(k - 1) & 1])
 
         def step_e2e(n=1):
             for _ in e2e_batches(n):
@@ -287,6 +302,8 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    rank_ms = []   # device time of the last timed region on every rank (N > 1)
+
     def timed(fn, steps):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -297,9 +314,10 @@ def main():
         barrier()
         ms = e0.elapsed_time(e1)
         if world > 1:
-            t = torch.tensor([ms], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t)
+            every = [torch.zeros(1, device=dev) for _ in range(world)]
+            dist.all_gather(every, torch.tensor([ms], device=dev))
+            rank_ms[:] = [float(v) for v in every]
+            ms = max(rank_ms)
         return ms
 
     for _ in range(max(3, args.warmup)):
@@ -310,6 +328,7 @@ def main():
     ms = timed(step_resident, args.steps)
     launches = ops.LAUNCHES
     clocks = sampler.stop()
+    ms_ranks = [v / args.steps for v in rank_ms]
     ips = world * B * args.steps / (ms * 1e-3)
 
     step_e2e(2)
@@ -418,6 +437,7 @@ def main():
             "parity": parity,
             "fp32_path": fp32_path,
             "ranks_in_sync": ranks_in_sync,
+            "ms_per_step_ranks": ms_ranks or None,
             ("final_loss" if wl["train"] else "final_counts_sum"): float(final.sum()),
         }
         if world == 1 and not args.no_cpu_baseline:

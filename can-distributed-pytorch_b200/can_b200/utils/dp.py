@@ -9,6 +9,8 @@ over ranks (DDP semantics) is NOT applied here: it is folded into the fused SGD 
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -22,15 +24,18 @@ class GradBuckets:
         self.arena, self.ranges, self.group = arena, dict(ranges), group
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self._pending = []
+        # diagnostic only (tools/gpu_scale8.sh): ranks run their steps without exchanging anything, which separates the
+        # cost of the exchange from the cost of waiting for the slowest GPU
+        self._nocomm = os.environ.get("CAN_B200_DP_NOCOMM", "0") == "1"
 
     def ready(self, tag: str):
         """Called when the gradients of bucket ``tag`` have been enqueued on the current stream."""
-        if self.world > 1:
+        if self.world > 1 and not self._nocomm:
             a, b = self.ranges[tag]
             self._pending.append(dist.all_reduce(self.arena[a:b], group=self.group, async_op=True))
 
     def reduce_scalar(self, t: torch.Tensor):
-        if self.world > 1:
+        if self.world > 1 and not self._nocomm:
             self._pending.append(dist.all_reduce(t, group=self.group, async_op=True))
 
     def wait(self):
