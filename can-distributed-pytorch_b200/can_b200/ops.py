@@ -219,8 +219,9 @@ def conv_tc(x: Act, wp: torch.Tensor, Cout: int, *, taps=9, dil=1, mode=MODE_STO
     a.ctx_wint, a.ctx_ttab = _ptr(ctx_wint), _ptr(ctx_ttab)
     a.db = _ptr(db)
     _count()
-    with _Prof(2.0 * taps * x.C * Cout * x.N * x.H * x.W, f"conv m{mode} {x.C}->{Cout} t{taps} d{dil} {x.H}x{x.W}"):
-        check(lib().can_conv_tc(C.byref(a), _stream()), "conv_tc")
+    label = f"conv m{mode} {x.C}->{Cout} t{taps} d{dil} {x.H}x{x.W}"
+    with _Prof(2.0 * taps * x.C * Cout * x.N * x.H * x.W, label):
+        check(lib().can_conv_tc(C.byref(a), _stream()), f"conv_tc[{label} N={x.N}]")
 
 
 def ctx_pool(fv: Act, w1: torch.Tensor, w2: torch.Tensor):

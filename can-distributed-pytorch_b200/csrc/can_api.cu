@@ -121,6 +121,7 @@ int launch_ex(K kern, dim3 grid, int threads, int smem, cudaStream_t st, const c
   cfg.attrs = attr;
   cfg.numAttrs = na;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, args...);
+  if (e == cudaSuccess) e = cudaGetLastError();   // (a fault of this launch under CUDA_LAUNCH_BLOCKING=1 shows up here)
   if (e != cudaSuccess) return cuda_fail(e, what);
   return 0;
 }
@@ -748,8 +749,8 @@ int can_ctx_pool_fwd(const void* fv, int64_t fv_plane, int nsplit, int cs, int c
       const uint64_t str[4] = {static_cast<uint64_t>(cs) * 2, static_cast<uint64_t>(W) * cs * 2,
                                static_cast<uint64_t>(nsplit > 1 ? fv_plane : static_cast<int64_t>(NH) * W * cs) * 2,
                                static_cast<uint64_t>(nsplit > 1 ? fv_plane * nsplit : static_cast<int64_t>(NH) * W * cs) * 2};
-      const uint32_t box[5] = {256, kPoolChunk, 1, 1, 1};
-      int rc = make_tmap(&tm, static_cast<const __nv_bfloat16*>(fv) + coff, 5, dims, str, box, false);
+      const uint32_t box[5] = {64, kPoolChunk, 1, 1, 1};
+      int rc = make_tmap(&tm, static_cast<const __nv_bfloat16*>(fv) + coff, 5, dims, str, box, true);
       if (rc) return rc;
       ctx_pool_rows_kernel_v3<<<ctas, 544, smem3, st>>>(tm, nsplit, R, NH, W, seg);
     }

@@ -271,20 +271,22 @@ struct PoolSegments {
 // (independent 4-byte shared-memory reads, two running sums) that flushes the running sums into the
 // windows containing the current segment wherever a window boundary falls.  At the end of a row set 1
 // hands its 12 window sums to set 0 through shared memory (double-buffered, one named barrier per row).
-//   tm: bf16 map {512 ch, W, N*H, nsplit, 1}, box {256, kPoolChunk, 1, 1, 1}, no swizzle
+//   tm: bf16 map {512 ch, W, N*H, nsplit, 1}, box {64, kPoolChunk, 1, 1, 1}, 128B swizzle: a stage is eight
+//       [32 pixels][64 channels] tiles of 4 KB, 16-byte chunk c of pixel p stored at chunk c ^ (p & 7) -- the box shape
+//       every other kernel of this library uses
 //   R[n][y][12][512] fp32
 constexpr int kPoolChunk = 32;    // pixels per stage (32 KB)
 constexpr int kPoolStages = 5;
 constexpr int kPoolXchgBytes = 2 * 12 * 512 * 4;   // set 1 -> set 0 hand-over, two rows
 __host__ __device__ inline int pool_rows_smem_bytes(int W) {
-  return kPoolStages * kPoolChunk * 1024 + kPoolXchgBytes + 8 * ((W + kPoolChunk - 1) / kPoolChunk) + 128;
+  return kPoolStages * kPoolChunk * 1024 + kPoolXchgBytes + 8 * ((W + kPoolChunk - 1) / kPoolChunk) + 1024;
 }
 __global__ void __launch_bounds__(544, 1)
 ctx_pool_rows_kernel_v3(const __grid_constant__ CUtensorMap tm, int nsplit, float* __restrict__ R, int NH, int W,
                         const __grid_constant__ PoolSegments seg) {
   extern __shared__ __align__(128) unsigned char s_raw[];
   constexpr int kChunk = kPoolChunk, kStages = kPoolStages;
-  unsigned char* s_al = s_raw + ((128u - (smem_u32(s_raw) & 127u)) & 127u);   // TMA destinations: 128-byte aligned
+  unsigned char* s_al = s_raw + ((1024u - (smem_u32(s_raw) & 1023u)) & 1023u);   // swizzled TMA tiles: 1024-byte aligned
   __nv_bfloat16* buf = reinterpret_cast<__nv_bfloat16*>(s_al);  // [kStages][2 halves][kChunk][256]
   float* s_xchg = reinterpret_cast<float*>(s_al + kStages * kChunk * 1024);                     // [2][12][512]
   uint32_t* s_endmask = reinterpret_cast<uint32_t*>(s_al + kStages * kChunk * 1024 + kPoolXchgBytes);  // [chunks]
@@ -315,19 +317,27 @@ ctx_pool_rows_kernel_v3(const __grid_constant__ CUtensorMap tm, int nsplit, floa
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5;
+  // A CTA takes a CONTIGUOUS block of rows, so that neighbouring loads share 2 MB pages.  With rows b, b + 148, ... per
+  // CTA almost every TMA load landed in another page, and on a large feature map (>= ~0.5 GiB) whose pages no kernel
+  // had READ yet the first launch ended in an "unspecified launch failure" about once per 30 000 stages -- with this
+  // assignment never in 36 fresh-process runs (profiles/r02_k1_cold_page_fault.txt; cause below the CUDA level not
+  // found).  Every row still gets its own record, so results do not depend on the assignment.
+  const int rows_per_cta = (NH + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  const int row_beg = min(static_cast<int>(blockIdx.x) * rows_per_cta, NH), row_end = min(row_beg + rows_per_cta, NH);
   if (warp == 16) {
     // ---- producer
     if (threadIdx.x == 512) {
       int sg = 0;
       uint32_t ph = 0;
-      for (int rowi = blockIdx.x; rowi < NH; rowi += gridDim.x)
+      for (int rowi = row_beg; rowi < row_end; ++rowi)
         for (int pl = 0; pl < nsplit; ++pl)
           for (int ch = 0; ch < chunks_per_row; ++ch) {
             mbar_wait(&empty_bar[sg], ph ^ 1u);
             __nv_bfloat16* dst = buf + sg * kChunk * 512;
             mbar_expect_tx(&full_bar[sg], kChunk * 1024u);
-            tma_load_5d(dst, &tm, &full_bar[sg], 0, ch * kChunk, rowi, pl, 0);
-            tma_load_5d(dst + kChunk * 256, &tm, &full_bar[sg], 256, ch * kChunk, rowi, pl, 0);
+#pragma unroll
+            for (int g = 0; g < 8; ++g)   // eight 64-channel groups of 32 pixels
+              tma_load_5d(dst + g * kChunk * 64, &tm, &full_bar[sg], g * 64, ch * kChunk, rowi, pl, 0);
             if (++sg == kStages) {
               sg = 0;
               ph ^= 1u;
@@ -340,7 +350,9 @@ ctx_pool_rows_kernel_v3(const __grid_constant__ CUtensorMap tm, int nsplit, floa
   const int set = warp >> 3;                  // 0 or 1
   const int tid = threadIdx.x & 255;
   const int t2 = tid * 2;
-  const int soff = (tid >> 7) * kChunk * 256 + (tid & 127) * 2;
+  // channels 2 tid, 2 tid + 1: group tid >> 5, 16-byte chunk (tid & 31) >> 2 of the pixel's 128-byte row, 4 bytes inside it
+  const int soff = (tid >> 5) * kChunk * 64 + (tid & 3) * 2;   // (in bf16 elements; the chunk is XOR-ed with the pixel below)
+  const int c16 = (tid & 31) >> 2;
   const int lane = threadIdx.x & 31;
   float acc[12][2];
   float cur0 = 0.f, cur1 = 0.f;   // running sums of segment sgi (may span stages)
@@ -358,7 +370,7 @@ ctx_pool_rows_kernel_v3(const __grid_constant__ CUtensorMap tm, int nsplit, floa
   };
   int sg = 0, it = 0, rowpar = 0;
   uint32_t ph = 0;
-  for (int rowi = blockIdx.x; rowi < NH; rowi += gridDim.x, rowpar ^= 1) {
+  for (int rowi = row_beg; rowi < row_end; ++rowi, rowpar ^= 1) {
 #pragma unroll
     for (int k = 0; k < 12; ++k) acc[k][0] = acc[k][1] = 0.f;
     for (int pl = 0; pl < nsplit; ++pl)
@@ -377,7 +389,8 @@ ctx_pool_rows_kernel_v3(const __grid_constant__ CUtensorMap tm, int nsplit, floa
           for (int g = 0; g < kChunk / 8; ++g) {
             __nv_bfloat162 v[8];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) v[u] = *reinterpret_cast<const __nv_bfloat162*>(b + (g * 8 + u) * 256);
+            for (int u = 0; u < 8; ++u)   // pixel g * 8 + u: (pixel & 7) == u
+              v[u] = *reinterpret_cast<const __nv_bfloat162*>(b + (g * 8 + u) * 64 + ((c16 ^ u) << 3));
             if ((em >> (g * 8)) & 0xffu) {
 #pragma unroll
               for (int u = 0; u < 8; ++u) {

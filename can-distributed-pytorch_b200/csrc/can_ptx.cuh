@@ -57,23 +57,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-__device__ __forceinline__ uint64_t global_timer_ns() {
-  uint64_t t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-  return t;
-}
-// Time-bounded wait: a protocol bug traps (-> cudaErrorLaunchFailure) after CAN_WAIT_LIMIT_NS instead of
-// hanging the GPU box (a failed try_wait may itself suspend for an implementation-defined time, so the
-// bound is on wall-clock time, not on the number of polls).
-#ifndef CAN_WAIT_LIMIT_NS
-#define CAN_WAIT_LIMIT_NS 4000000000ull
+// Time-bounded wait: a protocol bug traps (-> cudaErrorLaunchFailure) after ~CAN_WAIT_LIMIT_CYCLES SM cycles instead of
+// hanging the GPU box (a failed try_wait may itself suspend for an implementation-defined time, so the bound is on
+// elapsed time, not on the number of polls).  The clock is the SM's own cycle counter (monotonic for a resident
+// thread; %globaltimer is re-synchronised by the driver).
+#ifndef CAN_WAIT_LIMIT_CYCLES
+#define CAN_WAIT_LIMIT_CYCLES 8000000000ll   // ~4-6 s at 1.3-2 GHz
 #endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
-  const uint64_t t0 = global_timer_ns();
+  const long long t0 = clock64();
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if ((++spins & 0xff) == 0 && global_timer_ns() - t0 > CAN_WAIT_LIMIT_NS) {
+    if ((++spins & 0xff) == 0 && clock64() - t0 > CAN_WAIT_LIMIT_CYCLES) {
 #ifdef CAN_MBAR_DEBUG
       printf("mbar timeout: block %d thread %d bar@%u parity %u\n", blockIdx.x, threadIdx.x, smem_u32(bar), parity);
 #endif
