@@ -272,8 +272,9 @@ def backward_steps(model, saved, grad_out: torch.Tensor, grads=None):
     if grads is None:
         grads = new_grads(model)
     g = grad_out.contiguous().float()
-    # (measured on the power-capped B200s of this pool: 8.18 -> 8.12 ms, i.e. idle SMs were not the limit; opt-in)
-    side = _SideStream(dev, os.environ.get("CAN_B200_SIDE", "0") == "1")
+    # (measured on the power-capped B200s of this pool, three interleaved 40-step runs each: 8.40 -> 8.33 ms per step,
+    # profiles/r02_side_ab.txt; CAN_B200_SIDE=0 keeps everything on one stream)
+    side = _SideStream(dev, os.environ.get("CAN_B200_SIDE", "1") == "1")
 
     # ---- head + backend -----------------------------------------------------------
     hw = model.output_layer.weight.detach().float().reshape(64).contiguous()
@@ -375,6 +376,7 @@ def backward_steps(model, saved, grad_out: torch.Tensor, grads=None):
     if nsplit == 1 and col is None and grads[0].is_contiguous() and os.environ.get("CAN_B200_FIRST_TC", "2") == "2":
         ops.conv_first_wgrad(dz, saved["x"], grads[0])   # straight from the image, into the parameter's layout
     else:
+        side.join()   # this weight gradient runs on the main stream and shares the split-K workspace with the side stream's
         if col is None:
             col = ops.im2col_first(saved["x"], nsplit)
         g0 = torch.empty(64, 64, device=dev, dtype=torch.float32)
