@@ -18,6 +18,7 @@ import os
 import torch
 
 from . import ops
+from .utils import nvtx
 from .ops import (MODE_CTX, MODE_CTX2, MODE_CTX2_BWD, MODE_CTX_BWD, MODE_DFV, MODE_HEAD, MODE_POOL, MODE_STORE,
                   MODE_UNPOOL, Act)
 
@@ -107,6 +108,7 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
         prepack(model, nsplit)
 
     # ---- frontend (CANNet.py:40) -------------------------------------------------
+    nvtx.push("can.fwd.frontend")
     w0, b0 = fr[0]
     col = None
     first_mode = os.environ.get("CAN_B200_FIRST_TC", "2") if nsplit == 1 else "0"
@@ -150,8 +152,10 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
         a = out
         acts.append(a)
     fv = a
+    nvtx.pop()
 
     # ---- contextual module (CANNet.py:42-87) --------------------------------------
+    nvtx.push("can.fwd.context")
     w1s, w2s = _ctx_weights(model)
     w1 = cache.get(("w1",), w1s, lambda: ops.stack_1x1(w1s))
     w2 = cache.get(("w2",), w2s, lambda: ops.stack_1x1(w2s))
@@ -167,7 +171,10 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
         ttab = None
         ops.conv_tc(fv, w2stack, 2048, taps=1, mode=MODE_CTX, out=fi, tabA=tabA, tabB=tabB)
 
+    nvtx.pop()
+
     # ---- backend + head (CANNet.py:89-90) -----------------------------------------
+    nvtx.push("can.fwd.backend")
     a = cat.view(1024, 0)
     bacts = [a]
     density = torch.empty(N, 1, h, w, device=dev, dtype=torch.float32)
@@ -186,6 +193,7 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
             ops.conv_tc(a, wp, cout, dil=2, mode=MODE_STORE, relu=True, bias=bias, out=out)
         a = out
         bacts.append(a)
+    nvtx.pop()
     if save:
         saved.update(acts=acts, args=args, cat=cat, bacts=bacts, pooled=pooled, tabA=tabA, tabB=tabB, ttab=ttab, col=col,
                      nsplit=nsplit)
@@ -277,6 +285,7 @@ def backward_steps(model, saved, grad_out: torch.Tensor, grads=None):
     side = _SideStream(dev, os.environ.get("CAN_B200_SIDE", "1") == "1")
 
     # ---- head + backend -----------------------------------------------------------
+    nvtx.push("can.bwd.backend")
     hw = model.output_layer.weight.detach().float().reshape(64).contiguous()
     dz = ops.head_bwd(g, bacts[6], hw, grads[IDX_HEAD], grads[IDX_HEAD + 1])
     dcat = None
@@ -298,7 +307,9 @@ def backward_steps(model, saved, grad_out: torch.Tensor, grads=None):
             ops.conv_tc(dz, wd, cin, dil=2, mode=MODE_STORE, relu=False, out=ndz)
             dcat = ndz
     side.join()
+    nvtx.pop()
     yield "backend"
+    nvtx.push("can.bwd.context")
 
     # ---- contextual module ----------------------------------------------------------
     w1s, w2s = _ctx_weights(model)
@@ -348,7 +359,9 @@ def backward_steps(model, saved, grad_out: torch.Tensor, grads=None):
     dz = ops.new_act(nsplit, N, h, w, 512, dev)
     ops.conv_tc(D.view(2048, 0), w2d, 512, taps=1, mode=MODE_DFV, relu=False, out=dz, mask=fv, add=dcat.view(512, 0),
                 tabA=dpool, db=grads[2 * 9 + 1])
+    nvtx.pop()
     yield "ctx"
+    nvtx.push("can.bwd.frontend")
 
     # ---- frontend -------------------------------------------------------------------
     for li in range(9, 0, -1):
@@ -370,7 +383,9 @@ def backward_steps(model, saved, grad_out: torch.Tensor, grads=None):
         dz = ndz
         if li == 7:
             side.join()
+            nvtx.pop()
             yield "frontend_hi"   # weights of conv4_1..conv4_3 and the biases next to them are final
+            nvtx.push("can.bwd.frontend")
     # first conv (3 -> 64): K = 27 padded to 64 through an im2col of the image
     col = saved.get("col")
     if nsplit == 1 and col is None and grads[0].is_contiguous() and os.environ.get("CAN_B200_FIRST_TC", "2") == "2":
@@ -384,5 +399,6 @@ def backward_steps(model, saved, grad_out: torch.Tensor, grads=None):
         grads[0].copy_(g0[:, :27].reshape(64, 3, 3, 3))
     # (the bias gradient of conv1_1 was fused into conv1_2's dgrad)
     side.join()
+    nvtx.pop()
     yield "frontend"
     return grads

@@ -21,6 +21,7 @@ from .. import engine, ops
 from .graph_cache import GraphCache
 from .distributed_utils import get_world_size, is_dist_avail_and_initialized, is_main_process, reduce_value
 from .dp import GradBuckets
+from . import nvtx
 
 
 class FusedTrainer:
@@ -132,15 +133,18 @@ class FusedTrainer:
         xs.copy_(img, non_blocking=True)
         gs.copy_(gt, non_blocking=True)
         if self.world == 1:
-            graph.replay()
+            with nvtx.span("can.step.graph"):
+                graph.replay()
             loss = loss.clone()   # the static tensor is rewritten by the next replay
         else:
             for g, tag in zip(graph[:-1], self.DP_TAGS):
-                g.replay()
-                self.buckets.ready(tag)
+                with nvtx.span("can.dp." + tag):
+                    g.replay()
+                    self.buckets.ready(tag)
             self.buckets.wait()
             loss = self.loss_slot / self.world   # rank-mean of the local sum-losses (came with the last bucket)
-            graph[-1].replay()
+            with nvtx.span("can.sgd"):
+                graph[-1].replay()
         ops.LAUNCHES += self._graph_launches
         self.model._wcache.invalidate()   # the replay updated the arena: packed weights are stale for eager callers
         return loss
@@ -182,13 +186,15 @@ class FusedTrainer:
         out, saved = engine.forward(m, img, m.nsplit, save=True)
         # data parallel: the loss goes into the header slot of the gradient arena and is summed over ranks with the last
         # bucket (logged loss = rank-mean of the local sum-losses, reduce_value)
-        loss, _, _, grad = ops.mse_count(out, gt, want_grad=True, loss_out=self.loss_slot if self.world > 1 else None)
+        with nvtx.span("can.loss"):
+            loss, _, _, grad = ops.mse_count(out, gt, want_grad=True, loss_out=self.loss_slot if self.world > 1 else None)
         engine.backward(m, saved, grad, grads=self.gviews, on_ready=self.buckets.ready)
         if self.world > 1:
             self.buckets.wait()
             loss = self.loss_slot / self.world
-        ops.sgd_momentum_step(self.arena[self.hdr:], self.garena[self.hdr:], self.buf[self.hdr:], self.lr, self.momentum,
-                              self.buckets.grad_scale, first=self.first)
+        with nvtx.span("can.sgd"):
+            ops.sgd_momentum_step(self.arena[self.hdr:], self.garena[self.hdr:], self.buf[self.hdr:], self.lr,
+                                  self.momentum, self.buckets.grad_scale, first=self.first)
         self.first = False
         m._wcache.invalidate()  # the arena changed in place: packed weights must be rebuilt
         self._graph_launches = ops.LAUNCHES - launches0   # kernels of one step (what a graph replay launches)
@@ -229,6 +235,7 @@ def train_one_epoch(model, optimizer, train_loader, device, epoch):
         gt_dmap = gt_dmap.to(device, non_blocking=True)
         if on_cuda:
             check_late((step + 1) & 1)   # the flag of step - 1 (its kernels finished while this batch was fetched)
+        nvtx.push("can.step")
         if fused:
             loss = optimizer.step(img, gt_dmap)
         else:
@@ -238,6 +245,7 @@ def train_one_epoch(model, optimizer, train_loader, device, epoch):
             loss.backward()
             loss = reduce_value(loss.detach().reshape(1), average=True)
             optimizer.step()
+        nvtx.pop()
         mean_loss = (mean_loss * step + loss.detach()) / (step + 1)
         if on_cuda:
             ent = flags[step & 1]
