@@ -132,7 +132,8 @@ int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p,
   using L = ConvTcSmem<BN, gemm_planes(NSPLIT, MODE)>;
   constexpr int ctx = MODE;   // (ConvTcSmem::bytes sizes the table region from the mode)
   const int staged_bytes = p.out_stage_bytes + p.mask_bufs * BN * 256;
-  constexpr int kStage = PAIR ? L::kABytes + L::kBBytes / 2 : L::kStageBytes;   // pair: each CTA holds half of B
+  // pair: each CTA holds half of B; the 128-wide pair tiles put two 64-channel k-chunks in a stage (see the kernel)
+  constexpr int kStage = PAIR ? (BN == 128 ? 2 : 1) * (L::kABytes + L::kBBytes / 2) : L::kStageBytes;
   int stages = (kMaxSmem - L::bytes(0, ctx) - staged_bytes) / kStage;
   if (stages > 8) stages = 8;
   if (stages_override > 0 && stages_override < stages) stages = stages_override;
@@ -601,6 +602,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   const int pix_tiles = p.tiles_x * p.tiles_y * a->N;
   const int m = a->mode;
   if (ns == 1 && (bn == 128 || bn == 256) && pix_tiles >= 2 && ctas >= 2 && env_int("CAN_B200_PAIR", 1) != 0 &&
+      (bn == 256 || p.kchunks % 2 == 0) &&
       (m == CAN_MODE_STORE || m == CAN_MODE_POOL || m == CAN_MODE_UNPOOL || m == CAN_MODE_DFV)) {
     CUtensorMap tmBh;   // weight map with a box of half the n-tile (rank r loads rows [n0 + r bn/2, n0 + (r + 1) bn/2))
     const uint64_t K = static_cast<uint64_t>(a->taps) * a->Cin;

@@ -244,6 +244,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmM,
                const ConvTcParams p) {
   constexpr int GS = gemm_planes(NSPLIT, MODE);  // planes that enter the GEMM
+#ifdef CAN_DECOMP
+  constexpr bool kDecomp = true;    // tools/gpu_decomp_mainloop.py: main-loop bring-up bits of CAN_B200_DBG compiled in
+#else
+  constexpr bool kDecomp = false;
+#endif
   using L = ConvTcSmem<BN, GS>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-aligned, still a shared-space pointer
@@ -252,7 +257,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint8_t* s_mask = smem + p.out_stage_bytes;                       // staged mask tiles (p.mask_bufs x BN * 256 B)
   uint8_t* wbase = s_mask + p.mask_bufs * (BN * 256);               // HALO: resident weights
   uint8_t* ring = HALO ? wbase + p.w_bytes : wbase;                // stage ring
-  const int stage_bytes = HALO ? p.halo_stride : GS * (L::kABytes + (PAIR ? L::kBBytes / 2 : L::kBBytes));
+  // KPS = 64-channel k-chunks per pipeline stage.  The 128-wide pair tiles take two: one thread issues the loads and one
+  // the MMAs, each pays a fixed price per stage hand-shake (barrier wait ~90 cycles + issue), and four N = 128 MMAs are
+  // done in 256 cycles -- with one chunk per stage those two threads, not the tensor pipe, set the pace.
+  constexpr int KPS = (PAIR && BN == 128) ? 2 : 1;
+  const int stage_bytes = HALO ? p.halo_stride : GS * KPS * (L::kABytes + (PAIR ? L::kBBytes / 2 : L::kBBytes));
   // single-halo-tile variant: not compiled into the max-unpool kernels (their epilogue sits on the register limit)
   const bool halo1 = HALO && MODE != MODE_UNPOOL && p.halo1;
   uint8_t* tail = ring + stages * stage_bytes;
@@ -293,7 +302,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   };
   auto live_of = [&](int q) { return !PAIR || (2 * (q / p.n_tiles) + rank < pix_tiles); };
   constexpr int kBt = PAIR ? L::kBBytes / 2 : L::kBBytes;   // bytes of one weight tile in this CTA
-  constexpr int kStageSz = GS * (L::kABytes + kBt);         // non-HALO stage: A tile(s) + this CTA's part of B
+  constexpr int kStageSz = GS * KPS * (L::kABytes + kBt);   // non-HALO stage: A tile(s) + this CTA's part of B
   // MODE_CTX2: two extra k-blocks whose A operand is the interpolation matrix Wint[pixel][64 positions]
   // and whose B operands are the per-image tables (-U-side of z, then s) -- see the epilogue.
   constexpr bool kCtx2 = (MODE == MODE_CTX2 || MODE == MODE_CTX2_BWD);
@@ -386,46 +395,88 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
           }
         }
-      } else
+      } else {
+      // ONE thread issues every load, so whatever it spends per k-block is a floor under the whole main loop.  Measured
+      // with loads, MMAs and epilogue all switched off (tools/gpu_decomp_mainloop.py): ~500 cycles per k-block when tap and
+      // chunk came from a division per k-block and every address from a multiply -- as long as the four N = 256 MMAs of a
+      // k-block take, and twice what the N = 128 ones do.  Hence: taps and chunks are nested counters, a tap's coordinates
+      // are computed once per tap, stage / barrier addresses are running values, loop bounds live in registers.
+      int kchunks64, taps, dil, nst;
+      asm volatile("mov.u32 %0, %1;" : "=r"(kchunks64) : "r"(p.kchunks * 64));
+      asm volatile("mov.u32 %0, %1;" : "=r"(taps) : "r"(p.taps));
+      asm volatile("mov.u32 %0, %1;" : "=r"(dil) : "r"(p.dil));
+      asm volatile("mov.u32 %0, %1;" : "=r"(nst) : "r"(stages));
+      uint8_t* sa = ring;
+      uint64_t* fbar = full_bar;
+      uint64_t* ebar = empty_bar;
+      const uint32_t fb0 = PAIR ? mapa_shared(full_bar, 0) : 0u;   // (shared::cluster addresses are linear inside a CTA's window)
+      uint32_t fb = fb0;
+      // (CAN_DECOMP builds only: bring-up experiments, the A / B tile of every k-block is not loaded)
+      const bool skipA = kDecomp && (p.dbg & 1024), skipB = kDecomp && (p.dbg & 2048);
+      const uint32_t tx_bytes = PAIR ? 2 * KPS * ((skipA ? 0 : L::kABytes) + (skipB ? 0 : L::kBBytes / 2))
+                                     : (kDecomp && (p.dbg & (1024 | 2048)) && GS == 1 ? (skipA ? 0 : L::kABytes) + (skipB ? 0 : L::kBBytes)
+                                                                           : L::kStageBytes);
+      auto advance = [&]() {
+        sa += kStageSz;
+        ++fbar;
+        ++ebar;
+        fb += 8;
+        if (++stage == nst) {
+          stage = 0;
+          phase ^= 1;
+          sa = ring;
+          fbar = full_bar;
+          ebar = empty_bar;
+          fb = fb0;
+        }
+      };
       for (int q_ = W0; q_ < WN; q_ += WS) {
         const int tile = tile_of(q_);
         CAN_TILE_DECODE(tile)
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          const int tap = kb / p.kchunks;
-          const int chunk = kb - tap * p.kchunks;
-          int dy = 0, dx = 0;
-          if (p.taps == 9) {
-            dy = (tap / 3 - 1) * p.dil;
-            dx = (tap % 3 - 1) * p.dil;
+        const int nB = PAIR ? n0 + rank * (BN / 2) : n0;
+        int kb64 = 0;   // 64 x the k-block index = the weight tile's K coordinate
+        for (int tap = 0; tap < taps; ++tap) {
+          int cx = x0, cy = y0;
+          if (taps == 9) {
+            const int r = tap / 3;
+            cy += (r - 1) * dil;
+            cx += (tap - 3 * r - 1) * dil;
           }
-          uint8_t* sa = ring + stage * kStageSz;
-          uint8_t* sb = sa + GS * L::kABytes;
-          if (PAIR) {
-            // both CTAs' tiles are counted on the leader's barrier (a completion that overtakes the leader's expect_tx
-            // leaves the count transiently negative; the phase needs the leader's arrival too)
-            if (leader) mbar_expect_tx(&full_bar[stage], 2 * kStageSz);
-            const uint32_t fb = mapa_shared(&full_bar[stage], 0);
-            tma_load_5d_pair(sa, &tmA, fb, chunk * 64, x0 + dx, y0 + dy, n_img, 0);
-            tma_load_3d_pair(sb, &tmB, fb, kb * 64, n0 + rank * (BN / 2), 0);
-          } else {
-          mbar_expect_tx(&full_bar[stage], L::kStageBytes);
-          if (kCtx2 && kb >= base_kb) {
-            tma_load_5d(sa, &tmW, &full_bar[stage], 0, x0, y0, 0, 0);
-            tma_load_5d(sb, &tmT, &full_bar[stage], 0, n0, n_img, kb - base_kb, 0);
-          } else {
+          for (int c64 = 0; c64 < kchunks64; c64 += 64 * KPS, kb64 += 64 * KPS) {
+            uint8_t* sb = sa + GS * KPS * L::kABytes;
+            mbar_wait(ebar, phase ^ 1);
+            if (PAIR) {
+              // both CTAs' tiles are counted on the leader's barrier (a completion that overtakes the leader's expect_tx
+              // leaves the count transiently negative; the phase needs the leader's arrival too)
+              if (leader) mbar_expect_tx(fbar, tx_bytes);
 #pragma unroll
-            for (int pl = 0; pl < GS; ++pl) {
-              tma_load_5d(sa + pl * L::kABytes, &tmA, &full_bar[stage], chunk * 64, x0 + dx, y0 + dy, n_img, pl);
-              tma_load_3d(sb + pl * L::kBBytes, &tmB, &full_bar[stage], kb * 64, n0, pl);
+              for (int j = 0; j < KPS; ++j) {
+                if (!skipA) tma_load_5d_pair(sa + j * L::kABytes, &tmA, fb, c64 + 64 * j, cx, cy, n_img, 0);
+                if (!skipB) tma_load_3d_pair(sb + j * kBt, &tmB, fb, kb64 + 64 * j, nB, 0);
+              }
+            } else {
+              mbar_expect_tx(fbar, tx_bytes);
+#pragma unroll
+              for (int pl = 0; pl < GS; ++pl) {
+                if (!skipA || GS > 1) tma_load_5d(sa + pl * L::kABytes, &tmA, fbar, c64, cx, cy, n_img, pl);
+                if (!skipB || GS > 1) tma_load_3d(sb + pl * L::kBBytes, &tmB, fbar, kb64, n0, pl);
+              }
             }
-          }
-          }
-          if (++stage == stages) {
-            stage = 0;
-            phase ^= 1;
+            advance();
           }
         }
+        if (kCtx2) {
+          // two extra k-blocks: A = the interpolation matrix of this pixel tile, B = the per-image tables
+#pragma unroll 1
+          for (int e = 0; e < 2; ++e) {
+            mbar_wait(ebar, phase ^ 1);
+            mbar_expect_tx(fbar, L::kStageBytes);
+            tma_load_5d(sa, &tmW, fbar, 0, x0, y0, 0, 0);
+            tma_load_5d(sa + GS * L::kABytes, &tmT, fbar, 0, n0, n_img, e, 0);
+            advance();
+          }
+        }
+      }
       }
     }
   } else if (warp == 1) {
@@ -443,6 +494,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int stage = 0;
       uint32_t phase = 0;
       constexpr int NACC = AccLayout<BN, GS>::kNacc;
+      // non-HALO main loop: running descriptor / barrier addresses of the current stage
+      const uint64_t da_base = umma_smem_desc(smem_u32(ring), 16, 1024);
+      uint64_t da_run = da_base;
+      uint64_t* fbar = full_bar;
+      uint64_t* ebar = empty_bar;
+      int nst;
+      asm volatile("mov.u32 %0, %1;" : "=r"(nst) : "r"(stages));
       int it = 0;  // tiles processed by this CTA
       for (int q_ = W0; q_ < WN; q_ += WS, ++it) {
         const int as = it % ACC_STAGES;
@@ -516,13 +574,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               }
             }
           }
-        } else
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
+        } else {
+        // (the issuing thread is alone too: the stage's descriptors and barrier addresses are running values, see the
+        // producer's note; a descriptor's address field (>> 4, 14 bits) covers all of shared memory, so adding to it never
+        // carries into the other fields)
+        const int n_st = num_kb / KPS;   // stages per tile
+        for (int kb = 0; kb < n_st; ++kb) {
+          mbar_wait(fbar, phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(ring + stage * kStageSz);
-          const uint64_t da0 = umma_smem_desc(sa, 16, 1024);                       // one descriptor pair per
-          const uint64_t db0 = umma_smem_desc(sa + GS * L::kABytes, 16, 1024);     // stage (see HALO note)
+          const uint64_t da0 = da_run;                                     // one descriptor pair per
+          const uint64_t db0 = da_run + ((GS * KPS * L::kABytes) >> 4);    // stage (see HALO note)
+#pragma unroll
+          for (int j = 0; j < KPS; ++j)
 #pragma unroll
           for (int pa = 0; pa < GS; ++pa) {
 #pragma unroll
@@ -534,18 +597,26 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                                                     : ((pa + pb == 0) ? (kb % NACC) : NACC);
                 const uint32_t accf = (used >> acc) & 1u;
                 used |= 1u << acc;
+                if (kDecomp && (p.dbg & 4096)) continue;   // (CAN_DECOMP builds: the loads and hand-shakes without the MMAs)
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
-                  mma(tacc + acc * BN, da0 + ((pa * L::kABytes + k * 32) >> 4), db0 + ((pb * L::kBBytes + k * 32) >> 4),
-                      k ? 1u : accf);
+                  mma(tacc + acc * BN, da0 + (((j + pa) * L::kABytes + k * 32) >> 4),
+                      db0 + ((j * kBt + pb * L::kBBytes + k * 32) >> 4), (k | j) ? 1u : accf);
               }
             }
           }
-          commit(&empty_bar[stage]);   // frees the smem slot when these MMAs retire (pair: in both CTAs)
-          if (++stage == stages) {
+          commit(ebar);   // frees the smem slot when these MMAs retire (pair: in both CTAs)
+          da_run += kStageSz >> 4;
+          ++fbar;
+          ++ebar;
+          if (++stage == nst) {
             stage = 0;
             phase ^= 1;
+            da_run = da_base;
+            fbar = full_bar;
+            ebar = empty_bar;
           }
+        }
         }
         commit(&tmem_full_bar[as]);  // accumulator of this tile complete (pair: of both tiles, told to both CTAs)
       }
