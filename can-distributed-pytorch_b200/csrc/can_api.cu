@@ -133,13 +133,17 @@ int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvTcParams& p,
   constexpr int ctx = MODE;   // (ConvTcSmem::bytes sizes the table region from the mode)
   const int staged_bytes = p.out_stage_bytes + p.mask_bufs * BN * 256;
   // pair: each CTA holds half of B; the 128-wide pair tiles put two 64-channel k-chunks in a stage (see the kernel)
-  constexpr int kStage = PAIR ? (BN == 128 ? 2 : 1) * (L::kABytes + L::kBBytes / 2) : L::kStageBytes;
-  int stages = (kMaxSmem - L::bytes(0, ctx) - staged_bytes) / kStage;
+  // (PAIR == 2: the ring holds weight tiles only, three taps per stage at BN = 128; the A halo stages sit before it)
+  constexpr int kStage = PAIR == 2 ? (BN == 128 ? 3 : 1) * (L::kBBytes / 2)
+                         : PAIR    ? (BN == 128 ? 2 : 1) * (L::kABytes + L::kBBytes / 2)
+                                   : L::kStageBytes;
+  const int halo_a_bytes = PAIR == 2 ? p.n_a * p.halo_stride : 0;
+  int stages = (kMaxSmem - L::bytes(0, ctx) - staged_bytes - halo_a_bytes) / kStage;
   if (stages > 8) stages = 8;
   if (stages_override > 0 && stages_override < stages) stages = stages_override;
   if (stages < 2) return fail(-20, "conv_tc: tile BN=%d nsplit=%d does not fit shared memory", BN, NSPLIT);
   p.stages = stages;
-  const int smem = L::bytes(0, ctx) + stages * kStage + staged_bytes;
+  const int smem = L::bytes(0, ctx) + stages * kStage + staged_bytes + halo_a_bytes;
   // eight epilogue warps for the narrow, epilogue-bound tiles of the bf16 path
   constexpr int EW = ((NSPLIT == 1 && BN <= 128 && (MODE == MODE_STORE || MODE == MODE_POOL || MODE == MODE_UNPOOL)) ||
                       MODE == MODE_CTX2 || MODE == MODE_CTX2_BWD) ? 8 : 4;   // (MODE_DFV with 8: measured slower)
@@ -400,6 +404,15 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   const int halo1_env = env_int("CAN_B200_HALO1", 0);
   p.halo1 = halo && a->mode != CAN_MODE_UNPOOL && (halo1_env == 2 || (halo1_env == 1 && bn == 64));
   if (p.halo1) p.TW = 8;
+  // 3x3 layers that run as CTA pairs (below): the A operand comes from ONE halo tile per (pixel tile, channel chunk), the
+  // nine taps being shifted views of it, while the weight tiles stream.  An SM takes ~64 B/cycle from L2; with a fresh
+  // 16 KB A tile per tap and chunk a 128-wide pair tile needs 24 KB per 256 cycles of MMA (load-bound: 128->128 took
+  // 222 us where its MMAs need ~130) and a 256-wide one 32 KB per 512 (just balanced).  The halo tile cuts the A traffic
+  // by 6 (dil 1) / 4.7 (dil 2).  Tile = 8 x 16 pixels, as the 8-row groups of A must be whole patch rows.
+  const bool halo_a = !halo && a->nsplit == 1 && a->taps == 9 && (bn == 128 || bn == 256) && a->W >= 8 &&
+                      (a->mode == CAN_MODE_STORE || a->mode == CAN_MODE_POOL || a->mode == CAN_MODE_UNPOOL) &&
+                      env_int("CAN_B200_PAIR", 1) != 0 && env_int("CAN_B200_HALOA", 1) != 0;
+  if (halo_a) p.TW = 8;
   p.TH = 128 / p.TW;
   p.tiles_x = (a->W + p.TW - 1) / p.TW;
   p.tiles_y = (a->H + p.TH - 1) / p.TH;
@@ -615,6 +628,27 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     int pairs = ctas / 2;
     if (pairs > items) pairs = items;
     const dim3 pg(2 * pairs);
+    if (halo_a) {
+      CUtensorMap tmH;
+      const int halo_w = p.TW + 2 * a->dil, halo_h = p.TH + 2 * a->dil;
+      p.halo_bytes = halo_h * halo_w * 128;
+      p.halo_stride = (p.halo_bytes + 1023) & ~1023;
+      p.n_a = 2;   // halo stages: the next chunk's tile lands while this one's nine taps are multiplied
+      rc = make_act_tmap(&tmH, a->x, a->x_coff, a->Cin, a->x_cs, a->x_plane, 1, a->N, a->H, a->W, halo_w, halo_h);
+      if (rc) return rc;
+      g_tmW = &tmH;
+      if (bn == 256) {
+        rc = m == CAN_MODE_STORE  ? launch_conv<256, 1, MODE_STORE, 2>(tmA, tmBh, p, pg, so, st)
+             : m == CAN_MODE_POOL ? launch_conv<256, 1, MODE_POOL, 2>(tmA, tmBh, p, pg, so, st)
+                                  : launch_conv<256, 1, MODE_UNPOOL, 2>(tmA, tmBh, p, pg, so, st);
+      } else {
+        rc = m == CAN_MODE_STORE  ? launch_conv<128, 1, MODE_STORE, 2>(tmA, tmBh, p, pg, so, st)
+             : m == CAN_MODE_POOL ? launch_conv<128, 1, MODE_POOL, 2>(tmA, tmBh, p, pg, so, st)
+                                  : launch_conv<128, 1, MODE_UNPOOL, 2>(tmA, tmBh, p, pg, so, st);
+      }
+      g_tmW = nullptr;
+      return rc;
+    }
     if (bn == 256) {
       switch (m) {
         case CAN_MODE_STORE: return launch_conv<256, 1, MODE_STORE, 1>(tmA, tmBh, p, pg, so, st);

@@ -48,6 +48,7 @@ struct ConvTcParams {
   int halo_bytes;      // HALO: bytes of one activation stage ((TH + 2 dil) * TW * 128; halo1: (TH + 2 dil) * (TW + 2 dil) * 128)
   int halo_stride;     // HALO: distance between stages (halo_bytes rounded up to 1024)
   int halo1;           // HALO: one halo tile per (pixel tile, channel chunk) serves all nine taps
+  int n_a;             // PAIR == 2: number of A halo stages (each halo_stride bytes) in front of the weight ring
   int out_stage_bytes; // > 0: the epilogue stages the bf16 tile in shared memory (BN * 256 B) and writes it with TMA (tmO)
   int out_bufs;        // MODE_STORE staged epilogue: 1 or 2 staging buffers of BN * 256 B (out_stage_bytes = their sum)
   int mask_bufs;       // staged epilogue: 0 = mask read from global memory, 1|2 = mask tiles (BN * 256 B each) brought in by TMA (tmM)
@@ -260,11 +261,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   // KPS = 64-channel k-chunks per pipeline stage.  The 128-wide pair tiles take two: one thread issues the loads and one
   // the MMAs, each pays a fixed price per stage hand-shake (barrier wait ~90 cycles + issue), and four N = 128 MMAs are
   // done in 256 cycles -- with one chunk per stage those two threads, not the tensor pipe, set the pace.
-  constexpr int KPS = (PAIR && BN == 128) ? 2 : 1;
-  const int stage_bytes = HALO ? p.halo_stride : GS * KPS * (L::kABytes + (PAIR ? L::kBBytes / 2 : L::kBBytes));
+  constexpr int KPS = (PAIR == 1 && BN == 128) ? 2 : 1;
+  // PAIR == 2: pairs whose A operand is one halo tile per (pixel tile, channel chunk) -- the nine taps are shifted views of
+  // it, as in the single-tile HALO variant -- while the weight tiles stream through the ring, TPS taps per stage.
+  constexpr bool HA = PAIR == 2;
+  constexpr int TPS = HA ? (BN == 128 ? 3 : 1) : 1;
+  const int stage_bytes = HALO ? p.halo_stride
+                          : HA ? TPS * (L::kBBytes / 2)
+                               : GS * KPS * (L::kABytes + (PAIR ? L::kBBytes / 2 : L::kBBytes));
   // single-halo-tile variant: not compiled into the max-unpool kernels (their epilogue sits on the register limit)
   const bool halo1 = HALO && MODE != MODE_UNPOOL && p.halo1;
-  uint8_t* tail = ring + stages * stage_bytes;
+  uint8_t* ringB = ring + (HA ? p.n_a * p.halo_stride : 0);          // PAIR == 2: weight ring behind the A halo stages
+  uint8_t* tail = ringB + stages * stage_bytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
   uint64_t* empty_bar = full_bar + 8;
   uint64_t* tmem_full_bar = empty_bar + 8;    // [4]
@@ -274,7 +282,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* out_full_bar = out_free_bar + 2;     // [2] staged output: every epilogue thread has written its part of it
   uint64_t* mask_full_bar = out_full_bar + 2;    // [2] staged mask tile landed
   uint64_t* mask_free_bar = mask_full_bar + 2;   // [2] every epilogue thread is done with it
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(mask_free_bar + 2);
+  uint64_t* fullA_bar = mask_free_bar + 2;       // [4] PAIR == 2: A halo stage landed (both CTAs' tiles, on the leader's)
+  uint64_t* emptyA_bar = fullA_bar + 4;          // [4] PAIR == 2: the nine taps of that stage have been multiplied
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(emptyA_bar + 4);
   float* s_bias2 = reinterpret_cast<float*>(tail + 1024);  // [2][BN]
   float* s_db = s_bias2 + 2 * BN;   // [<=1024] per-CTA partial bias gradient (p.db)
   float* s_tab = s_db + 1024;       // MODE_CTX / MODE_CTX_BWD only: [2][50][64]
@@ -287,6 +297,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int base_kb = p.taps * p.kchunks;
   static_assert(!PAIR || (!HALO && NSPLIT == 1 && (MODE == MODE_STORE || MODE == MODE_POOL || MODE == MODE_UNPOOL || MODE == MODE_DFV)),
                 "CTA pairs exist for the streamed (non-HALO) tiles of the bf16 path");
+  static_assert(PAIR != 2 || (MODE != MODE_DFV && (BN == 128 || BN == 256)), "halo-A pairs: the 3x3 layers with 128/256-wide tiles");
   // Work items.  Plain: CTA b takes tiles b, b + grid, ...  Pair: the two CTAs walk the same list of tile PAIRS in
   // lockstep, rank r taking tile 2 q + r (an odd tile count leaves the last item's odd CTA a dead tile: it recomputes the
   // last tile and drops the result).
@@ -302,7 +313,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   };
   auto live_of = [&](int q) { return !PAIR || (2 * (q / p.n_tiles) + rank < pix_tiles); };
   constexpr int kBt = PAIR ? L::kBBytes / 2 : L::kBBytes;   // bytes of one weight tile in this CTA
-  constexpr int kStageSz = GS * KPS * (L::kABytes + kBt);   // non-HALO stage: A tile(s) + this CTA's part of B
+  constexpr int kStageSz = HA ? TPS * kBt : GS * KPS * (L::kABytes + kBt);   // non-HALO stage: A tile(s) + this CTA's part of B
   // MODE_CTX2: two extra k-blocks whose A operand is the interpolation matrix Wint[pixel][64 positions]
   // and whose B operands are the per-image tables (-U-side of z, then s) -- see the epilogue.
   constexpr bool kCtx2 = (MODE == MODE_CTX2 || MODE == MODE_CTX2_BWD);
@@ -326,6 +337,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tma_prefetch_desc(&tmW);
       tma_prefetch_desc(&tmT);
     }
+    if (HA) tma_prefetch_desc(&tmW);
     if (p.out_stage_bytes) tma_prefetch_desc(&tmO);
     if (p.mask_bufs) tma_prefetch_desc(&tmM);
   }
@@ -341,6 +353,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_init(&tmem_empty_bar[a], 32 * EW + (PAIR ? EW : 0));
       }
       mbar_init(w_bar, 1);
+      for (int a = 0; a < 4; ++a) {
+        mbar_init(&fullA_bar[a], 1);
+        mbar_init(&emptyA_bar[a], 1);
+      }
       for (int a = 0; a < 2; ++a) {
         mbar_init(&out_free_bar[a], 1);
         mbar_init(&out_full_bar[a], 32 * EW);
@@ -391,6 +407,50 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               if (++stage == stages) {
                 stage = 0;
                 phase ^= 1;
+              }
+            }
+          }
+        }
+      } else if (HA) {
+        // loads in the order the MMAs consume them: the halo tile of a chunk, then its nine weight tiles (TPS per stage)
+        int kchunks64, dil, nst, nA;
+        asm volatile("mov.u32 %0, %1;" : "=r"(kchunks64) : "r"(p.kchunks * 64));
+        asm volatile("mov.u32 %0, %1;" : "=r"(dil) : "r"(p.dil));
+        asm volatile("mov.u32 %0, %1;" : "=r"(nst) : "r"(stages));
+        asm volatile("mov.u32 %0, %1;" : "=r"(nA) : "r"(p.n_a));
+        const uint32_t fbA0 = mapa_shared(fullA_bar, 0), fbB0 = mapa_shared(full_bar, 0);
+        const int cin = kchunks64;              // K stride between taps in the weight matrix
+        int sA = 0, sB = 0;
+        uint32_t phA = 0, phB = 0;
+        uint8_t* pa = ring;
+        uint8_t* pb = ringB;
+        for (int q_ = W0; q_ < WN; q_ += WS) {
+          const int tile = tile_of(q_);
+          CAN_TILE_DECODE(tile)
+          const int nB = n0 + rank * (BN / 2);
+          const int hx = x0 - dil, hy = y0 - dil;
+          for (int c64 = 0; c64 < kchunks64; c64 += 64) {
+            mbar_wait(&emptyA_bar[sA], phA ^ 1);
+            if (leader) mbar_expect_tx(&fullA_bar[sA], 2u * static_cast<uint32_t>(p.halo_bytes));
+            tma_load_5d_pair(pa, &tmW, fbA0 + 8 * sA, c64, hx, hy, n_img, 0);
+            pa += p.halo_stride;
+            if (++sA == nA) {
+              sA = 0;
+              phA ^= 1;
+              pa = ring;
+            }
+            int kw = c64;                       // K coordinate of tap 0's tile of this chunk
+#pragma unroll 1
+            for (int t0 = 0; t0 < 9; t0 += TPS) {
+              mbar_wait(&empty_bar[sB], phB ^ 1);
+              if (leader) mbar_expect_tx(&full_bar[sB], 2 * kStageSz);
+#pragma unroll
+              for (int j = 0; j < TPS; ++j, kw += cin) tma_load_3d_pair(pb + j * kBt, &tmB, fbB0 + 8 * sB, kw, nB, 0);
+              pb += kStageSz;
+              if (++sB == nst) {
+                sB = 0;
+                phB ^= 1;
+                pb = ringB;
               }
             }
           }
@@ -501,6 +561,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint64_t* ebar = empty_bar;
       int nst;
       asm volatile("mov.u32 %0, %1;" : "=r"(nst) : "r"(stages));
+      int sA_ = 0;          // PAIR == 2: A halo stage and its phase
+      uint32_t phA_ = 0;
       int it = 0;  // tiles processed by this CTA
       for (int q_ = W0; q_ < WN; q_ += WS, ++it) {
         const int as = it % ACC_STAGES;
@@ -572,6 +634,47 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 stage = 0;
                 phase ^= 1;
               }
+            }
+          }
+        } else if (HA) {
+          // A = the chunk's halo tile: 8-pixel patch rows one halo pitch apart (SBO = pitch), tap (dy, dx) starts
+          // (dy * pitch + dx) * dil pixels into it (see the single-tile HALO variant above for why that is legal)
+          const uint32_t pitch = static_cast<uint32_t>(p.TW + 2 * p.dil);
+          const uint32_t dx_units = static_cast<uint32_t>(p.dil) * 8, dy_units = dx_units * pitch;
+          const uint64_t dbB0 = umma_smem_desc(smem_u32(ringB), 16, 1024);
+          uint32_t accum = 0;
+          for (int chunk = 0; chunk < p.kchunks; ++chunk) {
+            mbar_wait(&fullA_bar[sA_], phA_);
+            tc_fence_after();
+            const uint64_t da0 = umma_smem_desc(smem_u32(ring + sA_ * p.halo_stride), 16, pitch * 128);
+#pragma unroll
+            for (int dyi = 0; dyi < 3; ++dyi) {
+#pragma unroll
+              for (int dx0 = 0; dx0 < 3; dx0 += TPS) {
+                mbar_wait(&full_bar[stage], phase);
+                tc_fence_after();
+                const uint64_t db0 = dbB0 + static_cast<uint32_t>(stage * (kStageSz >> 4));
+#pragma unroll
+                for (int j = 0; j < TPS; ++j) {
+                  const uint64_t da = da0 + (dyi * dy_units + (dx0 + j) * dx_units);
+                  const uint64_t db = db0 + static_cast<uint32_t>(j * (kBt >> 4));
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) {
+                    mma(tacc, da + 2 * k, db + 2 * k, accum);
+                    accum = 1;
+                  }
+                }
+                commit(&empty_bar[stage]);
+                if (++stage == nst) {
+                  stage = 0;
+                  phase ^= 1;
+                }
+              }
+            }
+            commit(&emptyA_bar[sA_]);   // every tap of this halo tile has been issued: free it when they retire
+            if (++sA_ == p.n_a) {
+              sA_ = 0;
+              phA_ ^= 1;
             }
           }
         } else {
