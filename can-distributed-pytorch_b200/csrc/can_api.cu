@@ -518,7 +518,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
       rc = make_tmap(&tmM, static_cast<const __nv_bfloat16*>(a->mask) + a->mask_coff, 4, dimsO, strM, boxO);
       if (rc) return rc;
       g_tmM = &tmM;
-      p.mask_bufs = env_int("CAN_B200_MASKBUFS", bn == 64 ? 2 : 1);
+      p.mask_bufs = env_int("CAN_B200_MASKBUFS", (bn == 64 || halo_a) ? 2 : 1);   // (halo-A pairs: 128->128 dgrad 217 -> 193 us with two)
     }
   }
   // small-Cin layers on the bf16 path: resident weights + halo stages (L2->SM traffic / 3.6, / 9 with one halo tile)

@@ -420,6 +420,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         asm volatile("mov.u32 %0, %1;" : "=r"(nA) : "r"(p.n_a));
         const uint32_t fbA0 = mapa_shared(fullA_bar, 0), fbB0 = mapa_shared(full_bar, 0);
         const int cin = kchunks64;              // K stride between taps in the weight matrix
+        const bool skipA = kDecomp && (p.dbg & 1024), skipB = kDecomp && (p.dbg & 2048);   // (CAN_DECOMP builds only)
         int sA = 0, sB = 0;
         uint32_t phA = 0, phB = 0;
         uint8_t* pa = ring;
@@ -431,8 +432,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const int hx = x0 - dil, hy = y0 - dil;
           for (int c64 = 0; c64 < kchunks64; c64 += 64) {
             mbar_wait(&emptyA_bar[sA], phA ^ 1);
-            if (leader) mbar_expect_tx(&fullA_bar[sA], 2u * static_cast<uint32_t>(p.halo_bytes));
-            tma_load_5d_pair(pa, &tmW, fbA0 + 8 * sA, c64, hx, hy, n_img, 0);
+            if (leader) mbar_expect_tx(&fullA_bar[sA], skipA ? 0u : 2u * static_cast<uint32_t>(p.halo_bytes));
+            if (!skipA) tma_load_5d_pair(pa, &tmW, fbA0 + 8 * sA, c64, hx, hy, n_img, 0);
             pa += p.halo_stride;
             if (++sA == nA) {
               sA = 0;
@@ -443,9 +444,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll 1
             for (int t0 = 0; t0 < 9; t0 += TPS) {
               mbar_wait(&empty_bar[sB], phB ^ 1);
-              if (leader) mbar_expect_tx(&full_bar[sB], 2 * kStageSz);
+              if (leader) mbar_expect_tx(&full_bar[sB], skipB ? 0 : 2 * kStageSz);
 #pragma unroll
-              for (int j = 0; j < TPS; ++j, kw += cin) tma_load_3d_pair(pb + j * kBt, &tmB, fbB0 + 8 * sB, kw, nB, 0);
+              for (int j = 0; j < TPS; ++j, kw += cin)
+                if (!skipB) tma_load_3d_pair(pb + j * kBt, &tmB, fbB0 + 8 * sB, kw, nB, 0);
               pb += kStageSz;
               if (++sB == nst) {
                 sB = 0;
@@ -660,7 +662,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                   const uint64_t db = db0 + static_cast<uint32_t>(j * (kBt >> 4));
 #pragma unroll
                   for (int k = 0; k < 4; ++k) {
-                    mma(tacc, da + 2 * k, db + 2 * k, accum);
+                    if (!(kDecomp && (p.dbg & 4096))) mma(tacc, da + 2 * k, db + 2 * k, accum);
                     accum = 1;
                   }
                 }

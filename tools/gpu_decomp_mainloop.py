@@ -13,6 +13,7 @@ os.environ.setdefault("CAN_B200_LIB", os.path.join(ROOT, "can-distributed-pytorc
 from can_b200 import ops  # noqa: E402
 
 SHAPES = [(4, 384, 512, 128, 128), (4, 96, 128, 512, 512), (4, 192, 256, 256, 256), (4, 192, 256, 128, 256)]
+VARIANTS = [("1", "1", "pairs, halo A"), ("1", "0", "pairs, A per tap"), ("0", "0", "single CTA")]
 BITS = [(0, "all"), (16, "no epilogue"), (16 + 1024, "no epi, no A loads"), (16 + 2048, "no epi, no B loads"),
         (16 + 1024 + 2048, "no epi, no loads"), (16 + 4096, "no epi, no MMAs"), (16 + 4096 + 1024, "no epi, no MMAs, no A"),
         (16 + 4096 + 2048, "no epi, no MMAs, no B")]
@@ -26,9 +27,10 @@ def main():
         wp = ops.pack_conv_weight(torch.randn(Cout, Cin, 3, 3, device=dev) * 0.05, 1)
         b = torch.zeros(Cout, device=dev)
         out = ops.new_act(1, N, H, W, Cout, dev)
-        for pair in ("1", "0"):
+        for pair, haloa, vname in VARIANTS:
             os.environ["CAN_B200_PAIR"] = pair
-            for stages in ("0", "4"):
+            os.environ["CAN_B200_HALOA"] = haloa
+            for stages in ("0",):
                 os.environ["CAN_B200_STAGES"] = stages
                 for dbg, what in BITS:
                     if stages == "4" and dbg not in (0, 16):
@@ -47,7 +49,7 @@ def main():
                     e1.record()
                     torch.cuda.synchronize()
                     us = e0.elapsed_time(e1) * 100
-                    print(f"{Cin}->{Cout} {H}x{W} N={N} pair={pair} stages={stages or 'max'} {what:28s}: {us:7.1f} us "
+                    print(f"{Cin}->{Cout} {H}x{W} N={N} [{vname:16s}] {what:28s}: {us:7.1f} us "
                           f"({2 * 9 * Cin * Cout * N * H * W / us / 1e6:.0f} TF)", flush=True)
     os.environ["CAN_B200_DBG"] = "0"
 
