@@ -208,9 +208,9 @@ int dispatch_mode(int mode, const CUtensorMap& a, const CUtensorMap& b, ConvTcPa
 
 
 struct WgradPlan {
-  int TW, TH, tiles_x, tiles_y, total_patches, m_tiles, n_tiles, bn, ksplit, per, T, tap_groups, swap64, pix;
+  int TW, TH, tiles_x, tiles_y, total_patches, m_tiles, n_tiles, bn, ksplit, per, T, tap_groups, swap64, pix, hx;
 };
-WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nsplit) {
+WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nsplit, int dil = 1) {
   WgradPlan pl;
   pl.bn = Cin < 256 ? Cin : (nsplit > 1 ? 128 : 256);
   // 512-wide layers: nine taps in pairs (BN = 256) leave a half-loaded fifth tap group and 120 CTAs for 148 SMs;
@@ -221,6 +221,9 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   pl.pix = (nsplit == 1 && taps > 1 && (pl.bn == 256 || (pl.bn == 128 && env_int("CAN_B200_WGPIX128", 32) == 32)) &&
             env_int("CAN_B200_WGPIX", 32) == 32) ? 32 : 64;
   pl.TW = (W >= 16) ? 16 : 8;
+  // 128-wide three-tap tiles: the three X patches of a stage as shifted views of one halo tile (8-pixel patch rows)
+  pl.hx = (nsplit == 1 && taps == 9 && pl.bn == 128 && pl.pix == 32 && dil <= 2 && env_int("CAN_B200_WGHX", 1) != 0) ? 1 : 0;
+  if (pl.hx) pl.TW = 8;
   pl.TH = pl.pix / pl.TW;
   pl.tiles_x = (W + pl.TW - 1) / pl.TW;
   pl.tiles_y = (H + pl.TH - 1) / pl.TH;
@@ -268,14 +271,15 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
 
 thread_local const CUtensorMap* g_tmWS = nullptr;   // fp32 map of the split-K workspace (null -> per-lane stores)
 
-template <int BN, int NSPLIT, int T, int PIX = 64>
+template <int BN, int NSPLIT, int T, int PIX = 64, int HX = 0>
 int launch_wgrad(const CUtensorMap& tmDZ, const CUtensorMap& tmX, WgradTcParams& p, dim3 grid, cudaStream_t st) {
   using L = WgradTcSmem<BN, NSPLIT, T, PIX>;
-  int stages = (kMaxSmem - L::bytes(0)) / L::kStageBytes;
+  const int stage_b = HX ? p.hx_stage : L::kStageBytes;
+  int stages = (kMaxSmem - L::bytes(0)) / stage_b;
   if (stages > 8) stages = 8;
   if (stages < 2) return fail(-20, "wgrad_tc: tile BN=%d nsplit=%d does not fit shared memory", BN, NSPLIT);
   p.stages = stages;
-  auto kern = wgrad_tc_kernel<BN, NSPLIT, T, PIX>;
+  auto kern = wgrad_tc_kernel<BN, NSPLIT, T, PIX, HX>;
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
@@ -283,7 +287,7 @@ int launch_wgrad(const CUtensorMap& tmDZ, const CUtensorMap& tmX, WgradTcParams&
     attr_done = true;
   }
   p.ws_tma = g_tmWS ? 1 : 0;
-  return launch_ex(kern, grid, 192, L::bytes(stages), st, "wgrad_tc launch", 1, tmDZ, tmX, g_tmWS ? *g_tmWS : tmDZ, p);
+  return launch_ex(kern, grid, 192, L::bytes(0) + stages * stage_b, st, "wgrad_tc launch", 1, tmDZ, tmX, g_tmWS ? *g_tmWS : tmDZ, p);
 }
 
 int make_act_tmap(CUtensorMap* m, const void* base, int coff, int C, int cs, int64_t plane, int nsplit, int N, int H,
@@ -949,8 +953,9 @@ int can_nchw_f32_to_nhwc(const float* src, void* dst, int64_t plane, int nsplit,
 
 int64_t can_conv_wgrad_workspace_bytes(int N, int H, int W, int Cin, int Cout, int taps, int nsplit) {
   if (N <= 0 || H <= 0 || W <= 0 || Cin <= 0 || Cin % 64 || Cout <= 0 || Cout % 64) return -1;
-  const WgradPlan pl = wgrad_plan(N, H, W, Cin, Cout, taps, nsplit);
-  return static_cast<int64_t>(pl.ksplit) * taps * Cout * Cin * sizeof(float);
+  // (the patch shape, hence the split count, can depend on the dilation: the larger of the two plans)
+  const WgradPlan pl = wgrad_plan(N, H, W, Cin, Cout, taps, nsplit, 1), pl3 = wgrad_plan(N, H, W, Cin, Cout, taps, nsplit, 3);
+  return static_cast<int64_t>(pl.ksplit > pl3.ksplit ? pl.ksplit : pl3.ksplit) * taps * Cout * Cin * sizeof(float);
 }
 
 }  // extern "C"
@@ -1000,7 +1005,7 @@ int conv_wgrad_impl(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, co
   if (taps != 1 && taps != 9) return fail(-4, "conv_wgrad: taps=%d", taps);
   if (nsplit < 1 || nsplit > 3) return fail(-5, "conv_wgrad: nsplit=%d", nsplit);
   if (dz_cs % 8 || dz_coff % 8 || x_cs % 8 || x_coff % 8) return fail(-6, "conv_wgrad: strides/offsets must be multiples of 8");
-  const WgradPlan pl = wgrad_plan(N, H, W, Cin, Cout, taps, nsplit);
+  const WgradPlan pl = wgrad_plan(N, H, W, Cin, Cout, taps, nsplit, dil);
   const int64_t need = static_cast<int64_t>(pl.ksplit) * taps * Cout * Cin * sizeof(float);
   if (ws_bytes < need) return fail(-7, "conv_wgrad: workspace %lld < %lld bytes", (long long)ws_bytes, (long long)need);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -1033,9 +1038,13 @@ int conv_wgrad_impl(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, co
   if (nsplit == 1 && !pl.swap64) {
     rc = make_act_tmap_groups(&tmDZ, dz, dz_coff, Cout, dz_cs, N, H, W, pl.TW, pl.TH, p.m_groups);
     if (rc) return rc;
-    rc = make_act_tmap_groups(&tmX, x, x_coff, x_images > 0 ? cin_img : Cin, x_cs, x_images > 0 ? x_images : N, H, W, pl.TW,
-                              pl.TH, pl.bn / 64);
+    rc = make_act_tmap_groups(&tmX, x, x_coff, x_images > 0 ? cin_img : Cin, x_cs, x_images > 0 ? x_images : N, H, W,
+                              pl.hx ? pl.TW + 2 * dil : pl.TW, pl.TH, pl.bn / 64);   // (hx: the box is the halo tile)
     if (rc) return rc;
+    if (pl.hx) {
+      p.hx_bytes = (pl.bn / 64) * (pl.TW + 2 * dil) * pl.TH * 128;
+      p.hx_stage = 2 * pl.pix * 128 + ((p.hx_bytes + 1023) & ~1023);
+    }
     p.x_img_tiles = x_images > 0 ? cin_img / pl.bn : 0;
   }
   if (pl.swap64) {
@@ -1060,6 +1069,7 @@ int conv_wgrad_impl(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, co
   }
   if (pl.T > 1) {  // bf16 path, several taps per CTA
     if (pl.bn == 64) rc = launch_wgrad<64, 1, 3>(tmDZ, tmX, p, grid, st);
+    else if (pl.hx) rc = launch_wgrad<128, 1, 3, 32, 1>(tmDZ, tmX, p, grid, st);
     else if (pl.bn == 128 && pl.pix == 32) rc = launch_wgrad<128, 1, 3, 32>(tmDZ, tmX, p, grid, st);
     else if (pl.bn == 128) rc = launch_wgrad<128, 1, 3>(tmDZ, tmX, p, grid, st);
     else if (pl.pix == 32) rc = launch_wgrad<256, 1, 2, 32>(tmDZ, tmX, p, grid, st);

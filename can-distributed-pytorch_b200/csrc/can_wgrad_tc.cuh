@@ -32,6 +32,8 @@ struct WgradTcParams {
   int tap_groups;  // ceil(taps / T)
   int dbg;         // bring-up experiments only (bit 0: skip the partial-tile stores)
   int ws_tma;      // partial tiles leave through TMA stores (tmWS) instead of per-lane stores
+  int hx_bytes;    // HX: bytes of the X halo tile of a stage ((BN / 64) groups x (TW + 2 dil) x TH pixels x 128 B)
+  int hx_stage;    // HX: bytes of a stage (dZ patch + halo tile)
   float* ws;     // [split][tap][Cout][Cin]
 };
 
@@ -45,16 +47,22 @@ struct WgradTcSmem {
   static __host__ __device__ constexpr int bytes(int stages) { return 1024 + stages * kStageBytes + 1024; }
 };
 
-template <int BN, int NSPLIT, int T, int PIX = 64>
+// HX = 1 (bf16 path, BN = 128, the three taps of a CTA share dy): the three X patches are column-shifted views of ONE halo
+// tile ((TW + 2 dil) x TH pixels, TW = 8 so that the 8-pixel groups of the MN-major operand are whole patch rows one halo
+// pitch apart) instead of three tiles -- a stage is 18-20 KB instead of 32 KB.  The kernel was bound by what an SM can take
+// from L2 (ncu: 75 B/cycle/SM = 64 B per L2 clock, tensor pipe 86 %, `profiles/r02_ncu_wgrad_128_3_32_details.txt`).
+template <int BN, int NSPLIT, int T, int PIX = 64, int HX = 0>
 __global__ void __launch_bounds__(192, 1)
 wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant__ CUtensorMap tmX,
                 const __grid_constant__ CUtensorMap tmWS, const WgradTcParams p) {
   using L = WgradTcSmem<BN, NSPLIT, T, PIX>;
   static_assert(T * BN <= 512, "accumulators of one tap group must fit TMEM");
+  static_assert(!HX || (NSPLIT == 1 && T == 3 && PIX == 32), "halo X tiles: three taps of one row, 32-pixel patches");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-aligned, still a shared-space pointer
   const int stages = p.stages;
-  uint8_t* tail = smem + stages * L::kStageBytes;
+  const int stage_bytes = HX ? p.hx_stage : L::kStageBytes;
+  uint8_t* tail = smem + stages * stage_bytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
   uint64_t* empty_bar = full_bar + 8;
   uint64_t* tmem_full_bar = empty_bar + 8;
@@ -73,7 +81,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
   const int patch_begin = split * p.patches_per_split;
   const int patch_end = min(patch_begin + p.patches_per_split, p.total_patches);
   const int m_groups = p.m_groups;  // 1 or 2
-  const uint32_t stage_tx = NSPLIT * (m_groups * L::kGroupBytes + ntaps * L::kBBytes);
+  const uint32_t stage_tx = HX ? m_groups * L::kGroupBytes + p.hx_bytes : NSPLIT * (m_groups * L::kGroupBytes + ntaps * L::kBBytes);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmDZ);
@@ -116,10 +124,13 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
       for (int pid = patch_begin; pid < patch_end; ++pid) {
         const int x0 = tx_i * p.TW, y0 = ty_i * p.TH;
         mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sa = smem + stage * L::kStageBytes;
+        uint8_t* sa = smem + stage * stage_bytes;
         uint8_t* sb = sa + NSPLIT * L::kABytes;  // [plane][tap][BN/64 groups]
         mbar_expect_tx(&full_bar[stage], stage_tx);
-        if (NSPLIT == 1) {
+        if (HX) {
+          tma_load_5d(sa, &tmDZ, &full_bar[stage], 0, x0, y0, m_tile * 2, n_img);
+          tma_load_5d(sb, &tmX, &full_bar[stage], 0, x0 - p.dil, y0 + tdy[0], n_tile * (BN / 64), n_img);   // (box: the halo tile)
+        } else if (NSPLIT == 1) {
           // single-plane maps carry the 64-channel group as their 4th dimension: one TMA op per operand tile
           tma_load_5d(sa, &tmDZ, &full_bar[stage], 0, x0, y0, m_tile * 2, n_img);
           const int xg = p.x_img_tiles ? (n_tile % p.x_img_tiles) * (BN / 64) : n_tile * (BN / 64);
@@ -168,9 +179,30 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDZ, const __grid_constant_
       for (int pid = patch_begin; pid < patch_end; ++pid) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
+        const uint32_t sa = smem_u32(smem + stage * stage_bytes);
         // one descriptor pair per stage; planes, taps and k-steps only add to the address field (>> 4)
         const uint64_t da0 = umma_smem_desc(sa, L::kGroupBytes, 1024);
+        if (HX) {
+          // B = the halo tile: 8-pixel groups are patch rows one halo pitch apart (SBO), 64-channel groups one whole tile
+          // apart (LBO); tap dx starts dx * dil pixels into the rows; a k-step of 16 pixels is two rows
+          const uint32_t pitch = static_cast<uint32_t>(p.TW + 2 * p.dil) * 128u;
+          const uint64_t dbh = umma_smem_desc(sa + L::kABytes, pitch * p.TH, pitch);
+          constexpr uint32_t idesc_h = umma_idesc_bf16(128, BN, 1, 1);
+#pragma unroll
+          for (int tt = 0; tt < T; ++tt) {
+#pragma unroll
+            for (int k = 0; k < PIX / 16; ++k)
+              umma_bf16(tmem_base + tt * BN, da0 + ((k * 2048) >> 4), dbh + ((tt * p.dil * 128 + k * 2 * pitch) >> 4), idesc_h,
+                        (accum | k) ? 1u : 0u);
+          }
+          accum = 1;
+          umma_commit(&empty_bar[stage]);
+          if (++stage == stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+          continue;
+        }
         const uint64_t db0 = umma_smem_desc(sa + NSPLIT * L::kABytes, L::kGroupBytes, 1024);
         // Several taps per instruction: the X tiles of consecutive taps are consecutive 64-channel
         // groups in shared memory, exactly what one wider MMA (N = taps * BN <= 256) expects, and a
