@@ -217,6 +217,10 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   // three balanced groups of three taps at BN = 128 fill 144 (measured: 512->512 186 -> 172 us, 1024->512 369 -> 334 us;
   // the 256-wide layers are better off with BN = 256)
   if (nsplit == 1 && taps == 9 && Cin >= 512 && Cout >= 512 && env_int("CAN_B200_WGBN", 128) == 128) pl.bn = 128;
+  // With the halo X tile (hx below) the 128-wide three-tap tiles stay under the L2->SM fill rate (18-20 KB per 384 cycles of
+  // MMA) where the 256-wide two-tap ones need 40 KB per 512: every 3x3 layer with Cin >= 256 takes them (step 7.64 -> 7.49
+  // ms, `profiles/r02_wgbn256_ab.txt`; CAN_B200_WGBN256=256 keeps BN = 256 for Cin = 256 / Cout < 512).
+  if (nsplit == 1 && taps == 9 && Cin >= 256 && env_int("CAN_B200_WGBN256", 128) == 128) pl.bn = 128;
   // multi-tap tiles (bf16 path, BN >= 128): 64-80 KB stages would leave a 2-3 deep pipeline -> 32-pixel patches
   pl.pix = (nsplit == 1 && taps > 1 && (pl.bn == 256 || (pl.bn == 128 && env_int("CAN_B200_WGPIX128", 32) == 32)) &&
             env_int("CAN_B200_WGPIX", 32) == 32) ? 32 : 64;
