@@ -493,10 +493,13 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     g_tmO = &tmO;
     p.out_stage_bytes = 2 * bn * 256;
   }
-  if (ns == 1 && a->mode == CAN_MODE_STORE && bn == 256 && a->out && !a->out_f32 && env_int("CAN_B200_STAGE256", 0) != 0 &&
+  // (halo-A pairs have the shared memory to spare: two 16 KB staging tiles; 256->256 data gradient 164 -> 156 us, the
+  // other 256-wide launches unchanged, `profiles/r02_epi256_decomp.log`.  Without them it cost a ring stage: off.)
+  const int stage256 = env_int("CAN_B200_STAGE256", halo_a ? 2 : 0);
+  if (ns == 1 && a->mode == CAN_MODE_STORE && bn == 256 && a->out && !a->out_f32 && stage256 != 0 &&
       env_int("CAN_B200_TMASTORE", 1) != 0) {
-    // widest tiles (opt-in experiment): 64-channel blocks through two 16 KB staging tiles.  Measured 3 % SLOWER on the
-    // training step: the staging takes a fourth stage away from the operand ring, which matters more than the stores
+    // widest tiles: 64-channel blocks through two 16 KB staging tiles, written by TMA (before the halo-A pairs this took a
+    // fourth stage away from the operand ring and made the step 3 % slower)
     const uint64_t cs = static_cast<uint64_t>(a->out_cs) * 2;
     const uint64_t dimsO[4] = {static_cast<uint64_t>(a->Cout), static_cast<uint64_t>(a->W), static_cast<uint64_t>(a->H),
                                static_cast<uint64_t>(a->N)};
@@ -505,7 +508,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
     int rc = make_tmap(&tmO, static_cast<__nv_bfloat16*>(a->out) + a->out_coff, 4, dimsO, strO, boxO);
     if (rc) return rc;
     g_tmO = &tmO;
-    p.out_bufs = env_int("CAN_B200_STAGE256", 0) == 2 ? 2 : 1;
+    p.out_bufs = stage256 == 2 ? 2 : 1;
     p.out_stage_bytes = p.out_bufs * 16384;
   }
   if (ns == 1 && a->mode == CAN_MODE_STORE && (bn == 64 || bn == 128) && a->out && env_int("CAN_B200_TMASTORE", 1) != 0) {

@@ -798,7 +798,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int blk = 0; blk < BN / 64; ++blk, ++R) {
           const int nb = p.out_bufs, b = R % nb;
           mbar_wait(&out_full_bar[b], static_cast<uint32_t>(R / nb) & 1u);
-          tma_store_4d(&tmO, s_out + b * 16384, n0 + blk * 64, x0, y0, n_img);
+          // (a pair's dead tile goes through the hand-shakes but stores nothing: its threads wrote nothing to the buffer)
+          if (live_of(q_)) tma_store_4d(&tmO, s_out + b * 16384, n0 + blk * 64, x0, y0, n_img);
           bulk_commit_group();
           if (nb == 1) {
             bulk_wait_group_read0();
