@@ -222,8 +222,7 @@ WgradPlan wgrad_plan(int N, int H, int W, int Cin, int Cout, int taps, int nspli
   // ms, `profiles/r02_wgbn256_ab.txt`; CAN_B200_WGBN256=256 keeps BN = 256 for Cin = 256 / Cout < 512).
   if (nsplit == 1 && taps == 9 && Cin >= 256 && env_int("CAN_B200_WGBN256", 128) == 128) pl.bn = 128;
   // multi-tap tiles (bf16 path, BN >= 128): 64-80 KB stages would leave a 2-3 deep pipeline -> 32-pixel patches
-  pl.pix = (nsplit == 1 && taps > 1 && (pl.bn == 256 || (pl.bn == 128 && env_int("CAN_B200_WGPIX128", 32) == 32)) &&
-            env_int("CAN_B200_WGPIX", 32) == 32) ? 32 : 64;
+  pl.pix = (nsplit == 1 && taps > 1 && pl.bn >= 128) ? 32 : 64;
   pl.TW = (W >= 16) ? 16 : 8;
   // 128-wide three-tap tiles: the three X patches of a stage as shifted views of one halo tile (8-pixel patch rows)
   pl.hx = (nsplit == 1 && taps == 9 && pl.bn == 128 && pl.pix == 32 && dil <= 2 && env_int("CAN_B200_WGHX", 1) != 0) ? 1 : 0;
@@ -1077,10 +1076,8 @@ int conv_wgrad_impl(const void* dz, int64_t dz_plane, int dz_cs, int dz_coff, co
   if (pl.T > 1) {  // bf16 path, several taps per CTA
     if (pl.bn == 64) rc = launch_wgrad<64, 1, 3>(tmDZ, tmX, p, grid, st);
     else if (pl.hx) rc = launch_wgrad<128, 1, 3, 32, 1>(tmDZ, tmX, p, grid, st);
-    else if (pl.bn == 128 && pl.pix == 32) rc = launch_wgrad<128, 1, 3, 32>(tmDZ, tmX, p, grid, st);
-    else if (pl.bn == 128) rc = launch_wgrad<128, 1, 3>(tmDZ, tmX, p, grid, st);
-    else if (pl.pix == 32) rc = launch_wgrad<256, 1, 2, 32>(tmDZ, tmX, p, grid, st);
-    else rc = launch_wgrad<256, 1, 2>(tmDZ, tmX, p, grid, st);
+    else if (pl.bn == 128) rc = launch_wgrad<128, 1, 3, 32>(tmDZ, tmX, p, grid, st);
+    else rc = launch_wgrad<256, 1, 2, 32>(tmDZ, tmX, p, grid, st);
   } else if (pl.bn == 64) {
     rc = nsplit == 1   ? launch_wgrad<64, 1, 1>(tmDZ, tmX, p, grid, st)
          : nsplit == 2 ? launch_wgrad<64, 2, 1>(tmDZ, tmX, p, grid, st)
