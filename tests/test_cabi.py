@@ -84,3 +84,20 @@ def test_module_is_a_drop_in_without_gpu():
         m(torch.zeros(1, 3, 64, 64))  # no CPU fallback
     with pytest.raises(ValueError):
         m(torch.zeros(1, 1, 64, 64))
+
+
+def test_wgrad_workspace_query_covers_every_patch_shape(built, monkeypatch):
+    """can_conv_wgrad_workspace_bytes does not know the dilation, while the patch shape of the weight-gradient tiles (16 x 2
+    pixels, or 8 x 4 with the halo X tile for dil <= 2) and hence the split-K factor can depend on it: the query must
+    cover both plans, on ragged sizes too (host arithmetic only, no GPU)."""
+    lib = built.lib()
+    shapes = [(4, 96, 128, 512, 512), (1, 37, 41, 128, 128), (2, 23, 24, 256, 512), (1, 9, 21, 512, 512), (3, 50, 70, 256, 256)]
+    for N, H, W, Cin, Cout in shapes:
+        monkeypatch.delenv("CAN_B200_WGHX", raising=False)
+        q = lib.can_conv_wgrad_workspace_bytes(N, H, W, Cin, Cout, 9, 1)
+        monkeypatch.setenv("CAN_B200_WGHX", "0")
+        q_plain = lib.can_conv_wgrad_workspace_bytes(N, H, W, Cin, Cout, 9, 1)
+        per_split = 9 * Cout * Cin * 4
+        assert q > 0 and q % per_split == 0 and q_plain % per_split == 0
+        assert q >= q_plain, (N, H, W, Cin, Cout, q, q_plain)
+    assert lib.can_conv_wgrad_workspace_bytes(1, 8, 8, 60, 64, 9, 1) < 0   # Cin not a multiple of 64
