@@ -53,6 +53,7 @@ _SIGNATURES = {
     "can_pack_conv_weights_multi": (C.c_int, [C.POINTER(PackItem), C.c_int, C.c_int, C.c_void_p]),
     "can_pack_ctx_w2": (C.c_int, [C.c_void_p] * 5 + [C.c_int, C.c_void_p]),
     "can_transpose_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "can_transpose_f32_multi": (C.c_int, [C.POINTER(C.c_void_p), C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "can_conv_first_fwd": (C.c_int, [C.c_void_p] * 4 + [C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "can_ctx_pool_workspace_bytes": (C.c_int64, [C.c_int, C.c_int]),
     "can_ctx_pool_fwd": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]

@@ -157,8 +157,12 @@ def forward(model, x: torch.Tensor, nsplit: int, save: bool):
     # ---- contextual module (CANNet.py:42-87) --------------------------------------
     nvtx.push("can.fwd.context")
     w1s, w2s = _ctx_weights(model)
-    w1 = cache.get(("w1",), w1s, lambda: ops.stack_1x1(w1s))
-    w2 = cache.get(("w2",), w2s, lambda: ops.stack_1x1(w2s))
+    # (inside a FusedTrainer arena the four tables of a kind lie back to back: a view, no copy)
+    def stacked(ws):
+        v = _stacked_view([w_.detach() for w_ in ws])
+        return v if v is not None else ops.stack_1x1(ws)
+    w1 = cache.get(("w1",), w1s, lambda: stacked(w1s))
+    w2 = cache.get(("w2",), w2s, lambda: stacked(w2s))
     w2stack = cache.get(("w2stack", nsplit), w2s, lambda: ops.pack_ctx_w2(w2s, nsplit))
     pooled, tabA, tabB = ops.ctx_pool(fv, w1, w2)
     fi = cat.view(512, 512)
@@ -315,8 +319,8 @@ def backward_steps(model, saved, grad_out: torch.Tensor, grads=None):
     w1s, w2s = _ctx_weights(model)
     fv = cat.view(512, 0)
     w2stack = cache.get(("w2stack", nsplit), w2s, lambda: ops.pack_ctx_w2(w2s, nsplit))
-    w1t = cache.get(("w1t",), w1s, lambda: ops.transpose_stack(w1s))
-    w2t = cache.get(("w2t",), w2s, lambda: ops.transpose_stack(w2s))
+    wt = cache.get(("w12t",), w1s + w2s, lambda: ops.transpose_stack(w1s + w2s))   # eight W^T tables, one launch
+    w1t, w2t = wt[:4], wt[4:]
     D = ops.new_act(nsplit, N, h, w, 4096, dev)   # [dz_1..dz_6 | direct ds_1..ds_6], 512 channels each
     if saved.get("ttab") is not None:
         wint1 = cache.get(("wint", 1, h, w), (), lambda: ops.ctx_wint(1, 1, h, w, dev))

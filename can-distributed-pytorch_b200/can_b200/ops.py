@@ -175,12 +175,13 @@ def stack_1x1(ws) -> torch.Tensor:
 
 
 def transpose_stack(ws) -> torch.Tensor:
-    """[4] x [512(co),512(ci),1,1] -> [4][ci][co] fp32."""
+    """[n] x [512(co),512(ci),1,1] -> [n][ci][co] fp32, one launch for all n <= 16 matrices."""
+    import ctypes as C
     out = torch.empty(len(ws), 512, 512, device=ws[0].device, dtype=torch.float32)
-    for j, w in enumerate(ws):
-        w = w.detach().contiguous().float()
-        check(lib().can_transpose_f32(w.data_ptr(), out[j].data_ptr(), 512, 512, _stream()), "transpose_f32")
-        _count()
+    keep = [w.detach().contiguous().float() for w in ws]
+    ptrs = (C.c_void_p * len(keep))(*[w.data_ptr() for w in keep])
+    check(lib().can_transpose_f32_multi(ptrs, out.data_ptr(), len(keep), 512, 512, _stream()), "transpose_f32_multi")
+    _count()
     return out
 
 

@@ -721,6 +721,20 @@ int can_transpose_f32(const float* src, float* dst, int rows, int cols, void* st
   return 0;
 }
 
+int can_transpose_f32_multi(const float* const* srcs, float* dst, int n, int rows, int cols, void* stream) {
+  if (!srcs || !dst || n <= 0 || n > 16 || rows <= 0 || cols <= 0) return fail(-1, "transpose_f32_multi: bad arguments (n=%d)", n);
+  TransposeItems it;
+  memset(&it, 0, sizeof(it));
+  for (int i = 0; i < n; ++i) {
+    if (!srcs[i]) return fail(-1, "transpose_f32_multi: null matrix %d", i);
+    it.src[i] = srcs[i];
+  }
+  dim3 grid((cols + 31) / 32, (rows + 31) / 32, n), block(32, 8);
+  transpose_f32_multi_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(it, dst, rows, cols);
+  CAN_CHECK_LAUNCH("transpose_f32_multi");
+  return 0;
+}
+
 int can_conv_first_fwd(const float* x, const float* w, const float* b, void* out, int64_t out_plane, int nsplit,
                        int N, int H, int W, void* stream) {
   if (!x || !w || !b || !out || N <= 0 || H <= 0 || W <= 0 || nsplit < 1 || nsplit > 3)

@@ -94,6 +94,26 @@ __global__ void transpose_f32_kernel(const float* __restrict__ src, float* __res
   }
 }
 
+struct TransposeItems {
+  const float* src[16];
+};
+// n matrices of one shape in one launch (blockIdx.z = matrix); dst = [n][cols][rows]
+__global__ void transpose_f32_multi_kernel(TransposeItems it, float* __restrict__ dst, int rows, int cols) {
+  __shared__ float tile[32][33];
+  const float* __restrict__ src = it.src[blockIdx.z];
+  float* __restrict__ out = dst + static_cast<long long>(blockIdx.z) * rows * cols;
+  const int bx = blockIdx.x * 32, by = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = by + i, c = bx + threadIdx.x;
+    tile[i][threadIdx.x] = (r < rows && c < cols) ? src[static_cast<long long>(r) * cols + c] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = bx + i, r = by + threadIdx.x;
+    if (r < rows && c < cols) out[static_cast<long long>(c) * rows + r] = tile[threadIdx.x][i];
+  }
+}
+
 // --------------------------------------------------------------------------------
 // first convolution 3 -> 64, 3x3 pad 1, bias + ReLU.  K = 27 is too thin for the tensor
 // pipe; this is a direct fp32 conv bound by the 64-channel bf16 store (128 B / pixel).

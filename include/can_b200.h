@@ -115,6 +115,10 @@ int can_pack_conv_weights_multi(const can_pack_item* items, int n, int nsplit, v
 int can_pack_ctx_w2(const float* w1_2, const float* w2_2, const float* w3_2, const float* w6_2, void* dst,
                     int nsplit, void* stream);
 int can_transpose_f32(const float* src, float* dst, int rows, int cols, void* stream);
+/* The same for n <= 16 matrices of one shape in ONE launch: srcs is a HOST array of n device pointers, dst receives the
+ * n transposes back to back ([n][cols][rows]).  (The eight W^T tables of conv{1,2,3,6}_{1,2}, model/CANNet.py:18-25, that
+ * the backward of the contextual module needs after every optimizer step.)                                          */
+int can_transpose_f32_multi(const float* const* srcs, float* dst, int n, int rows, int cols, void* stream);
 
 /* First convolution 3->64 + bias + ReLU on the caller's NCHW fp32 image
  * (frontend.0 + frontend.1, model/CANNet.py:14,40). out: NHWC planes, cs = 64.               */
