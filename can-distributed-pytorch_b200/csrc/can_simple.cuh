@@ -732,25 +732,32 @@ ctx_wint_kernel(__nv_bfloat16* __restrict__ out, long long out_plane, int nsplit
 // (positions 50..63 are zero).  512 KB per image.
 __global__ void __launch_bounds__(256)
 ctx_ttab_kernel(const float* __restrict__ tabA, const float* __restrict__ tabB, __nv_bfloat16* __restrict__ T, int N) {
-  const long long per = 2048LL * 64;
-  const long long total = 2LL * N * per;
+  // one thread per 8 consecutive positions of a row (one 16-byte store); a row (which, n, cc, j, c) holds the table values
+  // of scale j only, so three quarters of the threads just write zeros
+  const int OFF[5] = {0, 1, 5, 14, 50};
+  const long long total = 2LL * N * 2048 * 8;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int pos = i & 63;
-    const int row = (i >> 6) & 2047;
-    const int n = (i / per) % N;
-    const int which = i / (per * N);
+    const int p0 = static_cast<int>(i & 7) * 8;
+    const int row = static_cast<int>(i >> 3) & 2047;
+    const long long img = i >> 14;            // which * N + n
+    const int n = static_cast<int>(img % N);
+    const int which = static_cast<int>(img / N);
     const int c = row & 63, j = (row >> 6) & 3, cc = row >> 8;
-    float v = 0.f;
-    if (pos < 50) {
-      int pj, S, wy, wx, xwin;
-      ctx_pos_decode(pos, pj, S, wy, wx, xwin);
-      if (pj == j) {
-        const long long src = (static_cast<long long>(n) * 50 + pos) * 512 + cc * 64 + c;
-        v = which == 0 ? -tabB[src] : tabA[src];
-      }
+    const float* __restrict__ tab = (which == 0 ? tabB : tabA) + static_cast<long long>(n) * 50 * 512 + cc * 64 + c;
+    const float sgn = which == 0 ? -1.f : 1.f;
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int pos = p0 + e;
+      v[e] = (pos >= OFF[j] && pos < OFF[j + 1]) ? sgn * tab[pos * 512] : 0.f;
     }
-    T[i] = __float2bfloat16_rn(v);
+    uint4 q;
+    q.x = pack_bf16x2(v[0], v[1]);
+    q.y = pack_bf16x2(v[2], v[3]);
+    q.z = pack_bf16x2(v[4], v[5]);
+    q.w = pack_bf16x2(v[6], v[7]);
+    *reinterpret_cast<uint4*>(T + i * 8) = q;
   }
 }
 
