@@ -416,7 +416,7 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
   // 16 KB A tile per tap and chunk a 128-wide pair tile needs 24 KB per 256 cycles of MMA (load-bound: 128->128 took
   // 222 us where its MMAs need ~130) and a 256-wide one 32 KB per 512 (just balanced).  The halo tile cuts the A traffic
   // by 6 (dil 1) / 4.7 (dil 2).  Tile = 8 x 16 pixels, as the 8-row groups of A must be whole patch rows.
-  const bool halo_a = !halo && a->nsplit == 1 && a->taps == 9 && (bn == 128 || bn == 256) && a->W >= 8 &&
+  const bool halo_a = !halo && a->nsplit == 1 && a->taps == 9 && (bn == 128 || bn == 256) && a->W >= 8 && a->dil <= 2 &&
                       (a->mode == CAN_MODE_STORE || a->mode == CAN_MODE_POOL || a->mode == CAN_MODE_UNPOOL) &&
                       env_int("CAN_B200_PAIR", 1) != 0 && env_int("CAN_B200_HALOA", 1) != 0;
   if (halo_a) p.TW = 8;
@@ -528,7 +528,9 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
       rc = make_tmap(&tmM, static_cast<const __nv_bfloat16*>(a->mask) + a->mask_coff, 4, dimsO, strM, boxO);
       if (rc) return rc;
       g_tmM = &tmM;
-      p.mask_bufs = env_int("CAN_B200_MASKBUFS", (bn == 64 || halo_a) ? 2 : 1);   // (halo-A pairs: 128->128 dgrad 217 -> 193 us with two)
+      // (halo-A pairs: 128->128 dgrad 217 -> 193 us with two; with the 30 KB halo stages of dil 2 a second buffer would
+      // leave the weight ring two stages)
+      p.mask_bufs = env_int("CAN_B200_MASKBUFS", (bn == 64 || (halo_a && a->dil == 1)) ? 2 : 1);
     }
   }
   // small-Cin layers on the bf16 path: resident weights + halo stages (L2->SM traffic / 3.6, / 9 with one halo tile)

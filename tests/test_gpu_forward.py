@@ -72,6 +72,10 @@ CONV_CASES = [
     (1, 16, 8, 64, 64, 1, 0),      # W < 16 -> 16x8 patch
     (1, 24, 16, 256, 512, 1, 256), # three pixel tiles x two n-tiles
     (3, 8, 16, 512, 256, 2, 256),  # one n-tile, three pixel tiles
+    (1, 24, 24, 256, 256, 3, 0),   # dil 3: not a halo-A pair (the halo stages would not fit), pairs with one A tile per tap
+    (1, 20, 12, 128, 128, 3, 0),   # same, 128 wide (two k-chunks per stage)
+    (3, 16, 8, 256, 256, 1, 0),    # three 8x16 pixel tiles: the pair's dead tile next to the staged TMA stores
+    (1, 40, 24, 64, 256, 1, 0),    # one channel chunk per halo-A tile
 ]
 
 
