@@ -28,16 +28,15 @@ cap() {  # tag, regex, launches to skip inside the profiled step, workload, batc
   ncu -i $OUT/prof_$1.ncu-rep --page details > $OUT/prof_$1.details.txt 2>/dev/null
   case " $KEEP_REP " in *" $1 "*) ;; *) rm -f $OUT/prof_$1.ncu-rep ;; esac
 }
-cap pair_store512      "$(rx conv_tc_kernel 256 1 0 0 4 1)"  3 train 4    # 512->512 3x3 @96x128, CTA pairs (dominant kernel)
-cap pair_store512_b16  "$(rx conv_tc_kernel 256 1 0 0 4 1)"  3 infer 16
+cap pair_store512      "$(rx conv_tc_kernel 256 1 0 0 4 2)"  3 train 4    # 512->512 3x3 @96x128, halo-A CTA pairs (dominant kernel)
+cap pair_store512_b16  "$(rx conv_tc_kernel 256 1 0 0 4 2)"  3 infer 16
 cap unpool_halo128_64  "$(rx conv_tc_kernel 64 1 3 1 8 0)"   0 train 4    # max-unpool 128->64 @384x512 (HALO)
-cap unpool_pair256_128 "$(rx conv_tc_kernel 128 1 3 0 8 1)"  0 train 4    # max-unpool 256->128 @192x256 (pairs)
-cap unpool_pair512_256 "$(rx conv_tc_kernel 256 1 3 0 4 1)"  0 train 4    # max-unpool 512->256 @96x128 (pairs)
+cap unpool_pair256_128 "$(rx conv_tc_kernel 128 1 3 0 8 2)"  0 train 4    # max-unpool 256->128 @192x256 (halo-A pairs)
+cap unpool_pair512_256 "$(rx conv_tc_kernel 256 1 3 0 4 2)"  0 train 4    # max-unpool 512->256 @96x128 (halo-A pairs)
 cap ctx2               "$(rx conv_tc_kernel 256 1 7)"            0 train 4
 cap ctx2_bwd           "$(rx conv_tc_kernel 256 1 8)"            0 train 4
 cap dfv                "$(rx conv_tc_kernel 256 1 6)"            0 train 4
-cap wgrad_128_3_32     "$(rx wgrad_tc_kernel 128 1 3 32)"      1 train 4    # 512->512 weight gradient
-cap wgrad_256_2_32     "$(rx wgrad_tc_kernel 256 1 2 32)"      0 train 4
+cap wgrad_128_3_32     "$(rx wgrad_tc_kernel 128 1 3 32 1)"    3 train 4    # 512->512 weight gradient (halo X tile)
 cap wgrad_swap64       'wgrad_tc_swap64_kernel'              0 train 4
 cap k1_rows            'ctx_pool_rows_kernel_v3'             0 infer 16
 ls -la $OUT/prof_* ; du -sh $OUT
