@@ -72,6 +72,8 @@ _SIGNATURES = {
                        + [C.c_int] * 8 + [C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_int64, C.c_void_p]),
     "can_ctx_wint": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "can_ctx_ttab": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "can_ctx_pint": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "can_ctx_dtab": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "can_ctx_pos_gemv": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                    C.c_int, C.c_void_p]),
     "can_ctx_outer": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int, C.c_void_p,

@@ -361,8 +361,14 @@ def backward_steps(model, saved, grad_out: torch.Tensor, grads=None):
     w2d = cache.get(("w2d", nsplit), w2s, lambda: ops.pack_conv_weight(
         torch.cat([wj.detach().float().reshape(512, 512).t() for wj in w2s], dim=1).reshape(512, 2048, 1, 1), nsplit))
     dz = ops.new_act(nsplit, N, h, w, 512, dev)
+    pint = dtab = None
+    if nsplit == 1:
+        # bf16 path: the pooling-transpose term as one more k-block of the same GEMM (the kernel takes it when the launch
+        # runs as 256-wide CTA pairs, else it adds the table rows in its epilogue as the fp32 path does)
+        pint = cache.get(("pint", h, w), (), lambda: ops.ctx_pint(h, w, dev))
+        dtab = ops.ctx_dtab(dpool)
     ops.conv_tc(D.view(2048, 0), w2d, 512, taps=1, mode=MODE_DFV, relu=False, out=dz, mask=fv, add=dcat.view(512, 0),
-                tabA=dpool, db=grads[2 * 9 + 1])
+                tabA=dpool, db=grads[2 * 9 + 1], ctx_wint=pint, ctx_ttab=dtab)
     nvtx.pop()
     yield "ctx"
     nvtx.push("can.bwd.frontend")

@@ -414,6 +414,23 @@ def ctx_ttab(tabA, tabB):
     return T
 
 
+def ctx_pint(H, W, device) -> torch.Tensor:
+    """[H][W][64] bf16: -1/area of every pooled window a pixel lies in (A operand of MODE_DFV's extra k-block)."""
+    out = torch.empty(H, W, 64, device=device, dtype=torch.bfloat16)
+    check(lib().can_ctx_pint(out.data_ptr(), H, W, _stream()), "ctx_pint")
+    _count()
+    return out
+
+
+def ctx_dtab(dpool: torch.Tensor) -> torch.Tensor:
+    """dpool [N][50][512] fp32 -> [N][512][64] bf16 (B operand of MODE_DFV's extra k-block)."""
+    N = dpool.shape[0]
+    out = torch.empty(N, 512, 64, device=dpool.device, dtype=torch.bfloat16)
+    check(lib().can_ctx_dtab(dpool.data_ptr(), out.data_ptr(), N, _stream()), "ctx_dtab")
+    _count()
+    return out
+
+
 def ctx_ut(wint: Act, x: Act) -> torch.Tensor:
     """U^T x for all images in one launch (bf16 path): returns [64 pos][B][C] fp32."""
     assert wint.nsplit == 1 and x.nsplit == 1 and wint.N == 1 and wint.C == 64

@@ -661,6 +661,23 @@ int can_conv_tc(const can_conv_args* a, void* stream) {
       g_tmW = nullptr;
       return rc;
     }
+    CUtensorMap tmP, tmD;   // MODE_DFV: pooling-transpose matrix (A) and the pooled-map gradient rows (B) of the extra k-block
+    if (m == CAN_MODE_DFV && bn == 256 && a->ctx_wint && a->ctx_ttab && env_int("CAN_B200_DFVKB", 1) != 0) {
+      rc = make_act_tmap(&tmP, a->ctx_wint, 0, 64, 64, 0, 1, 1, a->H, a->W, p.TW, p.TH);
+      if (rc) return rc;
+      const uint64_t dimsD[3] = {64, static_cast<uint64_t>(a->Cout), static_cast<uint64_t>(a->N)};
+      const uint64_t strD[2] = {128, 128ull * a->Cout};
+      const uint32_t boxD[3] = {64, static_cast<uint32_t>(bn / 2), 1};
+      rc = make_tmap(&tmD, a->ctx_ttab, 3, dimsD, strD, boxD);
+      if (rc) return rc;
+      p.dfv_kb = 1;
+      g_tmW = &tmP;
+      g_tmT = &tmD;
+      rc = launch_conv<256, 1, MODE_DFV, 1>(tmA, tmBh, p, pg, so, st);
+      g_tmW = nullptr;
+      g_tmT = nullptr;
+      return rc;
+    }
     if (bn == 256) {
       switch (m) {
         case CAN_MODE_STORE: return launch_conv<256, 1, MODE_STORE, 1>(tmA, tmBh, p, pg, so, st);
@@ -1278,6 +1295,20 @@ int can_ctx_wint(void* out, int64_t out_plane, int nsplit, int N, int H, int W, 
   ctx_wint_kernel<<<148 * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<__nv_bfloat16*>(out), out_plane,
                                                                          nsplit, N, H, W);
   CAN_CHECK_LAUNCH("ctx_wint");
+  return 0;
+}
+
+int can_ctx_pint(void* out, int H, int W, void* stream) {
+  if (!out || H <= 0 || W <= 0) return fail(-1, "ctx_pint: bad arguments");
+  ctx_pint_kernel<<<148 * 4, 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<__nv_bfloat16*>(out), H, W);
+  CAN_CHECK_LAUNCH("ctx_pint");
+  return 0;
+}
+
+int can_ctx_dtab(const float* dpool, void* D, int N, void* stream) {
+  if (!dpool || !D || N <= 0) return fail(-1, "ctx_dtab: bad arguments");
+  ctx_dtab_kernel<<<148, 256, 0, static_cast<cudaStream_t>(stream)>>>(dpool, static_cast<__nv_bfloat16*>(D), N);
+  CAN_CHECK_LAUNCH("ctx_dtab");
   return 0;
 }
 

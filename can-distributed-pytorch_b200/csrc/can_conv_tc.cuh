@@ -49,6 +49,8 @@ struct ConvTcParams {
   int halo_stride;     // HALO: distance between stages (halo_bytes rounded up to 1024)
   int halo1;           // HALO: one halo tile per (pixel tile, channel chunk) serves all nine taps
   int n_a;             // PAIR == 2: number of A halo stages (each halo_stride bytes) in front of the weight ring
+  int dfv_kb;          // MODE_DFV as a pair, BN = 256: the pooling-transpose term is one more k-block (A = tmW: can_ctx_pint
+                       // tile, B = tmT: can_ctx_dtab rows) instead of thirteen table rows per pixel in the epilogue
   int out_stage_bytes; // > 0: the epilogue stages the bf16 tile in shared memory (BN * 256 B) and writes it with TMA (tmO)
   int out_bufs;        // MODE_STORE staged epilogue: 1 or 2 staging buffers of BN * 256 B (out_stage_bytes = their sum)
   int mask_bufs;       // staged epilogue: 0 = mask read from global memory, 1|2 = mask tiles (BN * 256 B each) brought in by TMA (tmM)
@@ -317,7 +319,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   // MODE_CTX2: two extra k-blocks whose A operand is the interpolation matrix Wint[pixel][64 positions]
   // and whose B operands are the per-image tables (-U-side of z, then s) -- see the epilogue.
   constexpr bool kCtx2 = (MODE == MODE_CTX2 || MODE == MODE_CTX2_BWD);
-  const int num_kb = base_kb + (kCtx2 ? 2 : 0);
+  constexpr bool kDfvX = MODE == MODE_DFV && PAIR == 1 && BN == 256;   // (see ConvTcParams::dfv_kb)
+  const int num_kb = base_kb + (kCtx2 ? 2 : 0) + (kDfvX ? p.dfv_kb : 0);
   // Persistent CTA: tiles blockIdx.x, blockIdx.x + gridDim.x, ...; the n-tile index varies fastest so
   // that CTAs working at the same time share the activation patch in L2.
 #define CAN_TILE_DECODE(tile)                                   \
@@ -338,6 +341,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tma_prefetch_desc(&tmT);
     }
     if (HA) tma_prefetch_desc(&tmW);
+    if (kDfvX && p.dfv_kb) {
+      tma_prefetch_desc(&tmW);
+      tma_prefetch_desc(&tmT);
+    }
     if (p.out_stage_bytes) tma_prefetch_desc(&tmO);
     if (p.mask_bufs) tma_prefetch_desc(&tmM);
   }
@@ -526,6 +533,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             advance();
           }
+        }
+        if (kDfvX && p.dfv_kb) {
+          // one extra k-block: A = the pooling-transpose matrix of this CTA's pixel tile, B = its half of the image's
+          // pooled-map gradient rows
+          mbar_wait(ebar, phase ^ 1);
+          if (leader) mbar_expect_tx(fbar, 2 * kStageSz);
+          tma_load_5d_pair(sa, &tmW, fb, 0, x0, y0, 0, 0);
+          tma_load_3d_pair(sa + L::kABytes, &tmT, fb, 0, nB, n_img);
+          advance();
         }
         if (kCtx2) {
           // two extra k-blocks: A = the interpolation matrix of this pixel tile, B = the per-image tables
@@ -912,7 +928,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             *reinterpret_cast<const float4*>(gb + pos * 512 + c4);
       }
     }
-    if (MODE == MODE_DFV) {
+    if (MODE == MODE_DFV && !(kDfvX && p.dfv_kb)) {
       // dpool table of this image for the BN channels of this n-tile -> shared memory ([50][BN] fp32).  The
       // epilogue reads 13 of its rows per pixel and channel group; from global memory those reads miss the (small)
       // L1 next to a 200 KB shared-memory carve-out and pay the L2 latency 104 times per 32 channels.
@@ -1628,7 +1644,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int OFF[4] = {0, 1, 5, 14};
       int spos[13];
       float swgt[13];
-      {
+#pragma unroll
+      for (int k = 0; k < 13; ++k) {
+        spos[k] = 0;
+        swgt[k] = 0.f;
+      }
+      if (!(kDfvX && p.dfv_kb)) {   // (with the extra k-block the accumulator already holds this term)
         const int yy = min(y, p.H - 1), xx = min(x, p.W - 1);
         int k = 0;
 #pragma unroll
@@ -1691,6 +1712,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (valid) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = -r[i];
+          if (!(kDfvX && p.dfv_kb))
 #pragma unroll
           for (int k = 0; k < 13; ++k) {
             const float wk = swgt[k];

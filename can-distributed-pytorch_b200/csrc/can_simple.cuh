@@ -726,6 +726,54 @@ ctx_wint_kernel(__nv_bfloat16* __restrict__ out, long long out_plane, int nsplit
   }
 }
 
+// Transpose of the adaptive average pooling of the four scales as an NHWC "activation", negated:
+//   out[y][x][pos] = -1 / area(window pos)  if pixel (y, x) lies in window pos (0..49, scale-major; windows overlap when the
+//   size does not divide), else 0; positions 50..63 are zero.  A operand of MODE_DFV's extra k-block:
+//   acc[pixel][c] -= sum_pos (1 / area) [pixel in pos] dpool[pos][c]   (CANNet.py:42,51,60,70 backwards).
+__global__ void __launch_bounds__(256)
+ctx_pint_kernel(__nv_bfloat16* __restrict__ out, int H, int W) {
+  const long long total = static_cast<long long>(H) * W * 64;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int pos = i & 63;
+    const long long pix = i >> 6;
+    const int x = pix % W;
+    const int y = pix / W;
+    float wv = 0.f;
+    if (pos < 50) {
+      int j, S, wy, wx, xwin;
+      ctx_pos_decode(pos, j, S, wy, wx, xwin);
+      const int ys = adaptive_start(wy, H, S), ye = adaptive_end(wy, H, S);
+      const int xs = adaptive_start(wx, W, S), xe = adaptive_end(wx, W, S);
+      if (y >= ys && y < ye && x >= xs && x < xe) wv = -1.f / static_cast<float>((ye - ys) * (xe - xs));
+    }
+    out[i] = __float2bfloat16_rn(wv);
+  }
+}
+
+// B operand of that k-block (K-major, 64 positions per row): D[n][c][pos] = dpool[n][pos][c], positions 50..63 zero.
+// One thread per 8 positions of a row (one 16-byte store).
+__global__ void __launch_bounds__(256)
+ctx_dtab_kernel(const float* __restrict__ dpool, __nv_bfloat16* __restrict__ D, int N) {
+  const long long total = static_cast<long long>(N) * 512 * 8;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int p0 = static_cast<int>(i & 7) * 8;
+    const int c = static_cast<int>(i >> 3) & 511;
+    const long long n = i >> 12;
+    const float* __restrict__ tab = dpool + n * 50 * 512 + c;
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = (p0 + e < 50) ? tab[(p0 + e) * 512] : 0.f;
+    uint4 q;
+    q.x = pack_bf16x2(v[0], v[1]);
+    q.y = pack_bf16x2(v[2], v[3]);
+    q.z = pack_bf16x2(v[4], v[5]);
+    q.w = pack_bf16x2(v[6], v[7]);
+    *reinterpret_cast<uint4*>(D + i * 8) = q;
+  }
+}
+
 // Per-image B operands of the two extra k-blocks of MODE_CTX2 (K-major, 64 positions per row):
 //   T[0][n][(cc*4 + j)*64 + c][pos] = -tabB[n][pos][cc*64 + c]  if pos belongs to scale j, else 0
 //   T[1][n][(cc*4 + j)*64 + c][pos] =  tabA[n][pos][cc*64 + c]  if pos belongs to scale j, else 0

@@ -75,8 +75,8 @@ typedef struct can_conv_args {
   float* head_out;       /* HEAD: [N][H][W] fp32 density                                      */
   const float* tabA;     /* CTX: [N][50][512] a_j = conv{S}_1(pool_S(fv))                     */
   const float* tabB;     /* CTX: [N][50][512] b_j = conv{S}_2(a_j)                            */
-  const void* ctx_wint;  /* CTX2: can_ctx_wint(nsplit 1, N 1) interpolation matrix [H][W][64] bf16 */
-  const void* ctx_ttab;  /* CTX2: can_ctx_ttab tables [2][N][2048][64] bf16                      */
+  const void* ctx_wint;  /* CTX2: can_ctx_wint(nsplit 1, N 1) interpolation matrix [H][W][64] bf16; DFV: can_ctx_pint (optional) */
+  const void* ctx_ttab;  /* CTX2: can_ctx_ttab tables [2][N][2048][64] bf16; DFV: can_ctx_dtab (optional)                */
   float* db;             /* STORE/UNPOOL/DFV (dgrad use): [Cout] += per-channel sums of the stored
                             tile = bias gradient of the layer whose dZ this launch produces; NULL = off */
 } can_conv_args;
@@ -248,6 +248,14 @@ int can_ctx_ut(const void* wint, int wint_cs, const void* x, int x_cs, int x_cof
                void* ws, int64_t ws_bytes, void* stream);
 /* CTX2 operands: T[0][n][(cc*4+j)*64+c][pos] = -tabB[n][pos][cc*64+c], T[1] = +tabA (zero outside scale j). */
 int can_ctx_ttab(const float* tabA, const float* tabB, void* T, int N, void* stream);
+/* MODE_DFV with the transpose of the adaptive average pooling (the gradient of model/CANNet.py:42,51,60,70) as one more
+ * k-block of its GEMM instead of thirteen table rows per pixel in the epilogue (bf16 path, CTA pairs, 256-wide tiles):
+ *   can_ctx_pint: A operand, [H][W][64] bf16, -1/area(window) where the pixel lies in pooled position pos (image-
+ *                 independent: build once per feature-map size); pass it as can_conv_args.ctx_wint;
+ *   can_ctx_dtab: B operand, [N][512][64] bf16 = the pooled-map gradient dpool [N][50][512] fp32 transposed; pass it as
+ *                 can_conv_args.ctx_ttab (tabA must still be given: small shapes keep the epilogue form).          */
+int can_ctx_pint(void* out, int H, int W, void* stream);
+int can_ctx_dtab(const float* dpool, void* D, int N, void* stream);
 int can_ctx_pos_gemv(const float* Wm, const float* in, int64_t in_ns, int64_t in_ps, int64_t in_js,
                      const float* add, float* out, int N, void* stream);
 int can_ctx_outer(const float* A, int64_t a_ns, int64_t a_ps, int64_t a_js, const float* B, int N, float* dW,
