@@ -1148,14 +1148,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               *reinterpret_cast<uint4*>(abase + c0 + 16) = make_uint4(codes[4], codes[5], codes[6], codes[7]);
             }
           }
-          continue;
-        }
+        } else {   // fp32 path: per-channel exchange on the full-precision values
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           // floor-mode pooling only writes windows that lie fully inside the image, so the
           // garbage computed for out-of-image tile pixels never reaches a written window.
           float a = fmaxf(r[i] + v[i], 0.f);
-          if (NSPLIT == 1) a = bf16_round(a);  // ties are decided on the stored precision
           float mx = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, 1));
           mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, p.TW));
           int code = (a == mx) ? pos : 4;
@@ -1170,6 +1168,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             *reinterpret_cast<uint4*>(abase + c0) = make_uint4(codes[0], codes[1], codes[2], codes[3]);
             *reinterpret_cast<uint4*>(abase + c0 + 16) = make_uint4(codes[4], codes[5], codes[6], codes[7]);
           }
+        }
         }
       }
     } else if (MODE == MODE_HEAD) {
