@@ -10,6 +10,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "can-distributed-pytorch_b200"))
 # the bring-up build (`make -C can-distributed-pytorch_b200/csrc decomp`): the product library has no such switches in its loops
 os.environ.setdefault("CAN_B200_LIB", os.path.join(ROOT, "can-distributed-pytorch_b200", "can_b200", "libcan_b200_decomp.so"))
+if not os.path.exists(os.environ["CAN_B200_LIB"]):
+    sys.exit(f"{os.environ['CAN_B200_LIB']} not found: build it with `make -C can-distributed-pytorch_b200/csrc decomp`")
 from can_b200 import ops  # noqa: E402
 
 SHAPES = [(4, 384, 512, 128, 128), (4, 96, 128, 512, 512), (4, 192, 256, 256, 256), (4, 192, 256, 128, 256)]
