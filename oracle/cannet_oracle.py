@@ -144,6 +144,21 @@ def adaptive_avg_pool(x, s):
     return out
 
 
+def pool_transpose_matrix(h: int, w: int, scales=(1, 2, 3, 6), dtype=np.float64):
+    """[h][w][50]: entry (y, x, pos) = 1 / area(window pos) if pixel (y, x) lies in pooled position pos (scale-major,
+    row-major inside a scale), else 0 -- the transpose of F.adaptive_avg_pool2d for the four scales of
+    model/CANNet.py:42,51,60,70, i.e. d fv[y][x] = sum_pos M[y][x][pos] * d pooled[pos] (windows overlap when the size
+    does not divide: AdaptivePooling.h:32-38)."""
+    m = np.zeros((h, w, sum(s * s for s in scales)), dtype=dtype)
+    pos = 0
+    for s in scales:
+        for (y0, y1) in adaptive_windows(h, s):
+            for (x0, x1) in adaptive_windows(w, s):
+                m[y0:y1, x0:x1, pos] = 1.0 / ((y1 - y0) * (x1 - x0))
+                pos += 1
+    return m
+
+
 def conv1x1(x, w, b=None):
     out = np.einsum("kc,nchw->nkhw", w[:, :, 0, 0], x, optimize=True)
     if b is not None:

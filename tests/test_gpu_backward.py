@@ -297,3 +297,22 @@ def test_first_layer_fused_kernels_match_im2col_path(dev, shape):
     g_acc = g_fused.clone()
     ops.conv_first_wgrad(dza, x, g_acc, accumulate=True, alpha=0.5)
     assert harness.rel_l2(g_acc.cpu(), 1.5 * wg.grad) < 1e-5
+
+
+@pytest.mark.parametrize("hw", [(13, 17), (48, 64), (9, 21), (96, 128)])
+def test_pool_transpose_operands_match_oracle(dev, hw):
+    """can_ctx_pint / can_ctx_dtab (the A and B operands of MODE_DFV's extra k-block): bit-exact against the oracle's
+    pooling-transpose matrix rounded to bf16, and a plain transpose + rounding of the pooled-map gradient."""
+    from can_b200 import ops
+    from oracle import cannet_oracle as O
+    h, w = hw
+    got = ops.ctx_pint(h, w, dev).float().cpu()
+    want = torch.zeros(h, w, 64)
+    want[:, :, :50] = -torch.from_numpy(O.pool_transpose_matrix(h, w, dtype=np.float32))
+    assert torch.equal(got, want.bfloat16().float())
+    g = torch.Generator().manual_seed(6)
+    dpool = torch.randn(3, 50, 512, generator=g)
+    d = ops.ctx_dtab(dpool.to(dev)).float().cpu()
+    ref = torch.zeros(3, 512, 64)
+    ref[:, :, :50] = dpool.transpose(1, 2)
+    assert torch.equal(d, ref.bfloat16().float())

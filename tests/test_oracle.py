@@ -130,3 +130,27 @@ def test_sgd_oracle_matches_torch():
         opt.step()
         pn, buf = O.sgd_momentum_step(pn, g.numpy(), buf, 1e-3, 0.95)
     assert np.allclose(q.detach().numpy(), pn, rtol=1e-14)
+
+
+@pytest.mark.parametrize("hw", [(13, 17), (48, 64), (9, 21), (6, 6), (50, 70)])
+def test_pool_transpose_matrix_is_the_autograd_of_adaptive_avg_pool(hw):
+    """The A operand of MODE_DFV's extra k-block (can_ctx_pint = minus this matrix) against torch autograd of
+    F.adaptive_avg_pool2d for the four scales (model/CANNet.py:42,51,60,70), ragged sizes with overlapping windows too."""
+    import torch
+    import torch.nn.functional as F
+    h, w = hw
+    m = O.pool_transpose_matrix(h, w)
+    assert m.shape == (h, w, 50)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(1, 3, h, w, generator=g, dtype=torch.float64, requires_grad=True)
+    dps = [torch.randn(1, 3, s, s, generator=g, dtype=torch.float64) for s in (1, 2, 3, 6)]
+    loss = sum((F.adaptive_avg_pool2d(x, (s, s)) * dp).sum() for s, dp in zip((1, 2, 3, 6), dps))
+    loss.backward()
+    dpool = torch.cat([dp.reshape(1, 3, -1) for dp in dps], dim=2)[0].numpy()        # [c][50], scale-major
+    want = x.grad[0].numpy()                                                          # [c][h][w]
+    got = np.einsum("yxp,cp->cyx", m, dpool)
+    assert np.allclose(got, want, rtol=1e-12, atol=1e-12)
+    # every pixel lies in at least one window of every scale, in at most two per axis
+    for s, off in ((1, 0), (2, 1), (3, 5), (6, 14)):
+        cnt = (m[:, :, off:off + s * s] > 0).sum(axis=2)
+        assert cnt.min() >= 1 and cnt.max() <= 4
