@@ -316,3 +316,15 @@ def test_pool_transpose_operands_match_oracle(dev, hw):
     ref = torch.zeros(3, 512, 64)
     ref[:, :, :50] = dpool.transpose(1, 2)
     assert torch.equal(d, ref.bfloat16().float())
+
+
+def test_transpose_multi_is_exact(dev):
+    """can_transpose_f32_multi (the eight W^T tables of the contextual backward in one launch) against torch."""
+    from can_b200 import ops
+    g = torch.Generator().manual_seed(7)
+    ws = [torch.randn(512, 512, 1, 1, generator=g).to(dev) for _ in range(8)]
+    got = ops.transpose_stack(ws)
+    torch.cuda.synchronize()
+    assert got.shape == (8, 512, 512)
+    for j, w in enumerate(ws):
+        assert torch.equal(got[j], w.reshape(512, 512).t())
