@@ -6,6 +6,7 @@ where the tensor occupies channels ``[coff, coff + C)`` of the pixel stride ``cs
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 
 import torch
@@ -94,10 +95,34 @@ class Act:
         return out
 
 
+_RESERVED = {}   # device index -> bytes the caching allocator had reserved when a large buffer was last allocated
+_COLD_READ_MIN = 512 << 20
+
+
+def _read_if_fresh(t: torch.Tensor) -> None:
+    """One ordinary read pass over a LARGE buffer that made the caching allocator fetch new device memory.
+
+    On this pool's B200s the first TMA loads from feature maps of >= ~0.5 GiB whose pages no kernel had read before die,
+    rarely, with an "unspecified launch failure" (`profiles/r02_k1_cold_page_fault.txt`: never on a
+    second call, never after an ordinary read pass).  Memory the allocator hands out again has been read, so this runs on
+    the first calls of a process at a new size only (0.2 ms per GB); not during graph capture.  CAN_B200_COLD_READ=0: off."""
+    if t.numel() * t.element_size() < _COLD_READ_MIN or not t.is_cuda or os.environ.get("CAN_B200_COLD_READ", "1") != "1":
+        return
+    if torch.cuda.is_current_stream_capturing():
+        return
+    idx = t.device.index if t.device.index is not None else torch.cuda.current_device()
+    reserved = torch.cuda.memory_reserved(idx)
+    if reserved > _RESERVED.get(idx, 0):
+        _RESERVED[idx] = reserved
+        t.view(-1).view(torch.int32).sum()   # (an ATen reduction: plain loads of every byte; the value is dropped)
+
+
 def new_act(nsplit, N, H, W, C, device, cs=None, zero=False) -> Act:
     cs = cs or C
     f = torch.zeros if zero else torch.empty
-    return Act(f(nsplit, N, H, W, cs, device=device, dtype=torch.bfloat16), C, 0)
+    buf = f(nsplit, N, H, W, cs, device=device, dtype=torch.bfloat16)
+    _read_if_fresh(buf)
+    return Act(buf, C, 0)
 
 
 def act_from_nchw(x: torch.Tensor, nsplit: int) -> Act:
