@@ -49,3 +49,15 @@ def test_engine_sections_push_and_pop_in_pairs():
     for mod in (eng, tu):
         src = inspect.getsource(mod)
         assert src.count("nvtx.push(") == src.count("nvtx.pop()") and src.count("nvtx.push(") > 0
+
+
+def test_cold_read_pass_ignores_small_and_cpu_buffers(monkeypatch):
+    """ops._read_if_fresh (the one-off read pass over freshly allocated activation buffers >= 512 MB)
+    must be free for everything else: CPU tensors and small buffers return before any CUDA call."""
+    from can_b200 import ops
+    called = []
+    monkeypatch.setattr(torch.cuda, "memory_reserved", lambda *a, **k: called.append(1) or 0)
+    ops._read_if_fresh(torch.empty(16))
+    ops._read_if_fresh(torch.empty(1 << 20, dtype=torch.bfloat16))
+    assert not called
+    assert ops._COLD_READ_MIN == 512 << 20
